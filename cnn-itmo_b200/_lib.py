@@ -1,0 +1,74 @@
+"""ctypes binding of libitmo_b200.so (include/itmo_b200.h).
+
+The library is the product: there is no CPU or PyTorch fallback. Importing this module without the
+built library, or calling into it on a machine without an sm_100 GPU, raises.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from ctypes import POINTER, c_char_p, c_float, c_int, c_longlong, c_size_t, c_uint, c_void_p
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, 'libitmo_b200.so')
+
+PREC_TF32, PREC_BF16 = 0, 1
+DT_U8, DT_F32 = 0, 1
+NUM_LAYERS = 19
+
+
+class LayerWeights(ctypes.Structure):
+    _fields_ = [(n, POINTER(c_float)) for n in
+                ('kernel', 'bias', 'gamma', 'beta', 'moving_mean', 'moving_variance')]
+
+
+class ItmoError(RuntimeError):
+    pass
+
+
+_lib = None
+
+# every symbol include/itmo_b200.h declares: name -> (restype, argtypes)
+SIGNATURES = {
+    'itmo_last_error': (c_char_p, []),
+    'itmo_abi_version': (c_int, []),
+    'itmo_create': (c_int, [POINTER(c_void_p), c_int, c_int, c_int]),
+    'itmo_destroy': (None, [c_void_p]),
+    'itmo_load_weights': (c_int, [c_void_p, POINTER(LayerWeights), c_int, c_float]),
+    'itmo_forward': (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_int, c_uint, c_void_p]),
+    'itmo_predict_host': (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_int, c_uint]),
+    'itmo_launch_count': (c_longlong, [c_void_p]),
+    'itmo_read_activation': (c_int, [c_void_p, c_int, c_int, POINTER(c_float), c_size_t, POINTER(c_size_t)]),
+    'itmo_conv3x3_bn': (c_int, [c_int, c_void_p, c_int, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p,
+                                c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
+    'itmo_convT2x2_bn': (c_int, [c_int, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
+                                 c_int, c_void_p, c_void_p]),
+    'itmo_conv3x3_bn_head': (c_int, [c_int, c_void_p, c_int, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p,
+                                     c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
+    'itmo_conv3x3_bn_rgb': (c_int, [c_int, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
+                                    c_void_p, c_int, c_void_p, c_void_p]),
+}
+
+
+def load():
+    """Load libitmo_b200.so (once) and set the prototypes. Raises ItmoError if it is not built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ItmoError(
+            f'{LIB_PATH} is missing: build it with `python -c "import __graft_entry__ as g; g.build()"` '
+            '(nvcc, sm_100a). There is no CPU fallback.')
+    lib = ctypes.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def check(rc: int):
+    if rc != 0:
+        msg = load().itmo_last_error()
+        raise ItmoError(f'libitmo_b200 error {rc}: {msg.decode() if msg else "?"}')

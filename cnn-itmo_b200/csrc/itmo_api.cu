@@ -1,0 +1,869 @@
+// itmo_api.cu — C ABI (include/itmo_b200.h) over the sm_100a kernels: context, weight repacking,
+// tensor-map construction, the U-Net forward schedule (model.py:204-278) and the stateless
+// per-layer operators. PyTorch is not involved below this line; the Python shim passes raw
+// device pointers.
+#include <cuda_runtime.h>
+#include <cuda.h>
+#include <cudaTypedefs.h>
+#include <cuda_bf16.h>
+
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/itmo_b200.h"
+#include "conv_igemm.cuh"
+
+namespace {
+
+// ------------------------------------------------------------------------------------------------
+// errors
+// ------------------------------------------------------------------------------------------------
+thread_local std::string g_last_error;
+
+int fail(int code, const char* fmt, ...) {
+  char buf[1024];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  g_last_error = buf;
+  return code;
+}
+
+#define ITMO_CUDA(expr)                                                                              \
+  do {                                                                                               \
+    cudaError_t _e = (expr);                                                                         \
+    if (_e != cudaSuccess)                                                                           \
+      return fail(ITMO_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+  } while (0)
+
+// ------------------------------------------------------------------------------------------------
+// the graph: 19 weight layers in execution order (model.py:208-276, layers.txt)
+// ------------------------------------------------------------------------------------------------
+enum LayerKind { kRgbConv = 0, kConv = 1, kConvT = 2, kHead = 3 };
+struct LayerDef {
+  int kind;
+  int cin0, cin1, cout;
+  int hin;      // input (= output for convs) spatial size at 512x512 network input
+  bool pool;    // followed by MaxPooling2D (model.py:210,215,220,227)
+  int src0, src1;  // producing layer index (-1 = network input), src1 = -1 if single source
+  bool src0_pooled;
+};
+// concatenate([skip, up]) order = (encoder skip, decoder up) (model.py:246,251,256,261)
+const LayerDef kLayers[ITMO_NUM_LAYERS] = {
+    {kRgbConv, 3, 0, 32, 512, false, -1, -1, false},   // 0  conv2d_1
+    {kConv, 32, 0, 32, 512, true, 0, -1, false},       // 1  conv2d_2  (+pool1)
+    {kConv, 32, 0, 64, 256, false, 1, -1, true},       // 2  conv2d_3
+    {kConv, 64, 0, 64, 256, true, 2, -1, false},       // 3  conv2d_4  (+pool2)
+    {kConv, 64, 0, 128, 128, false, 3, -1, true},      // 4  conv2d_5
+    {kConv, 128, 0, 128, 128, true, 4, -1, false},     // 5  conv2d_6  (+pool3)
+    {kConv, 128, 0, 256, 64, false, 5, -1, true},      // 6  conv2d_7
+    {kConv, 256, 0, 256, 64, true, 6, -1, false},      // 7  conv2d_8  (+dropout(identity)+pool4)
+    {kConv, 256, 0, 512, 32, false, 7, -1, true},      // 8  conv2d_9
+    {kConv, 512, 0, 512, 32, false, 8, -1, false},     // 9  conv2d_10 (+dropout(identity))
+    {kConvT, 512, 0, 512, 32, false, 9, -1, false},    // 10 conv2d_transpose_1 -> 64x64
+    {kConv, 256, 512, 512, 64, false, 7, 10, false},   // 11 conv2d_11  concat(drop4, up6)
+    {kConvT, 512, 0, 256, 64, false, 11, -1, false},   // 12 conv2d_transpose_2 -> 128x128
+    {kConv, 128, 256, 256, 128, false, 5, 12, false},  // 13 conv2d_12  concat(conv3, up7)
+    {kConvT, 256, 0, 128, 128, false, 13, -1, false},  // 14 conv2d_transpose_3 -> 256x256
+    {kConv, 64, 128, 128, 256, false, 3, 14, false},   // 15 conv2d_13  concat(conv2, up8)
+    {kConvT, 128, 0, 64, 256, false, 15, -1, false},   // 16 conv2d_transpose_4 -> 512x512
+    {kConv, 32, 64, 64, 512, false, 1, 16, false},     // 17 conv2d_14  concat(conv1, up9) + fused head
+    {kHead, 64, 0, 3, 512, false, 17, -1, false},      // 18 conv2d_15  1x1 sigmoid
+};
+
+inline size_t elem_size(int precision) { return precision == ITMO_PREC_BF16 ? 2 : 4; }
+
+// ------------------------------------------------------------------------------------------------
+// TMA tensor maps
+// ------------------------------------------------------------------------------------------------
+PFN_cuTensorMapEncodeTiled_v12000 get_encode_fn() {
+  static PFN_cuTensorMapEncodeTiled_v12000 fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(p);
+  });
+  return fn;
+}
+
+CUtensorMapSwizzle swizzle_enum(int swz) {
+  return swz == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : swz == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B;
+}
+
+// NHWC activation tensor [N,H,W,C] viewed as (C, W, H, N); box = (bk channels, 16, 8, 1).
+int make_act_map(CUtensorMap* m, const void* ptr, int precision, int C, int W, int H, int N, int swz) {
+  auto enc = get_encode_fn();
+  if (!enc) return fail(ITMO_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
+  const size_t es = elem_size(precision);
+  cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
+  cuuint64_t strides[3] = {(cuuint64_t)C * es, (cuuint64_t)W * C * es, (cuuint64_t)H * W * C * es};
+  cuuint32_t box[4] = {(cuuint32_t)(swz / es), (cuuint32_t)itmo::kTileW, (cuuint32_t)itmo::kTileH, 1};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = enc(m, precision == ITMO_PREC_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32,
+                   4, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   swizzle_enum(swz), CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS)
+    return fail(ITMO_ERR_CUDA, "cuTensorMapEncodeTiled(activation C=%d W=%d H=%d N=%d swz=%d) -> %d", C, W, H, N, swz,
+                (int)r);
+  return ITMO_OK;
+}
+
+// Packed weights [taps][rows][cin_total] viewed as (cin_total, rows, taps); box = (bk, block_n, 1).
+int make_weight_map(CUtensorMap* m, const void* ptr, int precision, int cin_total, int rows, int taps, int block_n,
+                    int swz) {
+  auto enc = get_encode_fn();
+  if (!enc) return fail(ITMO_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
+  const size_t es = elem_size(precision);
+  cuuint64_t dims[3] = {(cuuint64_t)cin_total, (cuuint64_t)rows, (cuuint64_t)taps};
+  cuuint64_t strides[2] = {(cuuint64_t)cin_total * es, (cuuint64_t)rows * cin_total * es};
+  cuuint32_t box[3] = {(cuuint32_t)(swz / es), (cuuint32_t)block_n, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = enc(m, precision == ITMO_PREC_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32,
+                   3, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   swizzle_enum(swz), CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS)
+    return fail(ITMO_ERR_CUDA, "cuTensorMapEncodeTiled(weights cin=%d rows=%d taps=%d bn=%d swz=%d) -> %d", cin_total,
+                rows, taps, block_n, swz, (int)r);
+  return ITMO_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// small kernels: weight repacking, BN folding, first layer (Cin = 3)
+// ------------------------------------------------------------------------------------------------
+template <typename Elem>
+__device__ __forceinline__ Elem to_elem(float v);
+template <>
+__device__ __forceinline__ float to_elem<float>(float v) { return v; }
+template <>
+__device__ __forceinline__ __nv_bfloat16 to_elem<__nv_bfloat16>(float v) { return __float2bfloat16_rn(v); }
+
+// Keras Conv2D kernel [tap][cin][cout] (HWIO) -> K-major [tap][cout][cin]
+template <typename Elem>
+__global__ void pack_conv_weights_kernel(const float* __restrict__ src, Elem* __restrict__ dst, int taps, int cin,
+                                         int cout) {
+  const size_t total = size_t(taps) * cin * cout;
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < total; i += size_t(gridDim.x) * blockDim.x) {
+    const int ci = int(i % cin);
+    const int co = int((i / cin) % cout);
+    const int tap = int(i / (size_t(cin) * cout));
+    dst[i] = to_elem<Elem>(src[(size_t(tap) * cin + ci) * cout + co]);
+  }
+}
+// Keras Conv2DTranspose kernel [a][b][cout][cin] is already [(a*2+b)*cout + co][cin]: convert only
+template <typename Elem>
+__global__ void convert_weights_kernel(const float* __restrict__ src, Elem* __restrict__ dst, size_t total) {
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < total; i += size_t(gridDim.x) * blockDim.x)
+    dst[i] = to_elem<Elem>(src[i]);
+}
+// BatchNormalization inference affine (Keras defaults, eps = 1e-3): s = g/sqrt(v+eps), t = b - m*s
+__global__ void bn_fold_kernel(const float* g, const float* b, const float* m, const float* v, float eps, int n,
+                               float* scale, float* shift) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) {
+    const float s = g[i] / sqrtf(v[i] + eps);
+    scale[i] = s;
+    shift[i] = b[i] - m[i] * s;
+  }
+}
+
+// First ConvBN (3 -> 32 channels, model.py:208): K = 27 is too thin for the tensor-core path and the
+// layer is HBM-bound (0.45 GFLOP vs 17.6 MB / image), so it runs on CUDA cores in fp32. The /255 of
+// predict.py:59 is fused into the load. One thread = one pixel x 8 output channels; the 4 threads
+// of a pixel write 4 x 16 B (bf16) contiguous bytes, so a warp stores 512 contiguous bytes.
+template <typename Elem, typename InT>
+__global__ void __launch_bounds__(256) conv3x3_rgb_kernel(const InT* __restrict__ in, Elem* __restrict__ out,
+                                                          const float* __restrict__ w_hwio,  // [27][32]
+                                                          const float* __restrict__ bias,
+                                                          const float* __restrict__ scale,
+                                                          const float* __restrict__ shift, int NB, int H, int W) {
+  __shared__ float s_w[27 * 32];
+  __shared__ float s_b[32], s_s[32], s_t[32];
+  for (int i = threadIdx.x; i < 27 * 32; i += blockDim.x) s_w[i] = w_hwio[i];
+  if (threadIdx.x < 32) {
+    s_b[threadIdx.x] = bias[threadIdx.x];
+    s_s[threadIdx.x] = scale[threadIdx.x];
+    s_t[threadIdx.x] = shift[threadIdx.x];
+  }
+  __syncthreads();
+  const size_t total = size_t(NB) * H * W * 4;
+  for (size_t gid = blockIdx.x * size_t(blockDim.x) + threadIdx.x; gid < total; gid += size_t(gridDim.x) * blockDim.x) {
+    const int cg = int(gid & 3);
+    const size_t pix = gid >> 2;
+    const int x = int(pix % W);
+    const int y = int((pix / W) % H);
+    const size_t img = pix / (size_t(W) * H);
+    float acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = s_b[cg * 8 + j];
+#pragma unroll
+    for (int dy = -1; dy <= 1; ++dy) {
+      const int yy = y + dy;
+      if (yy < 0 || yy >= H) continue;
+#pragma unroll
+      for (int dx = -1; dx <= 1; ++dx) {
+        const int xx = x + dx;
+        if (xx < 0 || xx >= W) continue;
+        const InT* src = in + ((img * H + yy) * W + xx) * 3;
+        float v[3];
+        if constexpr (sizeof(InT) == 1) {
+          v[0] = __fdiv_rn(float(src[0]), 255.f);
+          v[1] = __fdiv_rn(float(src[1]), 255.f);
+          v[2] = __fdiv_rn(float(src[2]), 255.f);
+        } else {
+          v[0] = src[0];
+          v[1] = src[1];
+          v[2] = src[2];
+        }
+        const float* wp = s_w + ((dy + 1) * 3 + (dx + 1)) * 3 * 32 + cg * 8;
+#pragma unroll
+        for (int ci = 0; ci < 3; ++ci) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc[j] = fmaf(v[ci], wp[ci * 32 + j], acc[j]);
+        }
+      }
+    }
+    float f[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) f[j] = fmaf(fmaxf(acc[j], 0.f), s_s[cg * 8 + j], s_t[cg * 8 + j]);
+    if constexpr (sizeof(Elem) == 2) {
+      uint4 o = make_uint4(itmo::pack_bf16x2(f[0], f[1]), itmo::pack_bf16x2(f[2], f[3]), itmo::pack_bf16x2(f[4], f[5]),
+                           itmo::pack_bf16x2(f[6], f[7]));
+      *reinterpret_cast<uint4*>(out + pix * 32 + cg * 8) = o;
+    } else {
+      float4* dst = reinterpret_cast<float4*>(out + pix * 32 + cg * 8);
+      dst[0] = make_float4(f[0], f[1], f[2], f[3]);
+      dst[1] = make_float4(f[4], f[5], f[6], f[7]);
+    }
+  }
+}
+
+__global__ void bf16_to_f32_kernel(const __nv_bfloat16* __restrict__ src, float* __restrict__ dst, size_t n) {
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n; i += size_t(gridDim.x) * blockDim.x)
+    dst[i] = __bfloat162float(src[i]);
+}
+
+// ------------------------------------------------------------------------------------------------
+// conv launch
+// ------------------------------------------------------------------------------------------------
+int g_num_sms = 0;
+int num_sms() {
+  if (g_num_sms == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
+    if (g_num_sms <= 0) g_num_sms = 148;
+  }
+  return g_num_sms;
+}
+
+template <typename Elem, int BLOCK_N, int SWZ>
+int launch_conv_t(const itmo::ConvParams& p, int total_tiles, cudaStream_t stream) {
+  using Cfg = itmo::ConvCfg<Elem, BLOCK_N, SWZ>;
+  auto kern = itmo::conv_igemm_kernel<Elem, BLOCK_N, SWZ>;
+  static bool configured = false;  // per template instantiation
+  if (!configured) {
+    ITMO_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+    configured = true;
+  }
+  const int grid = std::min(total_tiles, num_sms());
+  kern<<<grid, 256, Cfg::kSmemBytes, stream>>>(p);
+  ITMO_CUDA(cudaGetLastError());
+  return ITMO_OK;
+}
+
+template <typename Elem, int SWZ>
+int launch_conv_n(int block_n, const itmo::ConvParams& p, int total_tiles, cudaStream_t stream) {
+  switch (block_n) {
+    case 32: return launch_conv_t<Elem, 32, SWZ>(p, total_tiles, stream);
+    case 64: return launch_conv_t<Elem, 64, SWZ>(p, total_tiles, stream);
+    case 128: return launch_conv_t<Elem, 128, SWZ>(p, total_tiles, stream);
+    case 256: return launch_conv_t<Elem, 256, SWZ>(p, total_tiles, stream);
+  }
+  return fail(ITMO_ERR_INVALID, "unsupported BLOCK_N %d", block_n);
+}
+
+struct ConvArgs {
+  int precision;
+  int mode;  // itmo::ConvMode
+  const void* src0;
+  int c0;
+  const void* src1;
+  int c1;
+  int n, h, w;           // input batch / spatial
+  const void* wpacked;   // [taps][rows][c0+c1] in the element type
+  const float *bias, *scale, *shift;
+  int cout;
+  void* out;
+  void* pooled;
+  const float* head_w;  // device [3][64] + bias [3] or null
+  const float* head_b;
+  void* head_out;
+  int head_dtype;  // itmo::HeadDtype
+};
+
+// Validates shapes, builds tensor maps and launches the implicit-GEMM kernel.
+int run_conv(const ConvArgs& a, cudaStream_t stream) {
+  const size_t es = elem_size(a.precision);
+  if (a.h % itmo::kTileH || a.w % itmo::kTileW)
+    return fail(ITMO_ERR_INVALID, "spatial size %dx%d must be a multiple of %dx%d", a.h, a.w, itmo::kTileH,
+                itmo::kTileW);
+  if (a.n <= 0) return fail(ITMO_ERR_INVALID, "batch must be positive");
+  const int cin = a.c0 + a.c1;
+  const int full_bk = int(128 / es), half_bk = int(64 / es);
+  int swz;
+  if (a.c0 % full_bk == 0 && a.c1 % full_bk == 0) {
+    swz = 128;
+  } else if (a.precision == ITMO_PREC_BF16 && a.c0 % half_bk == 0 && a.c1 % half_bk == 0) {
+    swz = 64;
+  } else {
+    return fail(ITMO_ERR_INVALID, "input channels (%d,%d) must be multiples of %d", a.c0, a.c1,
+                a.precision == ITMO_PREC_BF16 ? half_bk : full_bk);
+  }
+  if (a.cout > itmo::kMaxCout || a.cout % 16) return fail(ITMO_ERR_INVALID, "cout %d unsupported", a.cout);
+  const int taps = a.mode == itmo::kModeConv3x3 ? 9 : 1;
+  const int rows = a.mode == itmo::kModeConv3x3 ? a.cout : 4 * a.cout;
+  int block_n = std::min(rows, 256);
+  if (block_n != 32 && block_n != 64 && block_n != 128 && block_n != 256)
+    return fail(ITMO_ERR_INVALID, "weight rows %d not tileable", rows);
+  if (rows % block_n) return fail(ITMO_ERR_INVALID, "weight rows %d not a multiple of %d", rows, block_n);
+  if (a.pooled && a.mode != itmo::kModeConv3x3) return fail(ITMO_ERR_INVALID, "pool fusion only on conv3x3");
+  if (a.head_dtype != itmo::kHeadNone && (a.cout != 64 || block_n != 64 || a.mode != itmo::kModeConv3x3))
+    return fail(ITMO_ERR_INVALID, "head fusion needs cout == 64");
+
+  itmo::ConvParams p;
+  memset(&p, 0, sizeof(p));
+  int rc = make_act_map(&p.tmA0, a.src0, a.precision, a.c0, a.w, a.h, a.n, swz);
+  if (rc) return rc;
+  if (a.c1 > 0) {
+    rc = make_act_map(&p.tmA1, a.src1, a.precision, a.c1, a.w, a.h, a.n, swz);
+    if (rc) return rc;
+  } else {
+    p.tmA1 = p.tmA0;
+  }
+  rc = make_weight_map(&p.tmB, a.wpacked, a.precision, cin, rows, taps, block_n, swz);
+  if (rc) return rc;
+  const int bk = int(swz / es);
+  p.H = a.h;
+  p.W = a.w;
+  p.NB = a.n;
+  p.kb0 = a.c0 / bk;
+  p.kb1 = a.c1 / bk;
+  p.taps = taps;
+  p.n_tiles = rows / block_n;
+  p.cout = a.cout;
+  p.mode = a.mode;
+  p.bias = a.bias;
+  p.bn_scale = a.scale;
+  p.bn_shift = a.shift;
+  p.out = a.out;
+  p.pooled = a.pooled;
+  p.head_w = a.head_w;
+  p.head_b = a.head_b;
+  p.head_out = a.head_out;
+  p.head_dtype = a.head_dtype;
+  const int total_tiles = a.n * (a.h / itmo::kTileH) * (a.w / itmo::kTileW) * p.n_tiles;
+  if (a.precision == ITMO_PREC_BF16) {
+    if (swz == 128) return launch_conv_n<__nv_bfloat16, 128>(block_n, p, total_tiles, stream);
+    return launch_conv_n<__nv_bfloat16, 64>(block_n, p, total_tiles, stream);
+  }
+  return launch_conv_n<float, 128>(block_n, p, total_tiles, stream);
+}
+
+int pack_weights(int precision, int mode, const float* src_dev, void* dst_dev, int cin, int cout,
+                 cudaStream_t stream) {
+  if (mode == itmo::kModeConv3x3) {
+    const size_t total = size_t(9) * cin * cout;
+    const int grid = int(std::min<size_t>((total + 255) / 256, 4096));
+    if (precision == ITMO_PREC_BF16)
+      pack_conv_weights_kernel<__nv_bfloat16><<<grid, 256, 0, stream>>>(src_dev, (__nv_bfloat16*)dst_dev, 9, cin, cout);
+    else
+      pack_conv_weights_kernel<float><<<grid, 256, 0, stream>>>(src_dev, (float*)dst_dev, 9, cin, cout);
+  } else {
+    const size_t total = size_t(4) * cin * cout;
+    const int grid = int(std::min<size_t>((total + 255) / 256, 4096));
+    if (precision == ITMO_PREC_BF16)
+      convert_weights_kernel<__nv_bfloat16><<<grid, 256, 0, stream>>>(src_dev, (__nv_bfloat16*)dst_dev, total);
+    else
+      convert_weights_kernel<float><<<grid, 256, 0, stream>>>(src_dev, (float*)dst_dev, total);
+  }
+  ITMO_CUDA(cudaGetLastError());
+  return ITMO_OK;
+}
+
+int run_rgb_conv(int precision, const void* in, int in_dtype, int n, int h, int w, const float* w_hwio,
+                 const float* bias, const float* scale, const float* shift, void* out, cudaStream_t stream) {
+  const size_t total = size_t(n) * h * w * 4;
+  const int grid = int(std::min<size_t>((total + 255) / 256, size_t(num_sms()) * 16));
+  if (precision == ITMO_PREC_BF16) {
+    if (in_dtype == ITMO_DT_U8)
+      conv3x3_rgb_kernel<__nv_bfloat16, uint8_t><<<grid, 256, 0, stream>>>((const uint8_t*)in, (__nv_bfloat16*)out,
+                                                                             w_hwio, bias, scale, shift, n, h, w);
+    else
+      conv3x3_rgb_kernel<__nv_bfloat16, float><<<grid, 256, 0, stream>>>((const float*)in, (__nv_bfloat16*)out, w_hwio,
+                                                                           bias, scale, shift, n, h, w);
+  } else {
+    if (in_dtype == ITMO_DT_U8)
+      conv3x3_rgb_kernel<float, uint8_t><<<grid, 256, 0, stream>>>((const uint8_t*)in, (float*)out, w_hwio, bias, scale,
+                                                                     shift, n, h, w);
+    else
+      conv3x3_rgb_kernel<float, float><<<grid, 256, 0, stream>>>((const float*)in, (float*)out, w_hwio, bias, scale,
+                                                                   shift, n, h, w);
+  }
+  ITMO_CUDA(cudaGetLastError());
+  return ITMO_OK;
+}
+
+// Keras head kernel [64][3] -> [3][64] (tiny, host side)
+void transpose_head(const float* k64x3, float* out3x64) {
+  for (int c = 0; c < 64; ++c)
+    for (int k = 0; k < 3; ++k) out3x64[k * 64 + c] = k64x3[c * 3 + k];
+}
+
+__global__ void transpose_head_kernel(const float* __restrict__ k64x3, float* __restrict__ out3x64) {
+  const int i = threadIdx.x;
+  if (i < 192) out3x64[(i % 3) * 64 + i / 3] = k64x3[i];
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------------
+// context
+// ------------------------------------------------------------------------------------------------
+struct itmo_ctx {
+  int device = 0;
+  int precision = ITMO_PREC_BF16;
+  int cap = 0;  // images the arena holds
+  bool weights_loaded = false;
+  long long launches = 0;
+  int last_chunk = 0;  // images in the most recent forward chunk (for itmo_read_activation)
+
+  // per layer device parameters
+  void* wpacked[ITMO_NUM_LAYERS] = {};   // tensor-core layers: packed; layer 0: fp32 HWIO; head: fp32 [3][64]
+  float* bias[ITMO_NUM_LAYERS] = {};
+  float* scale[ITMO_NUM_LAYERS] = {};
+  float* shift[ITMO_NUM_LAYERS] = {};
+
+  // activation arena
+  void* arena = nullptr;
+  size_t arena_bytes = 0;
+  void* act[ITMO_NUM_LAYERS] = {};     // layer outputs (layer 17/18 not materialised)
+  void* pooled[ITMO_NUM_LAYERS] = {};  // pooled copies of layers 1,3,5,7
+  size_t act_elems_per_img[ITMO_NUM_LAYERS] = {};
+  size_t pooled_elems_per_img[ITMO_NUM_LAYERS] = {};
+
+  // host staging for itmo_predict_host
+  void* pin_in = nullptr;
+  void* pin_out = nullptr;
+  void* dev_in = nullptr;
+  void* dev_out = nullptr;
+  size_t stage_in_bytes = 0, stage_out_bytes = 0;
+  cudaStream_t own_stream = nullptr;
+};
+
+namespace {
+
+int out_hw(const LayerDef& L) { return L.kind == kConvT ? 2 * L.hin : L.hin; }
+
+int forward_chunk(itmo_ctx* ctx, const void* in_dev, int in_dtype, void* out_dev, int out_dtype, int nb,
+                  cudaStream_t stream) {
+  const int prec = ctx->precision;
+  for (int li = 0; li < ITMO_NUM_LAYERS; ++li) {
+    const LayerDef& L = kLayers[li];
+    if (L.kind == kHead) continue;  // fused into layer 17's epilogue
+    if (L.kind == kRgbConv) {
+      int rc = run_rgb_conv(prec, in_dev, in_dtype, nb, L.hin, L.hin, (const float*)ctx->wpacked[li], ctx->bias[li],
+                            ctx->scale[li], ctx->shift[li], ctx->act[li], stream);
+      if (rc) return rc;
+      ctx->launches++;
+      continue;
+    }
+    ConvArgs a;
+    memset(&a, 0, sizeof(a));
+    a.precision = prec;
+    a.mode = L.kind == kConvT ? itmo::kModeConvT2x2 : itmo::kModeConv3x3;
+    a.src0 = L.src0_pooled ? ctx->pooled[L.src0] : ctx->act[L.src0];
+    a.c0 = L.cin0;
+    a.src1 = L.src1 >= 0 ? ctx->act[L.src1] : nullptr;
+    a.c1 = L.cin1;
+    a.n = nb;
+    a.h = L.hin;
+    a.w = L.hin;
+    a.wpacked = ctx->wpacked[li];
+    a.bias = ctx->bias[li];
+    a.scale = ctx->scale[li];
+    a.shift = ctx->shift[li];
+    a.cout = L.cout;
+    a.out = ctx->act[li];
+    a.pooled = L.pool ? ctx->pooled[li] : nullptr;
+    a.head_dtype = itmo::kHeadNone;
+    if (li == 17) {
+      a.out = nullptr;  // conv2d_14's activation only feeds the head: never written to HBM
+      a.head_w = (const float*)ctx->wpacked[18];
+      a.head_b = ctx->bias[18];
+      a.head_out = out_dev;
+      a.head_dtype = out_dtype == ITMO_DT_U8 ? itmo::kHeadU8 : itmo::kHeadF32;
+    }
+    int rc = run_conv(a, stream);
+    if (rc) return rc;
+    ctx->launches++;
+  }
+  ctx->last_chunk = nb;
+  return ITMO_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* itmo_last_error(void) { return g_last_error.c_str(); }
+int itmo_abi_version(void) { return 1; }
+
+int itmo_create(itmo_ctx** out, int device, int precision, int max_batch) {
+  if (!out) return fail(ITMO_ERR_INVALID, "out is null");
+  *out = nullptr;
+  if (precision != ITMO_PREC_TF32 && precision != ITMO_PREC_BF16) return fail(ITMO_ERR_INVALID, "bad precision");
+  if (max_batch <= 0) return fail(ITMO_ERR_INVALID, "max_batch must be positive");
+  ITMO_CUDA(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  ITMO_CUDA(cudaGetDeviceProperties(&prop, device));
+  if (prop.major != 10)
+    return fail(ITMO_ERR_CUDA, "device %d is sm_%d%d; libitmo_b200 only contains sm_100a code", device, prop.major,
+                prop.minor);
+  itmo_ctx* ctx = new itmo_ctx();
+  ctx->device = device;
+  ctx->precision = precision;
+  ctx->cap = max_batch;
+  const size_t es = elem_size(precision);
+
+  // parameters
+  for (int li = 0; li < ITMO_NUM_LAYERS; ++li) {
+    const LayerDef& L = kLayers[li];
+    const int cin = L.cin0 + L.cin1;
+    size_t wbytes;
+    if (L.kind == kRgbConv) wbytes = size_t(27) * L.cout * 4;
+    else if (L.kind == kConv) wbytes = size_t(9) * cin * L.cout * es;
+    else if (L.kind == kConvT) wbytes = size_t(4) * cin * L.cout * es;
+    else wbytes = size_t(3) * 64 * 4;
+    cudaError_t e = cudaMalloc(&ctx->wpacked[li], wbytes);
+    if (e == cudaSuccess) e = cudaMalloc((void**)&ctx->bias[li], L.cout * 4);
+    if (e == cudaSuccess) e = cudaMalloc((void**)&ctx->scale[li], L.cout * 4);
+    if (e == cudaSuccess) e = cudaMalloc((void**)&ctx->shift[li], L.cout * 4);
+    if (e != cudaSuccess) {
+      itmo_destroy(ctx);
+      return fail(ITMO_ERR_NOMEM, "cudaMalloc(parameters) failed: %s", cudaGetErrorString(e));
+    }
+  }
+  // arena: every activation gets its own slot (256-byte aligned) — the skip tensors stay live until
+  // the decoder consumes them, so there is little to alias.
+  size_t off = 0;
+  size_t offs_act[ITMO_NUM_LAYERS], offs_pool[ITMO_NUM_LAYERS];
+  for (int li = 0; li < ITMO_NUM_LAYERS; ++li) {
+    const LayerDef& L = kLayers[li];
+    offs_act[li] = offs_pool[li] = size_t(-1);
+    if (L.kind == kHead || li == 17) continue;
+    const int ho = out_hw(L);
+    ctx->act_elems_per_img[li] = size_t(ho) * ho * L.cout;
+    offs_act[li] = off;
+    off += (ctx->act_elems_per_img[li] * es * max_batch + 255) / 256 * 256;
+    if (L.pool) {
+      ctx->pooled_elems_per_img[li] = size_t(ho / 2) * (ho / 2) * L.cout;
+      offs_pool[li] = off;
+      off += (ctx->pooled_elems_per_img[li] * es * max_batch + 255) / 256 * 256;
+    }
+  }
+  ctx->arena_bytes = off;
+  cudaError_t e = cudaMalloc(&ctx->arena, off);
+  if (e != cudaSuccess) {
+    itmo_destroy(ctx);
+    return fail(ITMO_ERR_NOMEM, "cudaMalloc(arena, %zu bytes) failed: %s", off, cudaGetErrorString(e));
+  }
+  for (int li = 0; li < ITMO_NUM_LAYERS; ++li) {
+    if (offs_act[li] != size_t(-1)) ctx->act[li] = (char*)ctx->arena + offs_act[li];
+    if (offs_pool[li] != size_t(-1)) ctx->pooled[li] = (char*)ctx->arena + offs_pool[li];
+  }
+  e = cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking);
+  if (e != cudaSuccess) {
+    itmo_destroy(ctx);
+    return fail(ITMO_ERR_CUDA, "cudaStreamCreate failed: %s", cudaGetErrorString(e));
+  }
+  *out = ctx;
+  return ITMO_OK;
+}
+
+void itmo_destroy(itmo_ctx* ctx) {
+  if (!ctx) return;
+  cudaSetDevice(ctx->device);
+  cudaDeviceSynchronize();
+  for (int li = 0; li < ITMO_NUM_LAYERS; ++li) {
+    cudaFree(ctx->wpacked[li]);
+    cudaFree(ctx->bias[li]);
+    cudaFree(ctx->scale[li]);
+    cudaFree(ctx->shift[li]);
+  }
+  cudaFree(ctx->arena);
+  cudaFree(ctx->dev_in);
+  cudaFree(ctx->dev_out);
+  if (ctx->pin_in) cudaFreeHost(ctx->pin_in);
+  if (ctx->pin_out) cudaFreeHost(ctx->pin_out);
+  if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
+  delete ctx;
+}
+
+int itmo_load_weights(itmo_ctx* ctx, const itmo_layer_weights* layers, int n_layers, float bn_eps) {
+  if (!ctx || !layers) return fail(ITMO_ERR_INVALID, "null argument");
+  if (n_layers != ITMO_NUM_LAYERS) return fail(ITMO_ERR_INVALID, "expected %d layers, got %d", ITMO_NUM_LAYERS, n_layers);
+  ITMO_CUDA(cudaSetDevice(ctx->device));
+  cudaStream_t s = ctx->own_stream;
+  float* tmp = nullptr;  // fp32 staging for the largest kernel (conv2d_11: 9*768*512)
+  const size_t tmp_elems = size_t(9) * 768 * 512;
+  float* bn = nullptr;   // gamma, beta, mean, var staging
+  ITMO_CUDA(cudaMalloc((void**)&tmp, tmp_elems * 4));
+  cudaError_t e0 = cudaMalloc((void**)&bn, 4 * itmo::kMaxCout * 4);
+  if (e0 != cudaSuccess) {
+    cudaFree(tmp);
+    return fail(ITMO_ERR_NOMEM, "cudaMalloc failed: %s", cudaGetErrorString(e0));
+  }
+  int rc = ITMO_OK;
+  for (int li = 0; li < ITMO_NUM_LAYERS && rc == ITMO_OK; ++li) {
+    const LayerDef& L = kLayers[li];
+    const itmo_layer_weights& w = layers[li];
+    const int cin = L.cin0 + L.cin1;
+    if (!w.kernel || !w.bias) {
+      rc = fail(ITMO_ERR_INVALID, "layer %d: kernel/bias missing", li);
+      break;
+    }
+    if (L.kind != kHead && (!w.gamma || !w.beta || !w.moving_mean || !w.moving_variance)) {
+      rc = fail(ITMO_ERR_INVALID, "layer %d: BatchNormalization parameters missing", li);
+      break;
+    }
+    cudaError_t e = cudaMemcpyAsync(ctx->bias[li], w.bias, L.cout * 4, cudaMemcpyHostToDevice, s);
+    if (e == cudaSuccess && L.kind != kHead) {
+      e = cudaMemcpyAsync(bn + 0 * itmo::kMaxCout, w.gamma, L.cout * 4, cudaMemcpyHostToDevice, s);
+      if (e == cudaSuccess) e = cudaMemcpyAsync(bn + 1 * itmo::kMaxCout, w.beta, L.cout * 4, cudaMemcpyHostToDevice, s);
+      if (e == cudaSuccess)
+        e = cudaMemcpyAsync(bn + 2 * itmo::kMaxCout, w.moving_mean, L.cout * 4, cudaMemcpyHostToDevice, s);
+      if (e == cudaSuccess)
+        e = cudaMemcpyAsync(bn + 3 * itmo::kMaxCout, w.moving_variance, L.cout * 4, cudaMemcpyHostToDevice, s);
+      if (e == cudaSuccess) {
+        bn_fold_kernel<<<(L.cout + 127) / 128, 128, 0, s>>>(bn, bn + itmo::kMaxCout, bn + 2 * itmo::kMaxCout,
+                                                            bn + 3 * itmo::kMaxCout, bn_eps, L.cout, ctx->scale[li],
+                                                            ctx->shift[li]);
+        e = cudaGetLastError();
+      }
+    }
+    if (e != cudaSuccess) {
+      rc = fail(ITMO_ERR_CUDA, "layer %d parameter upload failed: %s", li, cudaGetErrorString(e));
+      break;
+    }
+    if (L.kind == kRgbConv) {
+      e = cudaMemcpyAsync(ctx->wpacked[li], w.kernel, size_t(27) * L.cout * 4, cudaMemcpyHostToDevice, s);
+    } else if (L.kind == kHead) {
+      float t[192];
+      transpose_head(w.kernel, t);
+      e = cudaMemcpyAsync(ctx->wpacked[li], t, sizeof(t), cudaMemcpyHostToDevice, s);
+      if (e == cudaSuccess) e = cudaStreamSynchronize(s);  // t is a stack buffer
+    } else {
+      const size_t n = size_t(L.kind == kConv ? 9 : 4) * cin * L.cout;
+      e = cudaMemcpyAsync(tmp, w.kernel, n * 4, cudaMemcpyHostToDevice, s);
+      if (e == cudaSuccess)
+        rc = pack_weights(ctx->precision, L.kind == kConv ? itmo::kModeConv3x3 : itmo::kModeConvT2x2, tmp,
+                          ctx->wpacked[li], cin, L.cout, s);
+    }
+    if (e != cudaSuccess) rc = fail(ITMO_ERR_CUDA, "layer %d weight upload failed: %s", li, cudaGetErrorString(e));
+    // staging buffers are reused by the next layer: keep it simple and serialise
+    if (rc == ITMO_OK) {
+      e = cudaStreamSynchronize(s);
+      if (e != cudaSuccess) rc = fail(ITMO_ERR_CUDA, "layer %d: %s", li, cudaGetErrorString(e));
+    }
+  }
+  cudaStreamSynchronize(s);
+  cudaFree(tmp);
+  cudaFree(bn);
+  if (rc == ITMO_OK) ctx->weights_loaded = true;
+  return rc;
+}
+
+int itmo_forward(itmo_ctx* ctx, const void* in_dev, int in_dtype, void* out_dev, int out_dtype, int n, unsigned flags,
+                 void* stream) {
+  (void)flags;
+  if (!ctx || !in_dev || !out_dev) return fail(ITMO_ERR_INVALID, "null argument");
+  if (!ctx->weights_loaded) return fail(ITMO_ERR_STATE, "itmo_forward before itmo_load_weights");
+  if (n < 0) return fail(ITMO_ERR_INVALID, "negative batch");
+  if (in_dtype != ITMO_DT_U8 && in_dtype != ITMO_DT_F32) return fail(ITMO_ERR_INVALID, "bad in_dtype");
+  if (out_dtype != ITMO_DT_U8 && out_dtype != ITMO_DT_F32) return fail(ITMO_ERR_INVALID, "bad out_dtype");
+  ITMO_CUDA(cudaSetDevice(ctx->device));
+  const size_t in_img = size_t(ITMO_IMG) * ITMO_IMG * 3 * (in_dtype == ITMO_DT_U8 ? 1 : 4);
+  const size_t out_img = size_t(ITMO_IMG) * ITMO_IMG * 3 * (out_dtype == ITMO_DT_U8 ? 1 : 4);
+  for (int i0 = 0; i0 < n; i0 += ctx->cap) {
+    const int nb = std::min(ctx->cap, n - i0);
+    int rc = forward_chunk(ctx, (const char*)in_dev + i0 * in_img, in_dtype, (char*)out_dev + i0 * out_img, out_dtype,
+                           nb, (cudaStream_t)stream);
+    if (rc) return rc;
+  }
+  return ITMO_OK;
+}
+
+int itmo_predict_host(itmo_ctx* ctx, const void* in_host, int in_dtype, void* out_host, int out_dtype, int n,
+                      unsigned flags) {
+  if (!ctx || !in_host || !out_host) return fail(ITMO_ERR_INVALID, "null argument");
+  if (!ctx->weights_loaded) return fail(ITMO_ERR_STATE, "itmo_predict_host before itmo_load_weights");
+  if (in_dtype != ITMO_DT_U8 && in_dtype != ITMO_DT_F32) return fail(ITMO_ERR_INVALID, "bad in_dtype");
+  if (out_dtype != ITMO_DT_U8 && out_dtype != ITMO_DT_F32) return fail(ITMO_ERR_INVALID, "bad out_dtype");
+  ITMO_CUDA(cudaSetDevice(ctx->device));
+  const size_t in_img = size_t(ITMO_IMG) * ITMO_IMG * 3 * (in_dtype == ITMO_DT_U8 ? 1 : 4);
+  const size_t out_img = size_t(ITMO_IMG) * ITMO_IMG * 3 * (out_dtype == ITMO_DT_U8 ? 1 : 4);
+  const size_t need_in = in_img * ctx->cap, need_out = out_img * ctx->cap;
+  if (ctx->stage_in_bytes < need_in) {
+    if (ctx->pin_in) cudaFreeHost(ctx->pin_in);
+    cudaFree(ctx->dev_in);
+    ctx->pin_in = ctx->dev_in = nullptr;
+    ctx->stage_in_bytes = 0;
+    ITMO_CUDA(cudaMallocHost(&ctx->pin_in, need_in));
+    ITMO_CUDA(cudaMalloc(&ctx->dev_in, need_in));
+    ctx->stage_in_bytes = need_in;
+  }
+  if (ctx->stage_out_bytes < need_out) {
+    if (ctx->pin_out) cudaFreeHost(ctx->pin_out);
+    cudaFree(ctx->dev_out);
+    ctx->pin_out = ctx->dev_out = nullptr;
+    ctx->stage_out_bytes = 0;
+    ITMO_CUDA(cudaMallocHost(&ctx->pin_out, need_out));
+    ITMO_CUDA(cudaMalloc(&ctx->dev_out, need_out));
+    ctx->stage_out_bytes = need_out;
+  }
+  cudaStream_t s = ctx->own_stream;
+  for (int i0 = 0; i0 < n; i0 += ctx->cap) {
+    const int nb = std::min(ctx->cap, n - i0);
+    memcpy(ctx->pin_in, (const char*)in_host + i0 * in_img, nb * in_img);
+    ITMO_CUDA(cudaMemcpyAsync(ctx->dev_in, ctx->pin_in, nb * in_img, cudaMemcpyHostToDevice, s));
+    int rc = forward_chunk(ctx, ctx->dev_in, in_dtype, ctx->dev_out, out_dtype, nb, s);
+    if (rc) return rc;
+    ITMO_CUDA(cudaMemcpyAsync(ctx->pin_out, ctx->dev_out, nb * out_img, cudaMemcpyDeviceToHost, s));
+    ITMO_CUDA(cudaStreamSynchronize(s));
+    memcpy((char*)out_host + i0 * out_img, ctx->pin_out, nb * out_img);
+  }
+  (void)flags;
+  return ITMO_OK;
+}
+
+long long itmo_launch_count(const itmo_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+int itmo_read_activation(itmo_ctx* ctx, int layer, int which, float* dst_host, size_t cap_elems, size_t* n_elems) {
+  if (!ctx || !dst_host || !n_elems) return fail(ITMO_ERR_INVALID, "null argument");
+  if (layer < 0 || layer >= ITMO_NUM_LAYERS) return fail(ITMO_ERR_INVALID, "bad layer index");
+  const void* src = which ? ctx->pooled[layer] : ctx->act[layer];
+  const size_t per_img = which ? ctx->pooled_elems_per_img[layer] : ctx->act_elems_per_img[layer];
+  if (!src || ctx->last_chunk == 0) return fail(ITMO_ERR_STATE, "activation %d/%d is not materialised", layer, which);
+  const size_t n = per_img * ctx->last_chunk;
+  *n_elems = n;
+  if (n > cap_elems) return fail(ITMO_ERR_INVALID, "destination too small: need %zu elements", n);
+  ITMO_CUDA(cudaSetDevice(ctx->device));
+  ITMO_CUDA(cudaDeviceSynchronize());
+  if (ctx->precision == ITMO_PREC_TF32) {
+    ITMO_CUDA(cudaMemcpy(dst_host, src, n * 4, cudaMemcpyDeviceToHost));
+  } else {
+    float* tmp = nullptr;
+    ITMO_CUDA(cudaMalloc((void**)&tmp, n * 4));
+    bf16_to_f32_kernel<<<1024, 256>>>((const __nv_bfloat16*)src, tmp, n);
+    cudaError_t e = cudaMemcpy(dst_host, tmp, n * 4, cudaMemcpyDeviceToHost);
+    cudaFree(tmp);
+    if (e != cudaSuccess) return fail(ITMO_ERR_CUDA, "readback failed: %s", cudaGetErrorString(e));
+  }
+  return ITMO_OK;
+}
+
+// ---- stateless per-layer operators ---------------------------------------------------------------
+
+static int stateless_conv(int precision, int mode, const void* src0, int c0, const void* src1, int c1, int n, int h,
+                          int w, const float* kernel, const float* bias, const float* scale, const float* shift,
+                          int cout, void* out, void* pooled, const float* head_kernel, const float* head_bias,
+                          void* head_out, int head_dtype, void* stream) {
+  if (precision != ITMO_PREC_TF32 && precision != ITMO_PREC_BF16) return fail(ITMO_ERR_INVALID, "bad precision");
+  if (!src0 || !kernel || !bias || !scale || !shift) return fail(ITMO_ERR_INVALID, "null argument");
+  if (c1 > 0 && !src1) return fail(ITMO_ERR_INVALID, "src1 is null but c1 > 0");
+  cudaStream_t s = (cudaStream_t)stream;
+  const int cin = c0 + c1;
+  const size_t wbytes = size_t(mode == itmo::kModeConv3x3 ? 9 : 4) * cin * cout * elem_size(precision);
+  void* wp = nullptr;
+  float* hw = nullptr;
+  ITMO_CUDA(cudaMallocAsync(&wp, wbytes, s));
+  int rc = pack_weights(precision, mode, kernel, wp, cin, cout, s);
+  if (rc == ITMO_OK && head_dtype != itmo::kHeadNone) {
+    cudaError_t e = cudaMallocAsync((void**)&hw, 192 * 4, s);
+    if (e != cudaSuccess) rc = fail(ITMO_ERR_NOMEM, "cudaMallocAsync failed: %s", cudaGetErrorString(e));
+    else transpose_head_kernel<<<1, 192, 0, s>>>(head_kernel, hw);
+  }
+  if (rc == ITMO_OK) {
+    ConvArgs a;
+    memset(&a, 0, sizeof(a));
+    a.precision = precision;
+    a.mode = mode;
+    a.src0 = src0;
+    a.c0 = c0;
+    a.src1 = src1;
+    a.c1 = c1;
+    a.n = n;
+    a.h = h;
+    a.w = w;
+    a.wpacked = wp;
+    a.bias = bias;
+    a.scale = scale;
+    a.shift = shift;
+    a.cout = cout;
+    a.out = out;
+    a.pooled = pooled;
+    a.head_w = hw;
+    a.head_b = head_bias;
+    a.head_out = head_out;
+    a.head_dtype = head_dtype;
+    rc = run_conv(a, s);
+  }
+  cudaFreeAsync(wp, s);
+  if (hw) cudaFreeAsync(hw, s);
+  return rc;
+}
+
+int itmo_conv3x3_bn(int precision, const void* src0, int c0, const void* src1, int c1, int n, int h, int w,
+                    const float* kernel_hwio, const float* bias, const float* scale, const float* shift, int cout,
+                    void* out, void* pooled_or_null, void* stream) {
+  if (!out) return fail(ITMO_ERR_INVALID, "out is null");
+  return stateless_conv(precision, itmo::kModeConv3x3, src0, c0, src1, c1, n, h, w, kernel_hwio, bias, scale, shift,
+                        cout, out, pooled_or_null, nullptr, nullptr, nullptr, itmo::kHeadNone, stream);
+}
+
+int itmo_convT2x2_bn(int precision, const void* src, int cin, int n, int h, int w, const float* kernel_hwoi,
+                     const float* bias, const float* scale, const float* shift, int cout, void* out, void* stream) {
+  if (!out) return fail(ITMO_ERR_INVALID, "out is null");
+  return stateless_conv(precision, itmo::kModeConvT2x2, src, cin, nullptr, 0, n, h, w, kernel_hwoi, bias, scale, shift,
+                        cout, out, nullptr, nullptr, nullptr, nullptr, itmo::kHeadNone, stream);
+}
+
+int itmo_conv3x3_bn_head(int precision, const void* src0, int c0, const void* src1, int c1, int n, int h, int w,
+                         const float* kernel_hwio, const float* bias, const float* scale, const float* shift,
+                         const float* head_kernel, const float* head_bias, void* out, int out_dtype, void* stream) {
+  if (!out || !head_kernel || !head_bias) return fail(ITMO_ERR_INVALID, "null argument");
+  if (out_dtype != ITMO_DT_U8 && out_dtype != ITMO_DT_F32) return fail(ITMO_ERR_INVALID, "bad out_dtype");
+  return stateless_conv(precision, itmo::kModeConv3x3, src0, c0, src1, c1, n, h, w, kernel_hwio, bias, scale, shift, 64,
+                        nullptr, nullptr, head_kernel, head_bias, out,
+                        out_dtype == ITMO_DT_U8 ? itmo::kHeadU8 : itmo::kHeadF32, stream);
+}
+
+int itmo_conv3x3_bn_rgb(int precision, const void* in, int in_dtype, int n, int h, int w, const float* kernel_hwio,
+                        const float* bias, const float* scale, const float* shift, int cout, void* out, void* stream) {
+  if (precision != ITMO_PREC_TF32 && precision != ITMO_PREC_BF16) return fail(ITMO_ERR_INVALID, "bad precision");
+  if (!in || !kernel_hwio || !bias || !scale || !shift || !out) return fail(ITMO_ERR_INVALID, "null argument");
+  if (cout != 32) return fail(ITMO_ERR_INVALID, "first layer has 32 output channels (model.py:208)");
+  if (in_dtype != ITMO_DT_U8 && in_dtype != ITMO_DT_F32) return fail(ITMO_ERR_INVALID, "bad in_dtype");
+  return run_rgb_conv(precision, in, in_dtype, n, h, w, kernel_hwio, bias, scale, shift, out, (cudaStream_t)stream);
+}
+
+}  // extern "C"
