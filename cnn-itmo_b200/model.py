@@ -1,0 +1,282 @@
+"""Drop-in equivalents of the reference's model API for its one hot path.
+
+    from cnn_itmo_b200.model import U_net, load_model          # reference: model.py:204, predict.py:9,24
+    model = load_model('saved7-model-218-0.73.hdf5')            # predict.py:24
+    pred = model.predict(X)                                     # predict.py:62  -> float32 [N,512,512,3]
+
+``Model`` mirrors the subset of the Keras ``Model`` object the reference touches (predict, summary,
+save / save_weights / load_weights, get_weights / set_weights, compile, fit_generator / train_on_batch)
+with the same argument meaning and error behaviour (ValueError for a wrong input shape, OSError for an
+unreadable checkpoint). All arithmetic runs in libitmo_b200.so on an sm_100a GPU; there is no CPU path.
+"""
+from __future__ import annotations
+
+import ctypes
+import math
+import os
+from typing import Any, Callable, Dict, List, Optional, Sequence
+
+import numpy as np
+
+from . import _lib, checkpoint, graph
+
+_PRECISIONS = {'bf16': _lib.PREC_BF16, 'tf32': _lib.PREC_TF32, 'fp32': _lib.PREC_TF32}
+
+
+def _default_precision() -> str:
+    return os.environ.get('ITMO_PRECISION', 'bf16').lower()
+
+
+def _he_normal(rng: np.random.Generator, shape, fan_in: int) -> np.ndarray:
+    """Keras 2.2.4 he_normal = VarianceScaling(2, 'fan_in', 'normal'): truncated normal (|z| <= 2),
+    stddev sqrt(2/fan_in)/0.8796 so the truncated distribution has the requested variance."""
+    std = math.sqrt(2.0 / fan_in) / .87962566103423978
+    out = rng.standard_normal(shape)
+    bad = np.abs(out) > 2.0
+    while bad.any():
+        out[bad] = rng.standard_normal(int(bad.sum()))
+        bad = np.abs(out) > 2.0
+    return (out * std).astype(np.float32)
+
+
+def initial_weights(seed: Optional[int] = None) -> checkpoint.Weights:
+    """Fresh weights as U_net() creates them (model.py:196,200,276): he_normal kernels, zero biases,
+    BN gamma=1 beta=0 mean=0 var=1, glorot_uniform head."""
+    rng = np.random.default_rng(seed)
+    ws: checkpoint.Weights = []
+    for l in graph.LAYERS:
+        ks = graph.kernel_shape(l)
+        if l.kind == 'head':
+            lim = math.sqrt(6.0 / (ks[2] + ks[3]))
+            ws.append({'kernel': rng.uniform(-lim, lim, ks).astype(np.float32),
+                       'bias': np.zeros(l.cout, np.float32)})
+            continue
+        fan_in = ks[0] * ks[1] * (ks[2] if l.kind == 'conv' else ks[3])
+        ws.append({'kernel': _he_normal(rng, ks, fan_in), 'bias': np.zeros(l.cout, np.float32),
+                   'gamma': np.ones(l.cout, np.float32), 'beta': np.zeros(l.cout, np.float32),
+                   'moving_mean': np.zeros(l.cout, np.float32), 'moving_variance': np.ones(l.cout, np.float32)})
+    return ws
+
+
+class Model:
+    """The compiled U-Net ('ReinhardtPrediction', model.py:278) bound to one B200."""
+
+    def __init__(self, weights: Optional[checkpoint.Weights] = None, input_size=(512, 512, 3),
+                 precision: Optional[str] = None, device: int = 0, max_batch: int = 32,
+                 bn_epsilon: float = graph.BN_EPS):
+        if tuple(input_size) != (graph.IMG, graph.IMG, 3):
+            raise ValueError(f'input_size {tuple(input_size)} is not supported: the kernels are built for the '
+                             f'reference\'s native ({graph.IMG}, {graph.IMG}, 3) input (model.py:204); larger frames '
+                             'go through cnn_itmo_b200.tiling')
+        precision = (precision or _default_precision()).lower()
+        if precision not in _PRECISIONS:
+            raise ValueError(f"precision must be one of {sorted(_PRECISIONS)}, got {precision!r}")
+        self.name = graph.MODEL_NAME
+        self.input_shape = (None,) + tuple(input_size)
+        self.output_shape = (None, graph.IMG, graph.IMG, 3)
+        self.precision = 'tf32' if precision == 'fp32' else precision
+        self.device = int(device)
+        self.max_batch = int(max_batch)
+        self.bn_epsilon = float(bn_epsilon)
+        self.optimizer = None
+        self.loss = None
+        self.metrics: List[str] = []
+        self.meta: Dict[str, Any] = {}
+        self._weights = weights if weights is not None else initial_weights()
+        self._ctx = ctypes.c_void_p()
+        self._uploaded = False
+
+    # ---- device context -----------------------------------------------------------------------------
+    def _ensure_ctx(self):
+        lib = _lib.load()
+        if not self._ctx:
+            _lib.check(lib.itmo_create(ctypes.byref(self._ctx), self.device, _PRECISIONS[self.precision],
+                                       self.max_batch))
+        if not self._uploaded:
+            arr = (_lib.LayerWeights * graph.NUM_LAYERS)()
+            keep = []
+            for i, w in enumerate(self._weights):
+                for field in ('kernel', 'bias', 'gamma', 'beta', 'moving_mean', 'moving_variance'):
+                    if field in w:
+                        a = np.ascontiguousarray(w[field], dtype=np.float32)
+                        keep.append(a)
+                        setattr(arr[i], field, a.ctypes.data_as(ctypes.POINTER(ctypes.c_float)))
+            _lib.check(lib.itmo_load_weights(self._ctx, arr, graph.NUM_LAYERS, self.bn_epsilon))
+            self._uploaded = True
+        return lib
+
+    def close(self):
+        if getattr(self, '_ctx', None):
+            _lib.load().itmo_destroy(self._ctx)
+            self._ctx = ctypes.c_void_p()
+            self._uploaded = False
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:  # noqa: BLE001
+            pass
+
+    @property
+    def ctx(self) -> ctypes.c_void_p:
+        """The itmo_ctx* (for callers that drive itmo_forward on device buffers, e.g. bench.py)."""
+        self._ensure_ctx()
+        return self._ctx
+
+    # ---- Keras Model surface ------------------------------------------------------------------------
+    def summary(self, line_length=None, positions=None, print_fn: Optional[Callable[[str], None]] = None):
+        graph.print_summary(print_fn or print)
+
+    def count_params(self) -> int:
+        return graph.count_params()['total']
+
+    def compile(self, optimizer='rmsprop', loss='mse', metrics=None, **kwargs):
+        """model.compile(optimizer='rmsprop', loss='mse', metrics=['accuracy']) (model.py:281)."""
+        if loss not in ('mse', 'mean_squared_error'):
+            raise ValueError(f'loss {loss!r} is not supported (the reference trains with mse)')
+        self.optimizer, self.loss, self.metrics = optimizer, loss, list(metrics or [])
+
+    def _check_input(self, x) -> np.ndarray:
+        x = np.asarray(x)
+        if x.ndim != 4 or tuple(x.shape[1:]) != (graph.IMG, graph.IMG, 3):
+            raise ValueError('Error when checking input: expected input_1 to have shape '
+                             f'({graph.IMG}, {graph.IMG}, 3) but got array with shape {tuple(x.shape[1:])}'
+                             if x.ndim == 4 else
+                             f'Error when checking input: expected input_1 to have 4 dimensions, but got array '
+                             f'with shape {tuple(x.shape)}')
+        return x
+
+    def predict(self, x, batch_size: Optional[int] = None, verbose: int = 0, steps=None) -> np.ndarray:
+        """model.predict(X) (predict.py:62): X [N,512,512,3] float in [0,1] (any float dtype, the reference
+        passes float64) -> float32 [N,512,512,3]. Synchronous; host in, host out."""
+        x = self._check_input(x)
+        if x.dtype == np.uint8:
+            raise ValueError('predict() takes normalised floats like the reference (predict.py:59); '
+                             'use predict_u8() for raw 8-bit images')
+        xf = np.ascontiguousarray(x, dtype=np.float32)  # Keras casts the fed array to floatx
+        out = np.empty((xf.shape[0], graph.IMG, graph.IMG, 3), dtype=np.float32)
+        if xf.shape[0] == 0:
+            return out
+        lib = self._ensure_ctx()
+        _lib.check(lib.itmo_predict_host(self._ctx, xf.ctypes.data, _lib.DT_F32, out.ctypes.data, _lib.DT_F32,
+                                         xf.shape[0], 0))
+        return out
+
+    def predict_u8(self, images_u8) -> np.ndarray:
+        """predict.py:59-64 fused: raw uint8 [N,512,512,3] -> uint8 [N,512,512,3] = trunc(sigmoid(...)*255)."""
+        x = self._check_input(images_u8)
+        if x.dtype != np.uint8:
+            raise ValueError('predict_u8() expects uint8 images')
+        x = np.ascontiguousarray(x)
+        out = np.empty_like(x)
+        if x.shape[0] == 0:
+            return out
+        lib = self._ensure_ctx()
+        _lib.check(lib.itmo_predict_host(self._ctx, x.ctypes.data, _lib.DT_U8, out.ctypes.data, _lib.DT_U8,
+                                         x.shape[0], 0))
+        return out
+
+    def forward_device(self, in_ptr: int, in_dtype: str, out_ptr: int, out_dtype: str, n: int, stream: int = 0):
+        """itmo_forward on caller-owned DEVICE buffers (data_ptr() of torch tensors). Asynchronous."""
+        lib = self._ensure_ctx()
+        dt = {'u8': _lib.DT_U8, 'f32': _lib.DT_F32}
+        _lib.check(lib.itmo_forward(self._ctx, in_ptr, dt[in_dtype], out_ptr, dt[out_dtype], n, 0, stream or None))
+
+    def launch_count(self) -> int:
+        return int(_lib.load().itmo_launch_count(self._ctx)) if self._ctx else 0
+
+    def read_activation(self, layer: int, pooled: bool = False) -> np.ndarray:
+        """Intermediate activation of the last forward chunk as float32 NHWC (per-layer parity tests)."""
+        lib = self._ensure_ctx()
+        l = graph.LAYERS[layer]
+        ho = (2 * l.hin if l.kind == 'convT' else l.hin) // (2 if pooled else 1)
+        buf = np.empty((self.max_batch, ho, ho, l.cout), dtype=np.float32)
+        n = ctypes.c_size_t(0)
+        _lib.check(lib.itmo_read_activation(self._ctx, layer, int(pooled),
+                                            buf.ctypes.data_as(ctypes.POINTER(ctypes.c_float)), buf.size,
+                                            ctypes.byref(n)))
+        return buf.reshape(-1)[:n.value].reshape(-1, ho, ho, l.cout)
+
+    # ---- weights ------------------------------------------------------------------------------------
+    def get_weights(self) -> List[np.ndarray]:
+        """Flat list in Keras' model.get_weights() order (model.layers order; kernel, bias / gamma, beta,
+        moving_mean, moving_variance per layer)."""
+        out: List[np.ndarray] = []
+        for k in graph.keras_layers():
+            if k.weight_layer is None:
+                continue
+            w = self._weights[k.weight_layer]
+            keys = checkpoint.BN_KEYS if k.cls == 'BatchNormalization' else ('kernel', 'bias')
+            out += [w[key].copy() for key in keys]
+        return out
+
+    def set_weights(self, flat: Sequence[np.ndarray]):
+        flat = list(flat)
+        i = 0
+        new = [dict(w) for w in self._weights]
+        for k in graph.keras_layers():
+            if k.weight_layer is None:
+                continue
+            keys = checkpoint.BN_KEYS if k.cls == 'BatchNormalization' else ('kernel', 'bias')
+            for key in keys:
+                if i >= len(flat):
+                    raise ValueError('You called `set_weights(weights)` with a weight list that is too short')
+                a = np.asarray(flat[i], dtype=np.float32)
+                if a.shape != new[k.weight_layer][key].shape:
+                    raise ValueError(f'Layer weight shape {new[k.weight_layer][key].shape} not compatible with '
+                                     f'provided weight shape {a.shape}')
+                new[k.weight_layer][key] = a.copy()
+                i += 1
+        if i != len(flat):
+            raise ValueError(f'set_weights: expected {i} arrays, got {len(flat)}')
+        self._weights = new
+        self._uploaded = False
+
+    def load_weights(self, filepath: str, by_name: bool = False):
+        self._weights, meta = checkpoint.read_checkpoint(filepath)
+        self.meta.update(meta)
+        self._uploaded = False
+
+    def save_weights(self, filepath: str, overwrite: bool = True):
+        if not overwrite and os.path.exists(filepath):
+            raise OSError(f'{filepath} exists')
+        checkpoint.write_checkpoint(filepath, self._weights, weights_only=True)
+
+    def save(self, filepath: str, overwrite: bool = True, include_optimizer: bool = True):
+        """model.save (what ModelCheckpoint calls every epoch, main.py:123-124): full Keras HDF5 layout."""
+        if not overwrite and os.path.exists(filepath):
+            raise OSError(f'{filepath} exists')
+        checkpoint.write_checkpoint(filepath, self._weights, weights_only=False)
+
+    # ---- training (main.py:126-132) -----------------------------------------------------------------
+    def train_on_batch(self, x, y):
+        raise NotImplementedError('the training step (forward + dgrad/wgrad + RMSprop, main.py:126-132) is not built '
+                                  'yet in this round; inference is complete')
+
+    def fit_generator(self, generator, steps_per_epoch=None, epochs=1, verbose=1, callbacks=None,
+                      validation_data=None, validation_steps=None, **kwargs):
+        raise NotImplementedError('fit_generator needs train_on_batch, which is not built yet in this round')
+
+
+def U_net(pretrained_weights=None, input_size=(512, 512, 3), precision: Optional[str] = None, device: int = 0,
+          max_batch: int = 32, seed: Optional[int] = None) -> Model:
+    """Builder with the reference's signature (model.py:204). Like the reference it IGNORES
+    ``pretrained_weights`` (the load is commented out at model.py:285-286), compiles with
+    rmsprop / mse / accuracy (model.py:281) and prints the summary (model.py:288)."""
+    model = Model(initial_weights(seed), input_size=input_size, precision=precision, device=device,
+                  max_batch=max_batch)
+    model.compile(optimizer='rmsprop', loss='mse', metrics=['accuracy'])
+    model.summary()
+    return model
+
+
+def load_model(filepath: str, custom_objects=None, compile: bool = True, precision: Optional[str] = None,
+               device: int = 0, max_batch: int = 32) -> Model:
+    """keras.models.load_model (predict.py:24): read a Keras full-model (or weights-only) HDF5 file."""
+    weights, meta = checkpoint.read_checkpoint(filepath)
+    model = Model(weights, precision=precision, device=device, max_batch=max_batch,
+                  bn_epsilon=meta.get('bn_epsilon', graph.BN_EPS))
+    model.meta = meta
+    if compile:
+        model.compile(optimizer='rmsprop', loss='mse', metrics=['accuracy'])
+    return model

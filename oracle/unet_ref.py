@@ -464,3 +464,69 @@ def predict_like_reference(tw: TorchWeights, images_u8: np.ndarray, one_at_a_tim
             outs.append(postprocess_u8(forward_torch(tw, X))[0])
         return np.stack(outs)
     return postprocess_u8(forward_torch(tw, preprocess_u8(images_u8)))
+
+
+# --------------------------------------------------------------------------------------------
+# calibrated synthetic checkpoint
+# --------------------------------------------------------------------------------------------
+def synthetic_images_u8(n: int, seed: int = 0, size: int = IMG) -> np.ndarray:
+    """Seeded SDR-like test images [n,size,size,3] uint8: smooth illumination gradients, a few hard edges and
+    sensor-like noise, with per-image exposure — closer to camera output than white noise, and they exercise
+    saturated (0 / 255) regions like the reference's virtual_camera.m clipping does."""
+    rng = np.random.default_rng(seed)
+    yy, xx = np.mgrid[0:size, 0:size].astype(np.float64) / size
+    out = np.empty((n, size, size, 3), dtype=np.uint8)
+    for i in range(n):
+        img = np.zeros((size, size, 3))
+        for c in range(3):
+            fx, fy, ph = rng.uniform(0.5, 6.0), rng.uniform(0.5, 6.0), rng.uniform(0, 2 * np.pi)
+            img[:, :, c] = 0.5 + 0.35 * np.sin(2 * np.pi * (fx * xx + fy * yy) + ph)
+        for _ in range(4):  # rectangles with hard edges
+            x0, y0 = rng.integers(0, size - 8, 2)
+            w, h = rng.integers(8, size // 2, 2)
+            img[y0:y0 + h, x0:x0 + w, :] = rng.uniform(0, 1, 3)
+        img *= 2.0 ** rng.uniform(-1.5, 1.5)           # exposure
+        img += rng.normal(0, 0.02, img.shape)
+        out[i] = np.clip(img * 255.0, 0, 255).astype(np.uint8)
+    return out
+
+
+def calibrated_weights(seed: int = 218, calib_size: int = 128, calib_n: int = 4) -> List[Dict[str, np.ndarray]]:
+    """``synthetic_weights`` with BatchNormalization moving statistics set the way training would leave them:
+    equal to the statistics of each layer's post-ReLU activations on a calibration batch. Activations then
+    stay O(1) through all 19 layers (a freshly drawn moving_mean/variance makes them explode, which would
+    saturate the sigmoid head and hide errors)."""
+    torch = _torch()
+    F = torch.nn.functional
+    ws = synthetic_weights(seed)
+    x = torch.from_numpy(preprocess_u8(synthetic_images_u8(calib_n, seed=seed + 1, size=calib_size))).float()
+    x = x.permute(0, 3, 1, 2).contiguous()
+    outs: Dict[int, 'torch.Tensor'] = {}
+    pooled: Dict[int, 'torch.Tensor'] = {}
+    with torch.no_grad():
+        for s in LAYERS:
+            if s.kind == 'head':
+                break
+            w = ws[s.index]
+            if len(s.src) == 2:
+                inp = torch.cat([outs[s.src[0]], outs[s.src[1]]], dim=1)
+            elif s.src[0] < 0:
+                inp = x
+            else:
+                inp = pooled[s.src[0]] if s.src_pooled else outs[s.src[0]]
+            k = torch.from_numpy(w['kernel']).permute(3, 2, 0, 1).contiguous()
+            b = torch.from_numpy(w['bias'])
+            z = F.conv2d(inp, k, b, padding=1) if s.kind == 'conv' else F.conv_transpose2d(inp, k, b, stride=2)
+            z = torch.relu(z)
+            mean = z.mean(dim=(0, 2, 3))
+            var = z.var(dim=(0, 2, 3), unbiased=False)
+            w['moving_mean'] = mean.numpy().astype(np.float32)
+            w['moving_variance'] = np.maximum(var.numpy(), 1e-4).astype(np.float32)
+            g, be = torch.from_numpy(w['gamma']), torch.from_numpy(w['beta'])
+            y = (g[None, :, None, None] * (z - mean[None, :, None, None])
+                 / torch.sqrt(torch.from_numpy(w['moving_variance'])[None, :, None, None] + BN_EPS)
+                 + be[None, :, None, None])
+            outs[s.index] = y
+            if s.pool:
+                pooled[s.index] = F.max_pool2d(y, 2, 2)
+    return ws
