@@ -38,6 +38,10 @@ SIGNATURES = {
     'itmo_forward': (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_int, c_uint, c_void_p]),
     'itmo_predict_host': (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_int, c_uint]),
     'itmo_launch_count': (c_longlong, [c_void_p]),
+    'itmo_host_alloc': (c_int, [POINTER(c_void_p), c_size_t]),
+    'itmo_host_free': (None, [c_void_p]),
+    'itmo_set_profiling': (c_int, [c_void_p, c_int]),
+    'itmo_layer_times': (c_int, [c_void_p, POINTER(ctypes.c_double), POINTER(c_longlong), c_int]),
     'itmo_read_activation': (c_int, [c_void_p, c_int, c_int, POINTER(c_float), c_size_t, POINTER(c_size_t)]),
     'itmo_conv3x3_bn': (c_int, [c_int, c_void_p, c_int, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p,
                                 c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p]),

@@ -460,18 +460,55 @@ struct itmo_ctx {
   size_t act_elems_per_img[ITMO_NUM_LAYERS] = {};
   size_t pooled_elems_per_img[ITMO_NUM_LAYERS] = {};
 
-  // host staging for itmo_predict_host
-  void* pin_in = nullptr;
-  void* pin_out = nullptr;
-  void* dev_in = nullptr;
-  void* dev_out = nullptr;
+  // itmo_predict_host: double-buffered device staging, copy streams and the events that order them
+  void* dev_in[2] = {};
+  void* dev_out[2] = {};
   size_t stage_in_bytes = 0, stage_out_bytes = 0;
-  cudaStream_t own_stream = nullptr;
+  cudaStream_t own_stream = nullptr;  // compute
+  cudaStream_t h2d_stream = nullptr;
+  cudaStream_t d2h_stream = nullptr;
+  cudaEvent_t ev_in_ready[2] = {}, ev_compute_done[2] = {}, ev_out_free[2] = {};
+
+  // per-layer device timing (itmo_set_profiling): event pairs recorded around every layer launch
+  bool profiling = false;
+  struct Stamp { int layer; cudaEvent_t beg, end; };
+  std::vector<Stamp> stamps;
+  std::vector<cudaEvent_t> event_pool;
+  double layer_ms[ITMO_NUM_LAYERS] = {};
+  long long layer_calls[ITMO_NUM_LAYERS] = {};
 };
 
 namespace {
 
 int out_hw(const LayerDef& L) { return L.kind == kConvT ? 2 * L.hin : L.hin; }
+
+cudaEvent_t take_event(itmo_ctx* ctx) {
+  if (!ctx->event_pool.empty()) {
+    cudaEvent_t e = ctx->event_pool.back();
+    ctx->event_pool.pop_back();
+    return e;
+  }
+  cudaEvent_t e = nullptr;
+  cudaEventCreate(&e);
+  return e;
+}
+
+// Brackets one layer launch with an event pair when profiling is on.
+struct LayerStamp {
+  itmo_ctx* ctx;
+  cudaStream_t stream;
+  cudaEvent_t end = nullptr;
+  LayerStamp(itmo_ctx* c, int layer, cudaStream_t s) : ctx(c), stream(s) {
+    if (!ctx->profiling) return;
+    cudaEvent_t beg = take_event(ctx);
+    end = take_event(ctx);
+    cudaEventRecord(beg, stream);
+    ctx->stamps.push_back({layer, beg, end});
+  }
+  ~LayerStamp() {
+    if (end) cudaEventRecord(end, stream);
+  }
+};
 
 int forward_chunk(itmo_ctx* ctx, const void* in_dev, int in_dtype, void* out_dev, int out_dtype, int nb,
                   cudaStream_t stream) {
@@ -479,6 +516,7 @@ int forward_chunk(itmo_ctx* ctx, const void* in_dev, int in_dtype, void* out_dev
   for (int li = 0; li < ITMO_NUM_LAYERS; ++li) {
     const LayerDef& L = kLayers[li];
     if (L.kind == kHead) continue;  // fused into layer 17's epilogue
+    LayerStamp stamp(ctx, li, stream);
     if (L.kind == kRgbConv) {
       int rc = run_rgb_conv(prec, in_dev, in_dtype, nb, L.hin, L.hin, (const float*)ctx->wpacked[li], ctx->bias[li],
                             ctx->scale[li], ctx->shift[li], ctx->act[li], stream);
@@ -591,6 +629,13 @@ int itmo_create(itmo_ctx** out, int device, int precision, int max_batch) {
     if (offs_pool[li] != size_t(-1)) ctx->pooled[li] = (char*)ctx->arena + offs_pool[li];
   }
   e = cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking);
+  if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->h2d_stream, cudaStreamNonBlocking);
+  if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->d2h_stream, cudaStreamNonBlocking);
+  for (int b = 0; b < 2 && e == cudaSuccess; ++b) {
+    e = cudaEventCreateWithFlags(&ctx->ev_in_ready[b], cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ctx->ev_compute_done[b], cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ctx->ev_out_free[b], cudaEventDisableTiming);
+  }
   if (e != cudaSuccess) {
     itmo_destroy(ctx);
     return fail(ITMO_ERR_CUDA, "cudaStreamCreate failed: %s", cudaGetErrorString(e));
@@ -610,11 +655,21 @@ void itmo_destroy(itmo_ctx* ctx) {
     cudaFree(ctx->shift[li]);
   }
   cudaFree(ctx->arena);
-  cudaFree(ctx->dev_in);
-  cudaFree(ctx->dev_out);
-  if (ctx->pin_in) cudaFreeHost(ctx->pin_in);
-  if (ctx->pin_out) cudaFreeHost(ctx->pin_out);
+  for (int b = 0; b < 2; ++b) {
+    cudaFree(ctx->dev_in[b]);
+    cudaFree(ctx->dev_out[b]);
+    if (ctx->ev_in_ready[b]) cudaEventDestroy(ctx->ev_in_ready[b]);
+    if (ctx->ev_compute_done[b]) cudaEventDestroy(ctx->ev_compute_done[b]);
+    if (ctx->ev_out_free[b]) cudaEventDestroy(ctx->ev_out_free[b]);
+  }
+  for (auto& st : ctx->stamps) {
+    cudaEventDestroy(st.beg);
+    cudaEventDestroy(st.end);
+  }
+  for (auto e : ctx->event_pool) cudaEventDestroy(e);
   if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
+  if (ctx->h2d_stream) cudaStreamDestroy(ctx->h2d_stream);
+  if (ctx->d2h_stream) cudaStreamDestroy(ctx->d2h_stream);
   delete ctx;
 }
 
@@ -714,44 +769,100 @@ int itmo_forward(itmo_ctx* ctx, const void* in_dev, int in_dtype, void* out_dev,
 
 int itmo_predict_host(itmo_ctx* ctx, const void* in_host, int in_dtype, void* out_host, int out_dtype, int n,
                       unsigned flags) {
+  (void)flags;
   if (!ctx || !in_host || !out_host) return fail(ITMO_ERR_INVALID, "null argument");
   if (!ctx->weights_loaded) return fail(ITMO_ERR_STATE, "itmo_predict_host before itmo_load_weights");
   if (in_dtype != ITMO_DT_U8 && in_dtype != ITMO_DT_F32) return fail(ITMO_ERR_INVALID, "bad in_dtype");
   if (out_dtype != ITMO_DT_U8 && out_dtype != ITMO_DT_F32) return fail(ITMO_ERR_INVALID, "bad out_dtype");
+  if (n < 0) return fail(ITMO_ERR_INVALID, "negative batch");
   ITMO_CUDA(cudaSetDevice(ctx->device));
   const size_t in_img = size_t(ITMO_IMG) * ITMO_IMG * 3 * (in_dtype == ITMO_DT_U8 ? 1 : 4);
   const size_t out_img = size_t(ITMO_IMG) * ITMO_IMG * 3 * (out_dtype == ITMO_DT_U8 ? 1 : 4);
   const size_t need_in = in_img * ctx->cap, need_out = out_img * ctx->cap;
   if (ctx->stage_in_bytes < need_in) {
-    if (ctx->pin_in) cudaFreeHost(ctx->pin_in);
-    cudaFree(ctx->dev_in);
-    ctx->pin_in = ctx->dev_in = nullptr;
+    for (int b = 0; b < 2; ++b) {
+      cudaFree(ctx->dev_in[b]);
+      ctx->dev_in[b] = nullptr;
+    }
     ctx->stage_in_bytes = 0;
-    ITMO_CUDA(cudaMallocHost(&ctx->pin_in, need_in));
-    ITMO_CUDA(cudaMalloc(&ctx->dev_in, need_in));
+    for (int b = 0; b < 2; ++b) ITMO_CUDA(cudaMalloc(&ctx->dev_in[b], need_in));
     ctx->stage_in_bytes = need_in;
   }
   if (ctx->stage_out_bytes < need_out) {
-    if (ctx->pin_out) cudaFreeHost(ctx->pin_out);
-    cudaFree(ctx->dev_out);
-    ctx->pin_out = ctx->dev_out = nullptr;
+    for (int b = 0; b < 2; ++b) {
+      cudaFree(ctx->dev_out[b]);
+      ctx->dev_out[b] = nullptr;
+    }
     ctx->stage_out_bytes = 0;
-    ITMO_CUDA(cudaMallocHost(&ctx->pin_out, need_out));
-    ITMO_CUDA(cudaMalloc(&ctx->dev_out, need_out));
+    for (int b = 0; b < 2; ++b) ITMO_CUDA(cudaMalloc(&ctx->dev_out[b], need_out));
     ctx->stage_out_bytes = need_out;
   }
-  cudaStream_t s = ctx->own_stream;
-  for (int i0 = 0; i0 < n; i0 += ctx->cap) {
+  // Three streams: while chunk c computes, chunk c+1's input is on its way up and chunk c-1's result on its
+  // way down. Host buffers from itmo_host_alloc() (pinned) copy asynchronously; pageable buffers still work,
+  // the driver then stages the copies itself.
+  int c = 0;
+  for (int i0 = 0; i0 < n; i0 += ctx->cap, ++c) {
     const int nb = std::min(ctx->cap, n - i0);
-    memcpy(ctx->pin_in, (const char*)in_host + i0 * in_img, nb * in_img);
-    ITMO_CUDA(cudaMemcpyAsync(ctx->dev_in, ctx->pin_in, nb * in_img, cudaMemcpyHostToDevice, s));
-    int rc = forward_chunk(ctx, ctx->dev_in, in_dtype, ctx->dev_out, out_dtype, nb, s);
+    const int b = c & 1;
+    if (c >= 2) ITMO_CUDA(cudaStreamWaitEvent(ctx->h2d_stream, ctx->ev_compute_done[b], 0));  // dev_in[b] consumed
+    ITMO_CUDA(cudaMemcpyAsync(ctx->dev_in[b], (const char*)in_host + i0 * in_img, nb * in_img, cudaMemcpyHostToDevice,
+                              ctx->h2d_stream));
+    ITMO_CUDA(cudaEventRecord(ctx->ev_in_ready[b], ctx->h2d_stream));
+    ITMO_CUDA(cudaStreamWaitEvent(ctx->own_stream, ctx->ev_in_ready[b], 0));
+    if (c >= 2) ITMO_CUDA(cudaStreamWaitEvent(ctx->own_stream, ctx->ev_out_free[b], 0));      // dev_out[b] drained
+    int rc = forward_chunk(ctx, ctx->dev_in[b], in_dtype, ctx->dev_out[b], out_dtype, nb, ctx->own_stream);
     if (rc) return rc;
-    ITMO_CUDA(cudaMemcpyAsync(ctx->pin_out, ctx->dev_out, nb * out_img, cudaMemcpyDeviceToHost, s));
-    ITMO_CUDA(cudaStreamSynchronize(s));
-    memcpy((char*)out_host + i0 * out_img, ctx->pin_out, nb * out_img);
+    ITMO_CUDA(cudaEventRecord(ctx->ev_compute_done[b], ctx->own_stream));
+    ITMO_CUDA(cudaStreamWaitEvent(ctx->d2h_stream, ctx->ev_compute_done[b], 0));
+    ITMO_CUDA(cudaMemcpyAsync((char*)out_host + i0 * out_img, ctx->dev_out[b], nb * out_img, cudaMemcpyDeviceToHost,
+                              ctx->d2h_stream));
+    ITMO_CUDA(cudaEventRecord(ctx->ev_out_free[b], ctx->d2h_stream));
   }
-  (void)flags;
+  ITMO_CUDA(cudaStreamSynchronize(ctx->h2d_stream));
+  ITMO_CUDA(cudaStreamSynchronize(ctx->own_stream));
+  ITMO_CUDA(cudaStreamSynchronize(ctx->d2h_stream));
+  return ITMO_OK;
+}
+
+int itmo_host_alloc(void** out, size_t bytes) {
+  if (!out) return fail(ITMO_ERR_INVALID, "out is null");
+  *out = nullptr;
+  cudaError_t e = cudaMallocHost(out, bytes ? bytes : 1);
+  if (e != cudaSuccess) return fail(ITMO_ERR_NOMEM, "cudaMallocHost(%zu) failed: %s", bytes, cudaGetErrorString(e));
+  return ITMO_OK;
+}
+
+void itmo_host_free(void* p) {
+  if (p) cudaFreeHost(p);
+}
+
+int itmo_set_profiling(itmo_ctx* ctx, int enable) {
+  if (!ctx) return fail(ITMO_ERR_INVALID, "null argument");
+  ctx->profiling = enable != 0;
+  return ITMO_OK;
+}
+
+int itmo_layer_times(itmo_ctx* ctx, double* ms_sum, long long* calls, int reset) {
+  if (!ctx) return fail(ITMO_ERR_INVALID, "null argument");
+  ITMO_CUDA(cudaSetDevice(ctx->device));
+  for (auto& st : ctx->stamps) {
+    ITMO_CUDA(cudaEventSynchronize(st.end));
+    float ms = 0.f;
+    ITMO_CUDA(cudaEventElapsedTime(&ms, st.beg, st.end));
+    ctx->layer_ms[st.layer] += ms;
+    ctx->layer_calls[st.layer] += 1;
+    ctx->event_pool.push_back(st.beg);
+    ctx->event_pool.push_back(st.end);
+  }
+  ctx->stamps.clear();
+  for (int i = 0; i < ITMO_NUM_LAYERS; ++i) {
+    if (ms_sum) ms_sum[i] = ctx->layer_ms[i];
+    if (calls) calls[i] = ctx->layer_calls[i];
+    if (reset) {
+      ctx->layer_ms[i] = 0.0;
+      ctx->layer_calls[i] = 0;
+    }
+  }
   return ITMO_OK;
 }
 

@@ -58,6 +58,21 @@ def initial_weights(seed: Optional[int] = None) -> checkpoint.Weights:
     return ws
 
 
+def pinned_empty(shape, dtype) -> np.ndarray:
+    """numpy array in page-locked host memory (itmo_host_alloc): H2D/D2H copies from/to it are asynchronous, so
+    ``predict`` / ``predict_u8`` overlap them with the kernels. The memory is released with the array."""
+    import weakref
+    lib = _lib.load()
+    dtype = np.dtype(dtype)
+    nbytes = int(np.prod(shape, dtype=np.int64)) * dtype.itemsize
+    ptr = ctypes.c_void_p()
+    _lib.check(lib.itmo_host_alloc(ctypes.byref(ptr), nbytes))
+    buf = (ctypes.c_char * max(nbytes, 1)).from_address(ptr.value)
+    arr = np.frombuffer(buf, dtype=dtype, count=nbytes // dtype.itemsize).reshape(shape)
+    weakref.finalize(buf, lib.itmo_host_free, ptr)
+    return arr
+
+
 class Model:
     """The compiled U-Net ('ReinhardtPrediction', model.py:278) bound to one B200."""
 
@@ -153,11 +168,12 @@ class Model:
         if x.dtype == np.uint8:
             raise ValueError('predict() takes normalised floats like the reference (predict.py:59); '
                              'use predict_u8() for raw 8-bit images')
-        xf = np.ascontiguousarray(x, dtype=np.float32)  # Keras casts the fed array to floatx
-        out = np.empty((xf.shape[0], graph.IMG, graph.IMG, 3), dtype=np.float32)
-        if xf.shape[0] == 0:
-            return out
+        if x.shape[0] == 0:
+            return np.empty((0, graph.IMG, graph.IMG, 3), dtype=np.float32)
         lib = self._ensure_ctx()
+        xf = pinned_empty(x.shape, np.float32)
+        np.copyto(xf, x, casting='unsafe')              # Keras casts the fed array to floatx
+        out = pinned_empty((xf.shape[0], graph.IMG, graph.IMG, 3), np.float32)
         _lib.check(lib.itmo_predict_host(self._ctx, xf.ctypes.data, _lib.DT_F32, out.ctypes.data, _lib.DT_F32,
                                          xf.shape[0], 0))
         return out
@@ -167,11 +183,11 @@ class Model:
         x = self._check_input(images_u8)
         if x.dtype != np.uint8:
             raise ValueError('predict_u8() expects uint8 images')
-        x = np.ascontiguousarray(x)
-        out = np.empty_like(x)
         if x.shape[0] == 0:
-            return out
+            return np.empty_like(x)
         lib = self._ensure_ctx()
+        x = np.ascontiguousarray(x)
+        out = pinned_empty(x.shape, np.uint8)
         _lib.check(lib.itmo_predict_host(self._ctx, x.ctypes.data, _lib.DT_U8, out.ctypes.data, _lib.DT_U8,
                                          x.shape[0], 0))
         return out
@@ -181,6 +197,19 @@ class Model:
         lib = self._ensure_ctx()
         dt = {'u8': _lib.DT_U8, 'f32': _lib.DT_F32}
         _lib.check(lib.itmo_forward(self._ctx, in_ptr, dt[in_dtype], out_ptr, dt[out_dtype], n, 0, stream or None))
+
+    def set_profiling(self, enable: bool = True):
+        """Bracket every layer launch with CUDA events (itmo_set_profiling); read with layer_times()."""
+        lib = self._ensure_ctx()
+        _lib.check(lib.itmo_set_profiling(self._ctx, int(bool(enable))))
+
+    def layer_times(self, reset: bool = True):
+        """[(milliseconds, launches)] per layer of graph.LAYERS accumulated since the last reset."""
+        lib = self._ensure_ctx()
+        ms = (ctypes.c_double * graph.NUM_LAYERS)()
+        calls = (ctypes.c_longlong * graph.NUM_LAYERS)()
+        _lib.check(lib.itmo_layer_times(self._ctx, ms, calls, int(reset)))
+        return [(float(ms[i]), int(calls[i])) for i in range(graph.NUM_LAYERS)]
 
     def launch_count(self) -> int:
         return int(_lib.load().itmo_launch_count(self._ctx)) if self._ctx else 0

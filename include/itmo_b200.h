@@ -95,6 +95,18 @@ int itmo_forward(itmo_ctx* ctx, const void* in_dev, int in_dtype, void* out_dev,
 int itmo_predict_host(itmo_ctx* ctx, const void* in_host, int in_dtype, void* out_host, int out_dtype, int n,
                       unsigned flags);
 
+/* Pinned (page-locked) host memory for itmo_predict_host's in/out buffers: copies from/to it are asynchronous
+ * and overlap the kernels. Free with itmo_host_free(). */
+int itmo_host_alloc(void** out, size_t bytes);
+void itmo_host_free(void* p);
+
+/* Per-layer device timing. While enabled, every layer launch of itmo_forward / itmo_predict_host is bracketed by
+ * a CUDA event pair on its stream. itmo_layer_times() waits for the recorded events and returns, per layer of
+ * ITMO_NUM_LAYERS, the accumulated milliseconds and the number of launches since the last reset (either output
+ * may be NULL). The fused head (layer 18) reports 0. */
+int itmo_set_profiling(itmo_ctx* ctx, int enable);
+int itmo_layer_times(itmo_ctx* ctx, double* ms_sum, long long* calls, int reset);
+
 /* Number of kernels itmo launched on this context since creation (for bench.py's gpu_launches). */
 long long itmo_launch_count(const itmo_ctx* ctx);
 

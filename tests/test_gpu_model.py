@@ -1,0 +1,163 @@
+"""Whole-graph GPU parity (``-m gpu``): Model.predict / predict_u8 / itmo_forward against the CPU oracle, the
+committed fixtures, and size-independent properties at BASELINE.json's batch sizes."""
+import ctypes
+import os
+
+import numpy as np
+import pytest
+
+from oracle import unet_ref as R
+
+pytestmark = pytest.mark.gpu
+
+torch = pytest.importorskip('torch')
+
+
+@pytest.fixture(scope='module')
+def pkg():
+    assert torch.cuda.is_available(), 'the gpu tests need a CUDA device'
+    import cnn_itmo_b200 as M
+    return M
+
+
+@pytest.fixture(scope='module')
+def images():
+    return R.synthetic_images_u8(3, seed=5)
+
+
+@pytest.fixture(scope='module')
+def oracle_out(calibrated_weights, images):
+    outs, pooled = R.forward_torch(R.TorchWeights(calibrated_weights), R.preprocess_u8(images), return_all=True)
+    return outs, pooled
+
+
+def test_predict_tf32_matches_oracle(pkg, calibrated_weights, images, oracle_out):
+    """north_star: max abs error <= 1e-3 on [0,1] outputs in TF32/fp32 mode; every intermediate tensor too."""
+    m = pkg.Model(calibrated_weights, precision='tf32', max_batch=3)
+    out = m.predict(R.preprocess_u8(images).astype(np.float64))   # the reference feeds float64 (predict.py:59)
+    ref = oracle_out[0][18]
+    assert out.dtype == np.float32 and out.shape == (3, 512, 512, 3)
+    assert np.abs(out - ref).max() <= 1e-3, float(np.abs(out - ref).max())
+    for li in range(17):
+        act = m.read_activation(li)
+        r = oracle_out[0][li]
+        assert np.abs(act - r).max() <= 1e-3 * max(1.0, float(np.abs(r).max())), li
+        if R.LAYERS[li].pool:
+            pa = m.read_activation(li, pooled=True)
+            assert np.abs(pa - oracle_out[1][li]).max() <= 1e-3 * max(1.0, float(np.abs(r).max())), li
+    m.close()
+
+
+def test_predict_bf16_psnr(pkg, calibrated_weights, images, oracle_out):
+    """north_star: PSNR >= 45 dB against the reference in bf16 mode."""
+    m = pkg.Model(calibrated_weights, precision='bf16', max_batch=2)   # 3 images -> two arena chunks
+    out = m.predict(R.preprocess_u8(images))
+    ref = oracle_out[0][18]
+    assert R.psnr(out, ref) >= 45.0, R.psnr(out, ref)
+    for i in range(3):
+        assert R.psnr(out[i], ref[i]) >= 45.0
+    m.close()
+
+
+@pytest.mark.parametrize('prec', ['tf32', 'bf16'])
+def test_predict_u8_is_predict_py_flow(pkg, calibrated_weights, images, prec):
+    """predict.py:59-64: u8/255 -> predict -> trunc(p*255). The fused u8-in/u8-out path must equal the float path
+    of the same precision exactly (same kernels, only the load/store differ)."""
+    m = pkg.Model(calibrated_weights, precision=prec, max_batch=4)
+    u8 = m.predict_u8(images)
+    via_float = R.postprocess_u8(m.predict(R.preprocess_u8(images)))
+    assert u8.dtype == np.uint8 and u8.shape == images.shape
+    np.testing.assert_array_equal(u8, via_float)
+    ref = R.predict_like_reference(R.TorchWeights(calibrated_weights), images, one_at_a_time=False)
+    d = np.abs(u8.astype(np.int32) - ref.astype(np.int32))
+    if prec == 'tf32':
+        assert d.max() <= 1 and (d != 0).mean() < 0.02
+    else:
+        assert R.psnr(u8 / 255.0, ref / 255.0) >= 45.0
+    m.close()
+
+
+def test_reference_fixture_images(pkg, calibrated_weights, golden_dir):
+    """The reference's 12 committed inputs (images_to_predict/input) through the predict.py flow. Their committed
+    outputs belong to the stripped checkpoint, so the comparison is against the oracle with the same synthetic
+    weights; the shapes/dtypes of the committed outputs are checked as the format contract."""
+    from PIL import Image
+    from cnn_itmo_b200 import predict as P
+    files = P.list_inputs(os.path.join(golden_dir, 'images_to_predict', 'input'))
+    assert len(files) == 12
+    imgs = np.stack([P.load_png(f) for f in files])
+    m = pkg.Model(calibrated_weights, precision='tf32', max_batch=12)
+    got = m.predict_u8(imgs)
+    ref = R.predict_like_reference(R.TorchWeights(calibrated_weights), imgs, one_at_a_time=False)
+    d = np.abs(got.astype(np.int32) - ref.astype(np.int32))
+    assert d.max() <= 1 and (d != 0).mean() < 0.02
+    with Image.open(os.path.join(golden_dir, 'images_to_predict', 'output', os.path.basename(files[0]))) as im:
+        assert np.asarray(im).shape == got[0].shape and np.asarray(im).dtype == got.dtype
+    m.close()
+
+
+def test_checkpoint_file_to_prediction(pkg, calibrated_weights, images, oracle_out, tmp_path):
+    """load_model(path).predict(X) (predict.py:24,62) from a Keras-layout HDF5 file written by our writer."""
+    p = str(tmp_path / 'saved7-model-218-0.73.hdf5')
+    pkg.write_checkpoint(p, calibrated_weights)
+    m = pkg.load_model(p, precision='tf32', max_batch=1)
+    out = m.predict(R.preprocess_u8(images[:1]))
+    assert np.abs(out - oracle_out[0][18][:1]).max() <= 1e-3
+    m.close()
+
+
+@pytest.mark.parametrize('prec', ['bf16', 'tf32'])
+def test_properties_at_full_batch(pkg, calibrated_weights, prec):
+    """Size-independent properties at BASELINE batch sizes (the oracle cannot follow here): determinism, batch
+    independence (image i of a batch of 64 == the same image alone), arena-chunking invariance, range."""
+    n = 64
+    base = R.synthetic_images_u8(4, seed=9)
+    imgs = np.concatenate([base] * (n // 4))
+    imgs[7] = 0
+    imgs[8] = 255
+    dev = torch.device('cuda:0')
+    x = torch.from_numpy(imgs).to(dev)
+    m = pkg.Model(calibrated_weights, precision=prec, max_batch=n)
+    o1 = torch.empty_like(x)
+    o2 = torch.empty_like(x)
+    m.forward_device(x.data_ptr(), 'u8', o1.data_ptr(), 'u8', n)
+    m.forward_device(x.data_ptr(), 'u8', o2.data_ptr(), 'u8', n)
+    torch.cuda.synchronize()
+    assert torch.equal(o1, o2)                                      # deterministic
+    assert torch.equal(o1[0:3], o1[12:15]) and torch.equal(o1[1], o1[61])   # batch independence
+    m2 = pkg.Model(calibrated_weights, precision=prec, max_batch=5)  # ragged chunks 5,5,...,4
+    o3 = torch.empty_like(x)
+    m2.forward_device(x.data_ptr(), 'u8', o3.data_ptr(), 'u8', n)
+    torch.cuda.synchronize()
+    assert torch.equal(o1, o3)                                      # chunking invariance
+    single = m2.predict_u8(imgs[7:9])
+    np.testing.assert_array_equal(single, o1[7:9].cpu().numpy())
+    of = torch.empty((n, 512, 512, 3), dtype=torch.float32, device=dev)
+    m.forward_device(x.data_ptr(), 'u8', of.data_ptr(), 'f32', n)
+    torch.cuda.synchronize()
+    assert bool(torch.isfinite(of).all()) and float(of.min()) >= 0.0 and float(of.max()) <= 1.0
+    assert torch.equal((of * 255.0).to(torch.uint8), o1)            # u8 store == trunc(f32 store * 255)
+    assert m.launch_count() > 0 and m.launch_count() % 3 == 0       # three identical forward calls
+    m.close()
+    m2.close()
+
+
+def test_empty_batch_and_errors(pkg, calibrated_weights):
+    from cnn_itmo_b200 import _lib as L
+    m = pkg.Model(calibrated_weights, precision='bf16', max_batch=1)
+    assert m.predict(np.zeros((0, 512, 512, 3), np.float32)).shape == (0, 512, 512, 3)
+    with pytest.raises(ValueError):
+        m.predict(np.zeros((1, 256, 256, 3), np.float32))
+    lib = L.load()
+    ctx = ctypes.c_void_p()
+    L.check(lib.itmo_create(ctypes.byref(ctx), 0, L.PREC_BF16, 1))
+    x = torch.zeros((1, 512, 512, 3), dtype=torch.uint8, device='cuda:0')
+    rc = lib.itmo_forward(ctx, x.data_ptr(), L.DT_U8, x.data_ptr(), L.DT_U8, 1, 0, None)
+    assert rc == -3 and b'itmo_load_weights' in lib.itmo_last_error()      # ITMO_ERR_STATE, message set
+    assert lib.itmo_create(ctypes.byref(ctypes.c_void_p()), 0, 7, 1) == -1  # bad precision
+    lib.itmo_destroy(ctx)
+    # the stateless operators validate shapes instead of launching garbage
+    rc = lib.itmo_conv3x3_bn(L.PREC_BF16, x.data_ptr(), 24, None, 0, 1, 16, 16, x.data_ptr(), x.data_ptr(),
+                             x.data_ptr(), x.data_ptr(), 32, x.data_ptr(), None, None)
+    assert rc == -1
+    m.close()
