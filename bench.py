@@ -1,0 +1,398 @@
+#!/usr/bin/env python
+"""bench.py — throughput of the CNN-ITMO U-Net hot path (predict.py:62, model.py:204-278) on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W]            # this repo's sm_100a path
+    python bench.py --impl reference [--steps K] [--warmup W]      # CPU restatement of the reference path
+    torchrun --nnodes=1 --nproc-per-node N ... bench.py --gpus N   # one rank per GPU (weak scaling)
+
+A "step" is one forward pass of the whole U-Net over one batch of synthetic 512x512 SDR images per GPU
+(BASELINE.json configs[2]: full U-Net inference, batch 256, bf16 operands / fp32 accumulate). Weights are
+random-init (he_normal, exactly what ``U_net()`` creates): the committed checkpoint the reference names is
+absent from the reference tree (.MISSING_LARGE_BLOBS). Rank 0 prints ONE JSON line:
+
+  value      images/s over all ranks, inputs already resident in HBM (itmo_forward on device buffers)
+  e2e        images/s through Model.predict_u8 -> itmo_predict_host: pinned HOST uint8 in, HOST uint8 out,
+             H2D and D2H copies inside the timed region
+  roofline   the implicit-GEMM conv kernel (17 launches per arena chunk = 99.7 % of the FLOPs): algorithmic
+             FLOPs / summed CUDA-event duration of those launches inside the timed region, against the
+             measured bf16 tensor peak of MEASURED_PEAKS.json
+  cpu_baseline  the torch-CPU (oneDNN) restatement of the reference graph (oracle/unet_ref.py) timed on this
+             box's host cores on a bounded sample — TensorFlow itself cannot be installed here
+
+L2 hygiene: every step streams > 40 GB of activations through a 126 MB L2 (inputs alone are 201 MB), so no
+explicit flush is needed; ``config.l2`` says so.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+IMG = 512
+MPIX_PER_IMAGE = IMG * IMG / 1e6
+METRIC = 'U-Net SDR->HDR inference throughput (512x512 images)'
+UNIT = 'images/s'
+
+
+def log(*a):
+    print(*a, file=sys.stderr, flush=True)
+
+
+def measured_peaks():
+    """Roofline denominators: MEASURED_PEAKS.json (driver-written) or the profiling guide's fallback."""
+    p = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    try:
+        with open(p) as f:
+            d = json.load(f)
+        return {'hbm_gbs': float(d['hbm_gbs']), 'tflops_burst': float(d['bf16_tflops']),
+                'tflops_sustained': float(d.get('bf16_tflops_sustained', d['bf16_tflops'])), 'source': 'measured'}
+    except Exception:  # noqa: BLE001
+        return {'hbm_gbs': 6650.0, 'tflops_burst': 1590.0, 'tflops_sustained': 1400.0, 'source': 'fallback'}
+
+
+# --------------------------------------------------------------------------------------------------
+# clocks: sample nvidia-smi DURING the timed region
+# --------------------------------------------------------------------------------------------------
+class ClockSampler:
+    FIELDS = ('index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,'
+              'clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
+              'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, gpu_index: int):
+        self.gpu = gpu_index
+        self.proc = None
+        self.path = None
+
+    def start(self):
+        try:
+            fd, self.path = tempfile.mkstemp(prefix='itmo_clocks_', suffix='.csv')
+            os.close(fd)
+            self.proc = subprocess.Popen(['nvidia-smi', '-i', str(self.gpu), f'--query-gpu={self.FIELDS}',
+                                          '--format=csv,noheader,nounits', '-lms', '100'],
+                                         stdout=open(self.path, 'w'), stderr=subprocess.DEVNULL)
+        except Exception:  # noqa: BLE001
+            self.proc = None
+
+    def stop(self):
+        out = {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': [], 'samples': 0}
+        if self.proc is None:
+            return out
+        try:
+            self.proc.terminate()
+            self.proc.wait(timeout=5)
+        except Exception:  # noqa: BLE001
+            try:
+                self.proc.kill()
+            except Exception:  # noqa: BLE001
+                pass
+        sm, mx, pw, reasons = [], [], [], set()
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        try:
+            with open(self.path) as f:
+                for line in f:
+                    parts = [p.strip() for p in line.split(',')]
+                    if len(parts) < 9:
+                        continue
+                    try:
+                        sm.append(float(parts[1]))
+                        mx.append(float(parts[2]))
+                        pw.append(float(parts[3]))
+                    except ValueError:
+                        continue
+                    for nm, v in zip(names, parts[5:9]):
+                        if v.lower().startswith('active'):
+                            reasons.add(nm)
+            os.unlink(self.path)
+        except Exception:  # noqa: BLE001
+            pass
+        if sm:
+            # "under load" = samples whose power is in the upper half of what was seen
+            thr = 0.5 * max(pw) if pw else 0
+            load = sorted(s for s, p in zip(sm, pw) if p >= thr) or sorted(sm)
+            out.update(sm_mhz=load[len(load) // 2], sm_max_mhz=max(mx), reasons=sorted(reasons), samples=len(sm),
+                       power_w_max=max(pw) if pw else None)
+        return out
+
+
+# --------------------------------------------------------------------------------------------------
+# CPU restatement (oracle) legs — the only places bench.py touches oracle/
+# --------------------------------------------------------------------------------------------------
+def cpu_reference_time(weights, n_images_hint: int, budget_s: float = 15.0):
+    """Times the torch-CPU restatement of predict.py:50-64 (one image per call, like the reference loop) on all
+    host cores. Returns (images_per_s, n_images, cores, seconds)."""
+    import numpy as np
+    import torch
+    from oracle import unet_ref as R
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    tw = R.TorchWeights(weights)
+    rng = np.random.default_rng(0)
+    imgs = rng.integers(0, 256, (max(1, n_images_hint), IMG, IMG, 3), dtype=np.uint8)
+    R.predict_like_reference(tw, imgs[:1])                      # warm-up (oneDNN primitive creation)
+    t0 = time.perf_counter()
+    R.predict_like_reference(tw, imgs[:1])
+    t1 = time.perf_counter() - t0
+    n = int(max(2, min(n_images_hint, budget_s / max(t1, 1e-3))))
+    t0 = time.perf_counter()
+    R.predict_like_reference(tw, imgs[:n])
+    dt = time.perf_counter() - t0
+    return n / dt, n, cores, dt
+
+
+def run_reference_arm(a):
+    """--impl reference: the reference's own CPU path cannot run here (TensorFlow 1.x / Keras 2.2 are not
+    installable), so this times its CPU restatement (oracle/unet_ref.py, torch-CPU/oneDNN fp32) with all host
+    threads. Each step = a bounded sample of the batch-256 workload, one image per predict call."""
+    rank = int(os.environ.get('RANK', '0'))
+    if rank != 0:
+        return 0
+    import numpy as np
+    import torch
+    from oracle import unet_ref as R
+    import cnn_itmo_b200 as M
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    ws = M.initial_weights(seed=218)
+    tw = R.TorchWeights(ws)
+    imgs = np.random.default_rng(0).integers(0, 256, (a.cpu_sample, IMG, IMG, 3), dtype=np.uint8)
+    for _ in range(max(1, a.warmup)):
+        R.predict_like_reference(tw, imgs[:1])
+    t0 = time.perf_counter()
+    for _ in range(a.steps):
+        R.predict_like_reference(tw, imgs)
+    dt = time.perf_counter() - t0
+    ips = a.steps * a.cpu_sample / dt
+    sample = (f'{a.cpu_sample} of the {a.batch} images per step, one image per predict call (predict.py:50-62), '
+              f'torch-CPU fp32 restatement, {cores} threads')
+    line = {
+        'impl': 'reference', 'metric': METRIC, 'value': round(ips, 4), 'unit': UNIT, 'n_gpus': a.gpus,
+        'steps': a.steps, 'warmup': a.warmup, 'ms_per_step': round(1e3 * dt / a.steps, 3), 'higher_is_better': True,
+        'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+        'mpix_per_s': round(ips * MPIX_PER_IMAGE, 4),
+        'config': workload_config(a, chunk=None),
+        'cpu_baseline': {'value': round(ips, 4), 'unit': UNIT, 'cores': cores, 'kind': 'port', 'sample': sample},
+        'e2e': {'value': round(ips, 4), 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+        'gpu_launches': 0,
+        'note': 'TensorFlow-CPU (the reference runtime) is unavailable on this box; this is its CPU restatement',
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+def workload_config(a, chunk):
+    cfg = {'workload': f'full U-Net forward (19 weight layers, 165.37 GFLOP/image), batch {a.batch} per GPU, '
+                       f'512x512x3 uint8 in -> uint8 out, random-init weights (BASELINE configs[2])',
+           'batch_per_gpu': a.batch, 'global_batch': a.batch * a.gpus, 'precision': a.precision,
+           'parallelism': f'dp{a.gpus} (independent image batches, no collective on the data path)',
+           'l2': 'inputs and activations far larger than L2 (>40 GB streamed per step); no explicit flush'}
+    if chunk is not None:
+        cfg['arena_chunk_images'] = chunk
+    return cfg
+
+
+# --------------------------------------------------------------------------------------------------
+# the B200 arm
+# --------------------------------------------------------------------------------------------------
+def run_b200_arm(a):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    rank = int(os.environ.get('RANK', '0'))
+    local_rank = int(os.environ.get('LOCAL_RANK', '0'))
+    if not torch.cuda.is_available():
+        raise SystemExit('bench.py: no CUDA device — the sm_100a library is the only implementation '
+                         '(use --impl reference for the CPU restatement)')
+    if world != a.gpus:
+        if world == 1 and a.gpus > 1:
+            raise SystemExit(f'bench.py --gpus {a.gpus}: launch with torchrun --nproc-per-node {a.gpus} '
+                             '(one rank per GPU)')
+        a.gpus = world
+    torch.cuda.set_device(local_rank)
+    dev = torch.device('cuda', local_rank)
+    if world > 1:
+        os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
+        dist.init_process_group('nccl', device_id=dev)
+
+    import __graft_entry__ as G
+    if not os.path.exists(G.LIB):
+        G.build()
+    import cnn_itmo_b200 as M
+    from cnn_itmo_b200.model import pinned_empty
+
+    peaks = measured_peaks()
+    ws = M.initial_weights(seed=218)
+    model = M.Model(ws, precision=a.precision, device=local_rank, max_batch=a.chunk)
+    B = a.batch
+    g = torch.Generator(device=dev).manual_seed(1234 + rank)
+    x = torch.randint(0, 256, (B, IMG, IMG, 3), dtype=torch.uint8, device=dev, generator=g)
+    y = torch.empty_like(x)
+    stream = torch.cuda.current_stream()
+
+    def step():
+        model.forward_device(x.data_ptr(), 'u8', y.data_ptr(), 'u8', B, stream=stream.cuda_stream)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+
+    for _ in range(max(a.warmup, 3) if a.warmup else 0):
+        step()
+    barrier()
+    model.set_profiling(True)
+    model.layer_times(reset=True)
+    launches0 = model.launch_count()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    ev0.record(stream)
+    for _ in range(a.steps):
+        step()
+    ev1.record(stream)
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    ms_total = ev0.elapsed_time(ev1)
+    launches = model.launch_count() - launches0
+    layer_times = model.layer_times(reset=True)
+    model.set_profiling(False)
+    if world > 1:
+        t = torch.tensor([ms_total], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_total = float(t.item())
+    ms_step = ms_total / a.steps
+    value = world * B * a.steps / (ms_total / 1e3)
+
+    # sanity: the timed work really produced images (not NaN / constant)
+    probe = y[0, ::64, ::64].float()
+    if not bool(torch.isfinite(probe).all()):
+        raise SystemExit('bench.py: non-finite output')
+
+    # ---- end to end: pinned host uint8 -> predict_u8 -> pinned host uint8 --------------------------
+    hx = pinned_empty((B, IMG, IMG, 3), np.uint8)
+    hy = pinned_empty((B, IMG, IMG, 3), np.uint8)
+    hx[...] = x.cpu().numpy()
+    model.predict_u8(hx, out=hy)  # warm-up (allocates the device staging buffers)
+    e2e_steps = max(1, min(a.steps, 5))
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        model.predict_u8(hx, out=hy)
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    if world > 1:
+        t = torch.tensor([dt], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dt = float(t.item())
+    e2e_value = world * B * e2e_steps / dt
+    same = bool((torch.from_numpy(np.asarray(hy[:2])).to(dev) == y[:2]).all())
+    if not same:
+        raise SystemExit('bench.py: host path and device path disagree')
+
+    # ---- roofline of the dominant kernel (conv_igemm_kernel), from the events of the timed region ---
+    from cnn_itmo_b200 import graph
+    per_layer = []
+    igemm_flops = igemm_ms = 0.0
+    for l in graph.LAYERS:
+        ms, calls = layer_times[l.index]
+        ks = graph.kernel_shape(l)
+        if l.kind == 'convT':
+            fl = 2.0 * (2 * l.hin) ** 2 * ks[2] * ks[3]
+        else:
+            fl = 2.0 * l.hin ** 2 * ks[0] * ks[1] * ks[2] * ks[3]
+        if l.index == 17:
+            fl += 2.0 * IMG * IMG * 64 * 3  # fused 1x1 head
+        if l.kind == 'head':
+            continue
+        ms_per_step = ms / a.steps
+        tf = fl * B / (ms_per_step * 1e-3) / 1e12 if ms_per_step > 0 else 0.0
+        per_layer.append({'layer': l.name, 'ms_per_step': round(ms_per_step, 4), 'tflops': round(tf, 1),
+                          'launches_per_step': calls / a.steps})
+        if l.index != 0:
+            igemm_flops += fl * B
+            igemm_ms += ms_per_step
+    n_igemm = sum(int(p['launches_per_step']) for p in per_layer[1:])
+    achieved = igemm_flops / (igemm_ms * 1e-3) / 1e12 if igemm_ms > 0 else 0.0
+    peak = peaks['tflops_sustained']
+    roofline = {'bound': 'tensor', 'kernel': 'itmo::conv_igemm_kernel', 'achieved': round(achieved, 2),
+                'peak': peak, 'unit': 'TFLOP/s', 'frac': round(achieved / peak, 4), 'traffic': None,
+                'peak_source': f"{peaks['source']} (bf16 sustained; kernel timed inside a long step)",
+                'flops_per_launch': igemm_flops / max(1, n_igemm),
+                'avg_launch_ms': round(igemm_ms / max(1, n_igemm), 4),
+                'share_of_step': round(igemm_ms / ms_step, 4)}
+
+    if rank == 0:
+        log('per-layer (rank 0, CUDA events inside the timed region):')
+        for p in per_layer:
+            log(f"  {p['layer']:<22} {p['ms_per_step']:9.3f} ms/step  {p['tflops']:8.1f} TFLOP/s")
+        log(f'  sum of layers {sum(p["ms_per_step"] for p in per_layer):.3f} ms, step {ms_step:.3f} ms')
+        os.makedirs(os.path.join(ROOT, 'gpurun_out'), exist_ok=True)
+        with open(os.path.join(ROOT, 'gpurun_out', f'bench_layers_{a.precision}_n{world}.json'), 'w') as f:
+            json.dump({'batch': B, 'chunk': a.chunk, 'precision': a.precision, 'ms_per_step': ms_step,
+                       'layers': per_layer}, f, indent=1)
+
+    cpu_baseline = None
+    if rank == 0 and world == 1 and not a.no_cpu:
+        ips, n, cores, secs = cpu_reference_time(ws, a.cpu_sample, budget_s=a.cpu_budget)
+        cpu_baseline = {'value': round(ips, 4), 'unit': UNIT, 'cores': cores, 'kind': 'port',
+                        'sample': f'{n} of the {B} images, one image per predict call (predict.py:50-62), torch-CPU '
+                                  f'fp32 restatement of model.py:204-278, {secs:.1f} s; TensorFlow-CPU unavailable '
+                                  'on this box'}
+
+    if rank == 0:
+        line = {
+            'metric': METRIC, 'value': round(value, 2), 'unit': UNIT, 'n_gpus': world, 'steps': a.steps,
+            'warmup': max(a.warmup, 3) if a.warmup else 0, 'ms_per_step': round(ms_step, 3),
+            'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
+            'dtype': 'bf16' if a.precision == 'bf16' else 'tf32', 'data': 'synthetic',
+            'mpix_per_s': round(value * MPIX_PER_IMAGE, 2),
+            'tflops_per_gpu': round(value / world * graph.forward_flops_per_image() / 1e12, 2),
+            'config': workload_config(a, a.chunk),
+            'clocks': clocks,
+            'e2e': {'value': round(e2e_value, 2), 'unit': UNIT, 'h2d_bytes_per_step': int(hx.nbytes),
+                    'd2h_bytes_per_step': int(hy.nbytes), 'steps': e2e_steps,
+                    'api': 'Model.predict_u8 -> itmo_predict_host (pinned host buffers)'},
+            'gpu_launches': int(launches),
+            'roofline': roofline,
+            'cpu_baseline': cpu_baseline,
+        }
+        print(json.dumps(line), flush=True)
+    model.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+def main(argv=None) -> int:
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=5)
+    ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
+    ap.add_argument('--batch', type=int, default=256, help='images per GPU per step (BASELINE configs[2]: 256)')
+    ap.add_argument('--chunk', type=int, default=int(os.environ.get('ITMO_BENCH_CHUNK', '64')),
+                    help='images the activation arena holds (itmo_create max_batch)')
+    ap.add_argument('--precision', default='bf16', choices=['bf16', 'tf32'])
+    ap.add_argument('--cpu-sample', type=int, default=4, help='images per step of the CPU restatement')
+    ap.add_argument('--cpu-budget', type=float, default=15.0, help='seconds of CPU work for cpu_baseline')
+    ap.add_argument('--no-cpu', action='store_true', help='skip the cpu_baseline leg')
+    a = ap.parse_args(argv)
+    if a.impl == 'reference':
+        return run_reference_arm(a)
+    return run_b200_arm(a)
+
+
+if __name__ == '__main__':
+    sys.exit(main())

@@ -178,8 +178,10 @@ class Model:
                                          xf.shape[0], 0))
         return out
 
-    def predict_u8(self, images_u8) -> np.ndarray:
-        """predict.py:59-64 fused: raw uint8 [N,512,512,3] -> uint8 [N,512,512,3] = trunc(sigmoid(...)*255)."""
+    def predict_u8(self, images_u8, out: Optional[np.ndarray] = None) -> np.ndarray:
+        """predict.py:59-64 fused: raw uint8 [N,512,512,3] -> uint8 [N,512,512,3] = trunc(sigmoid(...)*255).
+        ``out`` (optional) is a caller-owned C-contiguous uint8 array of the same shape to write into — pass
+        ``pinned_empty`` buffers for both sides to keep the copies asynchronous and skip the per-call allocation."""
         x = self._check_input(images_u8)
         if x.dtype != np.uint8:
             raise ValueError('predict_u8() expects uint8 images')
@@ -187,7 +189,10 @@ class Model:
             return np.empty_like(x)
         lib = self._ensure_ctx()
         x = np.ascontiguousarray(x)
-        out = pinned_empty(x.shape, np.uint8)
+        if out is None:
+            out = pinned_empty(x.shape, np.uint8)
+        elif out.dtype != np.uint8 or out.shape != x.shape or not out.flags.c_contiguous:
+            raise ValueError('out must be a C-contiguous uint8 array with the input\'s shape')
         _lib.check(lib.itmo_predict_host(self._ctx, x.ctypes.data, _lib.DT_U8, out.ctypes.data, _lib.DT_U8,
                                          x.shape[0], 0))
         return out
