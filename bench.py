@@ -355,7 +355,7 @@ def run_b200_arm(a):
             'metric': METRIC, 'value': round(value, 2), 'unit': UNIT, 'n_gpus': world, 'steps': a.steps,
             'warmup': max(a.warmup, 3) if a.warmup else 0, 'ms_per_step': round(ms_step, 3),
             'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
-            'dtype': 'bf16' if a.precision == 'bf16' else 'tf32', 'data': 'synthetic',
+            'dtype': a.precision, 'data': 'synthetic',
             'mpix_per_s': round(value * MPIX_PER_IMAGE, 2),
             'tflops_per_gpu': round(value / world * graph.forward_flops_per_image() / 1e12, 2),
             'config': workload_config(a, a.chunk),
@@ -384,7 +384,7 @@ def main(argv=None) -> int:
     ap.add_argument('--batch', type=int, default=256, help='images per GPU per step (BASELINE configs[2]: 256)')
     ap.add_argument('--chunk', type=int, default=int(os.environ.get('ITMO_BENCH_CHUNK', '64')),
                     help='images the activation arena holds (itmo_create max_batch)')
-    ap.add_argument('--precision', default='bf16', choices=['bf16', 'tf32'])
+    ap.add_argument('--precision', default='bf16', choices=['bf16', 'fp16', 'tf32', 'fp32'])
     ap.add_argument('--cpu-sample', type=int, default=4, help='images per step of the CPU restatement')
     ap.add_argument('--cpu-budget', type=float, default=15.0, help='seconds of CPU work for cpu_baseline')
     ap.add_argument('--no-cpu', action='store_true', help='skip the cpu_baseline leg')

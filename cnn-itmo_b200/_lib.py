@@ -12,7 +12,7 @@ from ctypes import POINTER, c_char_p, c_float, c_int, c_longlong, c_size_t, c_ui
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, 'libitmo_b200.so')
 
-PREC_TF32, PREC_BF16 = 0, 1
+PREC_TF32, PREC_BF16, PREC_FP32, PREC_FP16 = 0, 1, 2, 3
 DT_U8, DT_F32 = 0, 1
 NUM_LAYERS = 19
 

@@ -5,49 +5,81 @@
 //   ConvBNTranspose (model.py:199-200)  = BN(ReLU(Conv2DTranspose(f, 2, strides=2)(x)))
 // plus the fusions the hot path needs around them:
 //   * concatenate([skip, up], axis=3) (model.py:246,251,256,261) folded into the operand loader:
-//     the K loop walks two NHWC source tensors through two TMA tensor maps, no concat buffer;
+//     the K loop walks a list of (source tensor, channel blocks) segments through TMA tensor maps,
+//     no concat buffer. The same mechanism carries the 3xTF32 split of the fp32 mode
+//     (x*w ~= x*w_hi + x*w_lo + x_lo*w_hi: three segments per source);
 //   * MaxPooling2D((2,2), strides=2) (model.py:210,215,220,227) fused into the epilogue
 //     (both the full-resolution skip tensor and the pooled tensor are written);
 //   * the 1x1 sigmoid head Conv2D(3, 1, activation='sigmoid') (model.py:276) and the
 //     uint8 truncation of predict.py:64 fused into the epilogue of the last 3x3 conv.
 //
-// GEMM view (per output tile):  D[128 pixels, BLOCK_N couts] = sum over (tap, cin-block) of
-//   A[128 pixels, BK cins] (an 8x16-pixel NHWC box shifted by the tap, TMA zero-fills the halo
-//   => 'same' padding for free) x B[BLOCK_N couts, BK cins] (pre-packed K-major weights).
-// Both operands land in shared memory in the canonical K-major swizzled layout via TMA, a single
-// thread issues tcgen05.mma with the fp32 accumulator in TMEM (double buffered so the epilogue of
-// tile i overlaps the main loop of tile i+1), four epilogue warps read TMEM with tcgen05.ld and
-// apply  y = max(acc + bias, 0) * bn_scale + bn_shift  (BN sits AFTER ReLU in the reference).
+// GEMM view. A CTA tile is 16 rows x (8*NM) columns of output pixels = NM "M blocks" of
+// 128 pixels (16 rows x 8 columns each, UMMA M = 128) that share every weight tile. For each
+// block of BK input channels ONE TMA box brings the (16+2) x (8*NM+2) pixel halo tile into
+// shared memory (TMA zero-fills outside the image => 'same' padding for free); the nine taps of
+// the 3x3 kernel are nine shared-memory descriptors into that one halo tile (start address
+// shifted by whole pixel rows, 8-pixel groups one halo row apart), so the activations cross
+// L2->SMEM ~1.3x instead of 9x. Weight tiles [BLOCK_N couts x BK cins] per (channel block, tap)
+// stream through their own ring, or — when the whole layer fits — are loaded once per CTA and
+// stay resident. A single thread issues tcgen05.mma with the fp32 accumulators in TMEM (double
+// buffered: the epilogue of tile i overlaps the main loop of tile i+1); eight epilogue warps
+// read TMEM with tcgen05.ld and apply  y = max(acc + bias, 0) * bn_scale + bn_shift
+// (BN sits AFTER ReLU in the reference, so it cannot be folded into the weights).
 #pragma once
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <stdio.h>
 #include "sm100_ptx.cuh"
 
 namespace itmo {
 
-constexpr int kTileH = 8;    // output tile: 8 rows x 16 cols = 128 pixels = UMMA M
-constexpr int kTileW = 16;
+constexpr int kBlkH = 16;    // M block: 16 rows x 8 cols = 128 pixels = UMMA M
+constexpr int kBlkW = 8;
 constexpr int kTileM = 128;
 constexpr int kMaxCout = 512;
+constexpr int kMaxSeg = 6;
+constexpr int kMaxAStages = 4;
+constexpr int kMaxBStages = 8;
+constexpr int kNumThreads = 384;       // warp 0 TMA, 1 MMA, 2 TMEM alloc, 3 idle, 4..11 epilogue
+constexpr int kNumEpiWarps = 8;
+constexpr int kSmemLimit = 227 * 1024;
+constexpr int kAuxBytes = 512 + 3 * kMaxCout * 4 + (3 * 64 + 4) * 4;
 
 enum ConvMode : int { kModeConv3x3 = 0, kModeConvT2x2 = 1 };
 enum HeadDtype : int { kHeadNone = 0, kHeadF32 = 1, kHeadU8 = 2 };
+// how fp32 results are stored (Elem = float): as computed, rounded to TF32 (so the tensor core's
+// operand truncation is a no-op and the error is unbiased), or split into a TF32 head + residual.
+enum StoreMode : int { kStorePlain = 0, kStoreTf32Rna = 1, kStoreSplit = 2 };
 
 struct ConvParams {
-  CUtensorMap tmA0;  // source 0 (skip / only source): dims (C0, W, H, N), box (BK, 16, 8, 1)
-  CUtensorMap tmA1;  // source 1 (upsampled) or a copy of tmA0 when unused
-  CUtensorMap tmB;   // packed weights: dims (Cin_total, rows, taps), box (BK, BLOCK_N, 1)
-  int H, W, NB;      // input spatial size and batch
-  int kb0, kb1;      // number of BK-wide channel blocks taken from source 0 / source 1
-  int taps;          // 9 for the 3x3 conv, 1 for the transposed conv
-  int n_tiles;       // weight rows / BLOCK_N
-  int cout;          // output channels (per 2x2 phase for the transposed conv)
-  int mode;          // ConvMode
+  CUtensorMap tmA[4];  // activation sources: dims (C, W, H, N), box (BK, 8*NM+2*pad, 16+2*pad, 1)
+  CUtensorMap tmB;     // packed weights: dims (K_total, rows, taps), box (BK, BLOCK_N, 1)
+  int H, W, NB;        // input spatial size and batch
+  int n_seg;           // K segments; segment s reads seg_kb[s] channel blocks from tmA[seg_map[s]]
+  int seg_map[kMaxSeg];
+  int seg_kb[kMaxSeg];
+  int taps;            // 9 for the 3x3 conv, 1 for the transposed conv
+  int pad;             // 1 for the 3x3 conv, 0 for the transposed conv
+  int nm;              // M blocks per CTA tile (1, 2 or 4)
+  int n_tiles;         // weight rows / BLOCK_N
+  int cout;            // output channels (per 2x2 phase for the transposed conv)
+  int mode;            // ConvMode
+  int a_stage_bytes;   // halo tile bytes rounded up to 1024
+  int n_a_stages, n_b_stages;
+  int b_resident;      // 1: all (channel block, tap) weight tiles are loaded once and kept in shared memory
+  int store_mode;      // StoreMode (Elem = float only)
+  int acc_split;       // S >= 1 TMEM accumulators per M block, summed in fp32 registers by the epilogue. The
+                       // tensor core adds into its fp32 accumulator with truncation, a bias that grows with the
+                       // number of chained MMAs; the fp32 mode spreads the x*w_hi products round-robin over S-1
+                       // accumulators and keeps the two small cross terms in the last one.
+  int kb_hi;           // channel blocks of the leading (x*w_hi) part; the rest go to accumulator S-1
   const float* bias;      // [cout]
   const float* bn_scale;  // [cout]  gamma / sqrt(var + eps)
   const float* bn_shift;  // [cout]  beta - mean * scale
-  void* out;              // NHWC activations (bf16 or fp32); may be null when the head is fused
+  void* out;              // NHWC activations; may be null when the head is fused
+  void* out_lo;           // kStoreSplit: residual tensor (or null)
   void* pooled;           // NHWC 2x2-max-pooled copy or null
+  void* pooled_lo;
   const float* head_w;    // [3][64] 1x1 head weights (row k = output channel k) or null
   const float* head_b;    // [3]
   void* head_out;         // [NB, H, W, 3] f32 or u8
@@ -62,51 +94,94 @@ struct ElemTraits<__nv_bfloat16> {
   static constexpr uint32_t kFmt = sm100::kFmtBF16;
 };
 template <>
+struct ElemTraits<__half> {
+  static constexpr bool kTF32 = false;
+  static constexpr uint32_t kFmt = sm100::kFmtF16;
+};
+template <>
 struct ElemTraits<float> {
   static constexpr bool kTF32 = true;
   static constexpr uint32_t kFmt = sm100::kFmtTF32;
 };
 
+// Pack two floats into a 16-bit pair (round-to-nearest-even), low half = a.
+template <typename Elem>
+__device__ __forceinline__ uint32_t pack2(float a, float b);
+template <>
+__device__ __forceinline__ uint32_t pack2<__nv_bfloat16>(float a, float b) {
+  __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+template <>
+__device__ __forceinline__ uint32_t pack2<__half>(float a, float b) {
+  // saturate instead of overflowing to inf: fp16 tops out at 65504
+  a = fminf(fmaxf(a, -65504.f), 65504.f);
+  b = fminf(fmaxf(b, -65504.f), 65504.f);
+  __half2 h = __floats2half2_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+__device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) { return pack2<__nv_bfloat16>(a, b); }
+
+template <typename Elem>
+__device__ __forceinline__ uint32_t max2(uint32_t a, uint32_t b);
+template <>
+__device__ __forceinline__ uint32_t max2<__nv_bfloat16>(uint32_t a, uint32_t b) {
+  __nv_bfloat162 r = __hmax2(*reinterpret_cast<__nv_bfloat162*>(&a), *reinterpret_cast<__nv_bfloat162*>(&b));
+  return *reinterpret_cast<uint32_t*>(&r);
+}
+template <>
+__device__ __forceinline__ uint32_t max2<__half>(uint32_t a, uint32_t b) {
+  __half2 r = __hmax2(*reinterpret_cast<__half2*>(&a), *reinterpret_cast<__half2*>(&b));
+  return *reinterpret_cast<uint32_t*>(&r);
+}
+
+__device__ __forceinline__ float tf32_rna(float v) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(v));
+  return __uint_as_float(r);
+}
+__device__ __forceinline__ float tf32_trunc(float v) { return __uint_as_float(__float_as_uint(v) & 0xFFFFE000u); }
+
+// fp32 vector store of 4 consecutive channels under a StoreMode
+__device__ __forceinline__ void store4_f32(float* dst, float* dst_lo, int mode, float a, float b, float c, float d) {
+  if (mode == kStoreTf32Rna) {
+    *reinterpret_cast<float4*>(dst) = make_float4(tf32_rna(a), tf32_rna(b), tf32_rna(c), tf32_rna(d));
+  } else {
+    *reinterpret_cast<float4*>(dst) = make_float4(a, b, c, d);
+    if (mode == kStoreSplit && dst_lo != nullptr)
+      *reinterpret_cast<float4*>(dst_lo) =
+          make_float4(a - tf32_trunc(a), b - tf32_trunc(b), c - tf32_trunc(c), d - tf32_trunc(d));
+  }
+}
+
 template <typename Elem, int BLOCK_N, int SWZ>
 struct ConvCfg {
   static constexpr int kBK = SWZ / int(sizeof(Elem));     // channels per K block
   static constexpr int kKSteps = SWZ / 32;                // one UMMA consumes 32 bytes of K
-  static constexpr int kABytes = kTileM * SWZ;
   static constexpr int kBBytes = BLOCK_N * SWZ;
-  static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kBudget = 196 * 1024;
-  static constexpr int kStagesRaw = kBudget / kStageBytes;
-  static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
-  static constexpr int kTmemCols = (2 * BLOCK_N) < 32 ? 32 : (2 * BLOCK_N);
-  // barriers + tmem ptr + epilogue params (bias, scale, shift) + head (3*64 + 4)
-  static constexpr int kAuxBytes = 512 + 3 * kMaxCout * 4 + (3 * 64 + 4) * 4;
-  static constexpr int kSmemBytes = 1024 /*align slack*/ + kStages * kStageBytes + kAuxBytes;
-  static_assert(kStages >= 2, "pipeline needs at least two stages");
-  static_assert((kTmemCols & (kTmemCols - 1)) == 0 && kTmemCols <= 512, "TMEM columns: power of two <= 512");
+  static constexpr int kChunk = 32;                       // accumulator columns per tcgen05.ld
 };
 
-// Pack two floats into a bf16x2 register (round-to-nearest-even), low half = a.
-__device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
-  __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
-  return *reinterpret_cast<uint32_t*>(&h);
-}
-
 template <typename Elem, int BLOCK_N, int SWZ>
-__global__ void __launch_bounds__(256, 1) conv_igemm_kernel(const __grid_constant__ ConvParams p) {
+__global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid_constant__ ConvParams p) {
   using Cfg = ConvCfg<Elem, BLOCK_N, SWZ>;
-  constexpr int kStages = Cfg::kStages;
   constexpr bool kTF32 = ElemTraits<Elem>::kTF32;
+  static_assert(BLOCK_N % 32 == 0 && BLOCK_N <= 256, "BLOCK_N: multiple of 32 up to 256");
 
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_addr = sm100::smem_u32(smem_raw);
   uint8_t* smem = smem_raw + (((raw_addr + 1023u) & ~1023u) - raw_addr);
 
-  uint8_t* smem_a = smem;                                   // kStages x [128 rows x SWZ bytes]
-  uint8_t* smem_b = smem + kStages * Cfg::kABytes;          // kStages x [BLOCK_N rows x SWZ bytes]
-  uint8_t* aux = smem + kStages * Cfg::kStageBytes;
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(aux);    // [kStages]
-  uint64_t* empty_bar = full_bar + kStages;                 // [kStages]
-  uint64_t* tmem_full_bar = empty_bar + kStages;            // [2]
+  const int nm = p.nm;
+  const int n_a = p.n_a_stages, n_b = p.n_b_stages;
+  uint8_t* smem_a = smem;                                   // n_a x halo tile
+  uint8_t* smem_b = smem + n_a * p.a_stage_bytes;           // n_b x [BLOCK_N rows x SWZ bytes]
+  uint8_t* aux = smem_b + n_b * Cfg::kBBytes;
+  uint64_t* a_full = reinterpret_cast<uint64_t*>(aux);      // [kMaxAStages]
+  uint64_t* a_empty = a_full + kMaxAStages;
+  uint64_t* b_full = a_empty + kMaxAStages;                 // [kMaxBStages]  (resident: b_full[0] only)
+  uint64_t* b_empty = b_full + kMaxBStages;
+  uint64_t* tmem_full_bar = b_empty + kMaxBStages;          // [2]
   uint64_t* tmem_empty_bar = tmem_full_bar + 2;             // [2]
   uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
   float* s_bias = reinterpret_cast<float*>(aux + 512);
@@ -117,31 +192,43 @@ __global__ void __launch_bounds__(256, 1) conv_igemm_kernel(const __grid_constan
   const int warp_idx = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
 
-  const int tiles_x = p.W / kTileW;
-  const int tiles_y = p.H / kTileH;
+  const int tile_w = kBlkW * nm;
+  const int tiles_x = p.W / tile_w;
+  const int tiles_y = p.H / kBlkH;
   const int m_tiles = p.NB * tiles_y * tiles_x;
   const int total_tiles = m_tiles * p.n_tiles;
-  const int k_iters = (p.kb0 + p.kb1) * p.taps;
+  int kb_total = 0;
+  for (int s = 0; s < p.n_seg; ++s) kb_total += p.seg_kb[s];
+  const int halo_w = tile_w + 2 * p.pad;                    // halo pitch in pixels
+  const int halo_h = kBlkH + 2 * p.pad;
+  const int S = p.acc_split;
+  const uint32_t buf_cols = uint32_t(S * nm * BLOCK_N);    // TMEM columns of one accumulator buffer
+  const uint32_t tmem_cols_used = 2 * buf_cols;
+  uint32_t tmem_cols = 32;
+  while (tmem_cols < tmem_cols_used) tmem_cols <<= 1;
 
   // ---------------------------------------------------------------- one-time setup
   if (warp_idx == 0 && lane == 0) {
-    sm100::tma_prefetch_desc(&p.tmA0);
-    sm100::tma_prefetch_desc(&p.tmA1);
+    for (int s = 0; s < 4; ++s) sm100::tma_prefetch_desc(&p.tmA[s]);
     sm100::tma_prefetch_desc(&p.tmB);
   }
   if (warp_idx == 1 && lane == 0) {
-    for (int i = 0; i < kStages; ++i) {
-      sm100::mbar_init(&full_bar[i], 1);
-      sm100::mbar_init(&empty_bar[i], 1);
+    for (int i = 0; i < kMaxAStages; ++i) {
+      sm100::mbar_init(&a_full[i], 1);
+      sm100::mbar_init(&a_empty[i], 1);
+    }
+    for (int i = 0; i < kMaxBStages; ++i) {
+      sm100::mbar_init(&b_full[i], 1);
+      sm100::mbar_init(&b_empty[i], 1);
     }
     for (int i = 0; i < 2; ++i) {
       sm100::mbar_init(&tmem_full_bar[i], 1);
-      sm100::mbar_init(&tmem_empty_bar[i], 4);  // one arrive per epilogue warp
+      sm100::mbar_init(&tmem_empty_bar[i], kNumEpiWarps);  // one arrive per epilogue warp
     }
     sm100::fence_barrier_init();
   }
   if (warp_idx == 2) {
-    sm100::tmem_alloc(tmem_ptr_smem, Cfg::kTmemCols);
+    sm100::tmem_alloc(tmem_ptr_smem, tmem_cols);
   }
   for (int i = threadIdx.x; i < p.cout; i += blockDim.x) {
     s_bias[i] = p.bias[i];
@@ -161,8 +248,17 @@ __global__ void __launch_bounds__(256, 1) conv_igemm_kernel(const __grid_constan
   if (warp_idx == 0) {
     // ===== TMA producer (one thread) =====
     if (lane == 0) {
-      int stage = 0;
-      uint32_t phase = 0;
+      const uint32_t a_bytes = uint32_t(SWZ) * halo_w * halo_h;
+      if (p.b_resident) {
+        // all weight tiles of the layer, once (n_tiles == 1 in this mode)
+        sm100::mbar_arrive_expect_tx(&b_full[0], uint32_t(kb_total * p.taps) * Cfg::kBBytes);
+        for (int kb = 0; kb < kb_total; ++kb)
+          for (int tap = 0; tap < p.taps; ++tap)
+            sm100::tma_load_3d(smem_b + (kb * p.taps + tap) * Cfg::kBBytes, &p.tmB, &b_full[0], kb * Cfg::kBK, 0, tap,
+                               sm100::kEvictLast);
+      }
+      int sa = 0, sb = 0;
+      uint32_t pa = 0, pb = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
         const int n_tile = tile % p.n_tiles;
         int m = tile / p.n_tiles;
@@ -170,23 +266,30 @@ __global__ void __launch_bounds__(256, 1) conv_igemm_kernel(const __grid_constan
         m /= tiles_x;
         const int ty = m % tiles_y;
         const int img = m / tiles_y;
-        const int x0 = tx * kTileW, y0 = ty * kTileH;
-        for (int kb = 0; kb < p.kb0 + p.kb1; ++kb) {
-          const bool second = kb >= p.kb0;
-          const CUtensorMap* tmA = second ? &p.tmA1 : &p.tmA0;
-          const int c_off = (second ? kb - p.kb0 : kb) * Cfg::kBK;
-          for (int tap = 0; tap < p.taps; ++tap) {
-            const int dy = (p.taps == 9) ? tap / 3 - 1 : 0;
-            const int dx = (p.taps == 9) ? tap % 3 - 1 : 0;
-            sm100::mbar_wait(&empty_bar[stage], phase ^ 1);
-            sm100::mbar_arrive_expect_tx(&full_bar[stage], Cfg::kStageBytes);
-            sm100::tma_load_4d(smem_a + stage * Cfg::kABytes, tmA, &full_bar[stage], c_off, x0 + dx, y0 + dy, img,
+        const int x0 = tx * tile_w - p.pad, y0 = ty * kBlkH - p.pad;
+        int kb_glob = 0;
+        for (int s = 0; s < p.n_seg; ++s) {
+          const CUtensorMap* tmA = &p.tmA[p.seg_map[s]];
+          for (int kb = 0; kb < p.seg_kb[s]; ++kb, ++kb_glob) {
+            sm100::mbar_wait(&a_empty[sa], pa ^ 1);
+            sm100::mbar_arrive_expect_tx(&a_full[sa], a_bytes);
+            sm100::tma_load_4d(smem_a + sa * p.a_stage_bytes, tmA, &a_full[sa], kb * Cfg::kBK, x0, y0, img,
                                sm100::kEvictNormal);
-            sm100::tma_load_3d(smem_b + stage * Cfg::kBBytes, &p.tmB, &full_bar[stage], kb * Cfg::kBK,
-                               n_tile * BLOCK_N, tap, sm100::kEvictLast);
-            if (++stage == kStages) {
-              stage = 0;
-              phase ^= 1;
+            if (++sa == n_a) {
+              sa = 0;
+              pa ^= 1;
+            }
+            if (!p.b_resident) {
+              for (int tap = 0; tap < p.taps; ++tap) {
+                sm100::mbar_wait(&b_empty[sb], pb ^ 1);
+                sm100::mbar_arrive_expect_tx(&b_full[sb], Cfg::kBBytes);
+                sm100::tma_load_3d(smem_b + sb * Cfg::kBBytes, &p.tmB, &b_full[sb], kb_glob * Cfg::kBK,
+                                   n_tile * BLOCK_N, tap, sm100::kEvictLast);
+                if (++sb == n_b) {
+                  sb = 0;
+                  pb ^= 1;
+                }
+              }
             }
           }
         }
@@ -196,41 +299,77 @@ __global__ void __launch_bounds__(256, 1) conv_igemm_kernel(const __grid_constan
     // ===== MMA issuer (one thread) =====
     if (lane == 0) {
       constexpr uint32_t idesc = sm100::make_idesc(ElemTraits<Elem>::kFmt, kTileM, BLOCK_N);
-      int stage = 0;
-      uint32_t phase = 0;
+      const uint32_t sbo = uint32_t(halo_w) * SWZ;          // 8-pixel groups are one halo row apart
+      int sa = 0, sb = 0;
+      uint32_t pa = 0, pb = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
+      if (p.b_resident) {
+        sm100::mbar_wait(&b_full[0], 0);
+        sm100::tc_fence_after_sync();
+      }
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
         sm100::mbar_wait(&tmem_empty_bar[acc], acc_phase ^ 1);
         sm100::tc_fence_after_sync();
-        const uint32_t tmem_d = tmem_base + acc * BLOCK_N;
-        for (int it = 0; it < k_iters; ++it) {
-          sm100::mbar_wait(&full_bar[stage], phase);
+        const uint32_t tmem_d = tmem_base + uint32_t(acc) * buf_cols;
+        uint32_t used = 0;   // accumulators that already hold a partial sum in this tile
+        int it_hi = 0;
+        for (int kb = 0; kb < kb_total; ++kb) {
+          sm100::mbar_wait(&a_full[sa], pa);
           sm100::tc_fence_after_sync();
-          const uint32_t a_addr = sm100::smem_u32(smem_a + stage * Cfg::kABytes);
-          const uint32_t b_addr = sm100::smem_u32(smem_b + stage * Cfg::kBBytes);
+          const uint32_t a_base = sm100::smem_u32(smem_a + sa * p.a_stage_bytes);
+          for (int tap = 0; tap < p.taps; ++tap) {
+            uint32_t b_addr;
+            if (p.b_resident) {
+              b_addr = sm100::smem_u32(smem_b + (kb * p.taps + tap) * Cfg::kBBytes);
+            } else {
+              sm100::mbar_wait(&b_full[sb], pb);
+              sm100::tc_fence_after_sync();
+              b_addr = sm100::smem_u32(smem_b + sb * Cfg::kBBytes);
+            }
+            const int ty_ = (p.taps == 9) ? tap / 3 : 0;    // halo row / column of the tap's first pixel
+            const int tx_ = (p.taps == 9) ? tap % 3 : 0;
+            const uint32_t a_tap = a_base + uint32_t(ty_ * halo_w + tx_) * SWZ;
+            const int sacc = S == 1 ? 0 : (kb < p.kb_hi ? (it_hi++ % (S - 1)) : S - 1);
+            const uint32_t have = (used >> sacc) & 1u;
+            used |= 1u << sacc;
+            for (int j = 0; j < nm; ++j) {
+              const uint32_t a_blk = a_tap + uint32_t(j * kBlkW) * SWZ;
 #pragma unroll
-          for (int k = 0; k < Cfg::kKSteps; ++k) {
-            const uint64_t da = sm100::make_smem_desc_kmajor<SWZ>(a_addr + k * 32);
-            const uint64_t db = sm100::make_smem_desc_kmajor<SWZ>(b_addr + k * 32);
-            sm100::umma_ss<kTF32>(tmem_d, da, db, idesc, (it | k) != 0 ? 1u : 0u);
+              for (int k = 0; k < Cfg::kKSteps; ++k) {
+                const uint64_t da = sm100::make_smem_desc_kmajor_sbo<SWZ>(a_blk + k * 32, sbo);
+                const uint64_t db = sm100::make_smem_desc_kmajor<SWZ>(b_addr + k * 32);
+                sm100::umma_ss<kTF32>(tmem_d + uint32_t((sacc * nm + j) * BLOCK_N), da, db, idesc, (have | k) != 0 ? 1u : 0u);
+              }
+            }
+            if (!p.b_resident) {
+              sm100::umma_commit(&b_empty[sb]);  // frees this weight stage once the MMAs retire
+              if (++sb == n_b) {
+                sb = 0;
+                pb ^= 1;
+              }
+            }
           }
-          sm100::umma_commit(&empty_bar[stage]);  // frees this smem stage once the MMAs retire
-          if (++stage == kStages) {
-            stage = 0;
-            phase ^= 1;
+          sm100::umma_commit(&a_empty[sa]);      // halo tile consumed by all taps
+          if (++sa == n_a) {
+            sa = 0;
+            pa ^= 1;
           }
         }
-        sm100::umma_commit(&tmem_full_bar[acc]);  // accumulator complete -> epilogue
+        sm100::umma_commit(&tmem_full_bar[acc]);  // accumulators complete -> epilogue
         acc ^= 1;
         if (acc == 0) acc_phase ^= 1;
       }
     }
   } else if (warp_idx >= 4) {
     // ===== epilogue warps: TMEM -> registers -> bias/ReLU/BN (-> pool / head) -> global =====
-    const int e = warp_idx - 4;             // TMEM lane quarter (warp_idx % 4)
-    const int r = 2 * e + (lane >> 4);      // pixel row inside the 8x16 tile
-    const int c = lane & 15;                // pixel column inside the tile
+    const int ew = warp_idx - 4;            // 0..7
+    const int q = warp_idx & 3;             // TMEM lane quarter this warp may read
+    const int ws = ew >> 2;                 // warp set 0 / 1: the two sets split the tile's work items
+    const int r = 4 * q + (lane >> 3);      // pixel row inside the 16x8 M block
+    const int c = lane & 7;                 // pixel column inside the M block
+    constexpr int kChunk = Cfg::kChunk;
+    constexpr int kChunksPerBlk = BLOCK_N / kChunk;
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
@@ -240,121 +379,136 @@ __global__ void __launch_bounds__(256, 1) conv_igemm_kernel(const __grid_constan
       m /= tiles_x;
       const int ty = m % tiles_y;
       const int img = m / tiles_y;
-      const int y = ty * kTileH + r, x = tx * kTileW + c;
+      const int y = ty * kBlkH + r;
 
       sm100::mbar_wait(&tmem_full_bar[acc], acc_phase);
       sm100::tc_fence_after_sync();
-      const uint32_t taddr = tmem_base + (uint32_t(32 * e) << 16) + acc * BLOCK_N;
+      const uint32_t taddr = tmem_base + (uint32_t(32 * q) << 16) + uint32_t(acc) * buf_cols;
 
-      float h0 = 0.f, h1 = 0.f, h2 = 0.f;
+      // the two warp sets split the tile: by M block when there are several, else by column chunk; a fused
+      // head needs every channel of a pixel in one thread, so a lone block then stays with set 0
+      const bool split_by_chunk = nm == 1 && kChunksPerBlk > 1 && p.head_dtype == kHeadNone;
+      for (int j = 0; j < nm; ++j) {
+        if (nm > 1 ? (j & 1) != ws : (!split_by_chunk && ws != 0)) continue;
+        const int x = tx * tile_w + j * kBlkW + c;
+        float h0 = 0.f, h1 = 0.f, h2 = 0.f;
 #pragma unroll 1
-      for (int chunk = 0; chunk < BLOCK_N / 16; ++chunk) {
-        uint32_t v[16];
-        sm100::tmem_ld_32x32b_x16(taddr + chunk * 16, v);
-        sm100::tmem_ld_wait();
-        const int n_glob = n_tile * BLOCK_N + chunk * 16;  // row of the packed weight matrix
-        int co0, oy, ox, Ho, Wo;
-        if (p.mode == kModeConvT2x2) {
-          const int ph = n_glob / p.cout;  // phase a*2+b of the 2x2 transposed kernel
-          co0 = n_glob - ph * p.cout;
-          oy = 2 * y + (ph >> 1);
-          ox = 2 * x + (ph & 1);
-          Ho = 2 * p.H;
-          Wo = 2 * p.W;
-        } else {
-          co0 = n_glob;
-          oy = y;
-          ox = x;
-          Ho = p.H;
-          Wo = p.W;
-        }
-        float f[16];
+        for (int chunk = 0; chunk < kChunksPerBlk; ++chunk) {
+          if (split_by_chunk && (chunk & 1) != ws) continue;
+          uint32_t v[kChunk];
+          sm100::tmem_ld_32x32b_x32(taddr + uint32_t(j * BLOCK_N + chunk * kChunk), v);
+          sm100::tmem_ld_wait();
+          for (int sa = 1; sa < S; ++sa) {  // split accumulators: sum the partial results in fp32 (rn)
+            uint32_t u[kChunk];
+            sm100::tmem_ld_32x32b_x32(taddr + uint32_t((sa * nm + j) * BLOCK_N + chunk * kChunk), u);
+            sm100::tmem_ld_wait();
 #pragma unroll
-        for (int j = 0; j < 16; ++j) {
-          const float a = __uint_as_float(v[j]) + s_bias[co0 + j];
-          f[j] = fmaf(fmaxf(a, 0.f), s_scale[co0 + j], s_shift[co0 + j]);
+            for (int i = 0; i < kChunk; ++i) v[i] = __float_as_uint(__uint_as_float(v[i]) + __uint_as_float(u[i]));
+          }
+          const int n_glob = n_tile * BLOCK_N + chunk * kChunk;  // row of the packed weight matrix
+          int co0, oy, ox, Ho, Wo;
+          if (p.mode == kModeConvT2x2) {
+            const int ph = n_glob / p.cout;  // phase a*2+b of the 2x2 transposed kernel
+            co0 = n_glob - ph * p.cout;
+            oy = 2 * y + (ph >> 1);
+            ox = 2 * x + (ph & 1);
+            Ho = 2 * p.H;
+            Wo = 2 * p.W;
+          } else {
+            co0 = n_glob;
+            oy = y;
+            ox = x;
+            Ho = p.H;
+            Wo = p.W;
+          }
+          float f[kChunk];
+#pragma unroll
+          for (int i = 0; i < kChunk; ++i) {
+            const float a = __uint_as_float(v[i]) + s_bias[co0 + i];
+            f[i] = fmaf(fmaxf(a, 0.f), s_scale[co0 + i], s_shift[co0 + i]);
+          }
+          if (p.head_dtype != kHeadNone) {
+#pragma unroll
+            for (int i = 0; i < kChunk; ++i) {
+              h0 = fmaf(f[i], s_head[0 * 64 + co0 + i], h0);
+              h1 = fmaf(f[i], s_head[1 * 64 + co0 + i], h1);
+              h2 = fmaf(f[i], s_head[2 * 64 + co0 + i], h2);
+            }
+          }
+          const size_t pix = (size_t(img) * Ho + oy) * Wo + ox;
+          const bool pool_writer = (lane & 9) == 0;          // even row, even column of the block
+          const size_t ppix = (size_t(img) * (p.H / 2) + (y >> 1)) * (p.W / 2) + (x >> 1);
+          if constexpr (sizeof(Elem) == 2) {
+            uint32_t pk[kChunk / 2];
+#pragma unroll
+            for (int i = 0; i < kChunk / 2; ++i) pk[i] = pack2<Elem>(f[2 * i], f[2 * i + 1]);
+            if (p.out != nullptr) {
+              uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<Elem*>(p.out) + pix * p.cout + co0);
+#pragma unroll
+              for (int i = 0; i < kChunk / 8; ++i) dst[i] = make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
+            }
+            if (p.pooled != nullptr) {
+#pragma unroll
+              for (int i = 0; i < kChunk / 2; ++i) {
+                pk[i] = max2<Elem>(pk[i], __shfl_xor_sync(0xFFFFFFFFu, pk[i], 1));   // horizontal neighbour
+                pk[i] = max2<Elem>(pk[i], __shfl_xor_sync(0xFFFFFFFFu, pk[i], 8));   // vertical neighbour
+              }
+              if (pool_writer) {
+                uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<Elem*>(p.pooled) + ppix * p.cout + co0);
+#pragma unroll
+                for (int i = 0; i < kChunk / 8; ++i)
+                  dst[i] = make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
+              }
+            }
+          } else {
+            if (p.out != nullptr) {
+              float* dst = reinterpret_cast<float*>(p.out) + pix * p.cout + co0;
+              float* dst_lo = p.out_lo ? reinterpret_cast<float*>(p.out_lo) + pix * p.cout + co0 : nullptr;
+#pragma unroll
+              for (int i = 0; i < kChunk / 4; ++i)
+                store4_f32(dst + 4 * i, dst_lo ? dst_lo + 4 * i : nullptr, p.store_mode, f[4 * i], f[4 * i + 1],
+                           f[4 * i + 2], f[4 * i + 3]);
+            }
+            if (p.pooled != nullptr) {
+#pragma unroll
+              for (int i = 0; i < kChunk; ++i) {
+                f[i] = fmaxf(f[i], __shfl_xor_sync(0xFFFFFFFFu, f[i], 1));
+                f[i] = fmaxf(f[i], __shfl_xor_sync(0xFFFFFFFFu, f[i], 8));
+              }
+              if (pool_writer) {
+                float* dst = reinterpret_cast<float*>(p.pooled) + ppix * p.cout + co0;
+                float* dst_lo = p.pooled_lo ? reinterpret_cast<float*>(p.pooled_lo) + ppix * p.cout + co0 : nullptr;
+#pragma unroll
+                for (int i = 0; i < kChunk / 4; ++i)
+                  store4_f32(dst + 4 * i, dst_lo ? dst_lo + 4 * i : nullptr, p.store_mode, f[4 * i], f[4 * i + 1],
+                             f[4 * i + 2], f[4 * i + 3]);
+              }
+            }
+          }
         }
         if (p.head_dtype != kHeadNone) {
-#pragma unroll
-          for (int j = 0; j < 16; ++j) {
-            h0 = fmaf(f[j], s_head[0 * 64 + co0 + j], h0);
-            h1 = fmaf(f[j], s_head[1 * 64 + co0 + j], h1);
-            h2 = fmaf(f[j], s_head[2 * 64 + co0 + j], h2);
-          }
-        }
-        const size_t pix = (size_t(img) * Ho + oy) * Wo + ox;
-        if constexpr (sizeof(Elem) == 2) {
-          uint32_t pk[8];
-#pragma unroll
-          for (int j = 0; j < 8; ++j) pk[j] = pack_bf16x2(f[2 * j], f[2 * j + 1]);
-          if (p.out != nullptr) {
-            uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.out) + pix * p.cout + co0);
-            dst[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-            dst[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
-          }
-          if (p.pooled != nullptr) {
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              __nv_bfloat162 a = *reinterpret_cast<__nv_bfloat162*>(&pk[j]);
-              uint32_t o = __shfl_xor_sync(0xFFFFFFFFu, pk[j], 1);
-              a = __hmax2(a, *reinterpret_cast<__nv_bfloat162*>(&o));
-              uint32_t au = *reinterpret_cast<uint32_t*>(&a);
-              o = __shfl_xor_sync(0xFFFFFFFFu, au, 16);
-              a = __hmax2(a, *reinterpret_cast<__nv_bfloat162*>(&o));
-              pk[j] = *reinterpret_cast<uint32_t*>(&a);
-            }
-            if ((lane & 17) == 0) {
-              const size_t ppix = (size_t(img) * (p.H / 2) + (y >> 1)) * (p.W / 2) + (x >> 1);
-              uint4* dst =
-                  reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.pooled) + ppix * p.cout + co0);
-              dst[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-              dst[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
-            }
-          }
-        } else {
-          if (p.out != nullptr) {
-            float4* dst = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + pix * p.cout + co0);
-#pragma unroll
-            for (int j = 0; j < 4; ++j) dst[j] = make_float4(f[4 * j], f[4 * j + 1], f[4 * j + 2], f[4 * j + 3]);
-          }
-          if (p.pooled != nullptr) {
-#pragma unroll
-            for (int j = 0; j < 16; ++j) {
-              f[j] = fmaxf(f[j], __shfl_xor_sync(0xFFFFFFFFu, f[j], 1));
-              f[j] = fmaxf(f[j], __shfl_xor_sync(0xFFFFFFFFu, f[j], 16));
-            }
-            if ((lane & 17) == 0) {
-              const size_t ppix = (size_t(img) * (p.H / 2) + (y >> 1)) * (p.W / 2) + (x >> 1);
-              float4* dst = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.pooled) + ppix * p.cout + co0);
-#pragma unroll
-              for (int j = 0; j < 4; ++j) dst[j] = make_float4(f[4 * j], f[4 * j + 1], f[4 * j + 2], f[4 * j + 3]);
-            }
+          // Conv2D(3, 1, activation='sigmoid') (model.py:276) on the post-BN fp32 values
+          const float z0 = h0 + s_head[192], z1 = h1 + s_head[193], z2 = h2 + s_head[194];
+          const float q0 = 1.f / (1.f + expf(-z0)), q1 = 1.f / (1.f + expf(-z1)), q2 = 1.f / (1.f + expf(-z2));
+          const size_t pix = (size_t(img) * p.H + y) * p.W + x;
+          if (p.head_dtype == kHeadF32) {
+            float* dst = reinterpret_cast<float*>(p.head_out) + pix * 3;
+            dst[0] = q0;
+            dst[1] = q1;
+            dst[2] = q2;
+          } else {
+            // predict.py:64  (pred * 255).astype('uint8')  -> fp32 multiply, truncation toward zero
+            uint8_t* dst = reinterpret_cast<uint8_t*>(p.head_out) + pix * 3;
+            dst[0] = static_cast<uint8_t>(static_cast<int>(q0 * 255.f));
+            dst[1] = static_cast<uint8_t>(static_cast<int>(q1 * 255.f));
+            dst[2] = static_cast<uint8_t>(static_cast<int>(q2 * 255.f));
           }
         }
       }
-      // accumulator drained: hand the TMEM buffer back to the MMA warp
+      // accumulators drained: hand the TMEM buffer back to the MMA warp
       sm100::tc_fence_before_sync();
       __syncwarp();
       if (lane == 0) sm100::mbar_arrive(&tmem_empty_bar[acc]);
-
-      if (p.head_dtype != kHeadNone) {
-        // Conv2D(3, 1, activation='sigmoid') (model.py:276) on the post-BN fp32 values
-        const float z0 = h0 + s_head[192], z1 = h1 + s_head[193], z2 = h2 + s_head[194];
-        const float q0 = 1.f / (1.f + expf(-z0)), q1 = 1.f / (1.f + expf(-z1)), q2 = 1.f / (1.f + expf(-z2));
-        const size_t pix = (size_t(img) * p.H + y) * p.W + x;
-        if (p.head_dtype == kHeadF32) {
-          float* dst = reinterpret_cast<float*>(p.head_out) + pix * 3;
-          dst[0] = q0;
-          dst[1] = q1;
-          dst[2] = q2;
-        } else {
-          // predict.py:64  (pred * 255).astype('uint8')  -> fp32 multiply, truncation toward zero
-          uint8_t* dst = reinterpret_cast<uint8_t*>(p.head_out) + pix * 3;
-          dst[0] = static_cast<uint8_t>(static_cast<int>(q0 * 255.f));
-          dst[1] = static_cast<uint8_t>(static_cast<int>(q1 * 255.f));
-          dst[2] = static_cast<uint8_t>(static_cast<int>(q2 * 255.f));
-        }
-      }
       acc ^= 1;
       if (acc == 0) acc_phase ^= 1;
     }
@@ -365,7 +519,7 @@ __global__ void __launch_bounds__(256, 1) conv_igemm_kernel(const __grid_constan
   __syncthreads();
   if (warp_idx == 2) {
     sm100::tc_fence_after_sync();
-    sm100::tmem_dealloc(tmem_base, Cfg::kTmemCols);
+    sm100::tmem_dealloc(tmem_base, tmem_cols);
   }
 }
 

@@ -10,6 +10,7 @@
 #include <algorithm>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <string>
@@ -77,7 +78,18 @@ const LayerDef kLayers[ITMO_NUM_LAYERS] = {
     {kHead, 64, 0, 3, 512, false, 17, -1, false},      // 18 conv2d_15  1x1 sigmoid
 };
 
-inline size_t elem_size(int precision) { return precision == ITMO_PREC_BF16 ? 2 : 4; }
+inline bool prec_valid(int p) {
+  return p == ITMO_PREC_TF32 || p == ITMO_PREC_BF16 || p == ITMO_PREC_FP32 || p == ITMO_PREC_FP16;
+}
+inline bool prec_is16(int p) { return p == ITMO_PREC_BF16 || p == ITMO_PREC_FP16; }
+inline size_t elem_size(int precision) { return prec_is16(precision) ? 2 : 4; }
+// K multiplier of the packed weights: the fp32 mode runs x*w as x*w_hi + x*w_lo + x_lo*w_hi (3xTF32)
+inline int k_mult(int precision) { return precision == ITMO_PREC_FP32 ? 3 : 1; }
+inline CUtensorMapDataType tm_dtype(int precision) {
+  return precision == ITMO_PREC_BF16   ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16
+         : precision == ITMO_PREC_FP16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16
+                                       : CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
+}
 
 // ------------------------------------------------------------------------------------------------
 // TMA tensor maps
@@ -99,16 +111,18 @@ CUtensorMapSwizzle swizzle_enum(int swz) {
   return swz == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : swz == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B;
 }
 
-// NHWC activation tensor [N,H,W,C] viewed as (C, W, H, N); box = (bk channels, 16, 8, 1).
-int make_act_map(CUtensorMap* m, const void* ptr, int precision, int C, int W, int H, int N, int swz) {
+// NHWC activation tensor [N,H,W,C] viewed as (C, W, H, N); box = (bk channels, box_w, box_h, 1): the halo tile
+// of one CTA tile. Out-of-bounds pixels are zero-filled ('same' padding).
+int make_act_map(CUtensorMap* m, const void* ptr, int precision, int C, int W, int H, int N, int swz, int box_w,
+                 int box_h) {
   auto enc = get_encode_fn();
   if (!enc) return fail(ITMO_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
   const size_t es = elem_size(precision);
   cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
   cuuint64_t strides[3] = {(cuuint64_t)C * es, (cuuint64_t)W * C * es, (cuuint64_t)H * W * C * es};
-  cuuint32_t box[4] = {(cuuint32_t)(swz / es), (cuuint32_t)itmo::kTileW, (cuuint32_t)itmo::kTileH, 1};
+  cuuint32_t box[4] = {(cuuint32_t)(swz / es), (cuuint32_t)box_w, (cuuint32_t)box_h, 1};
   cuuint32_t estr[4] = {1, 1, 1, 1};
-  CUresult r = enc(m, precision == ITMO_PREC_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32,
+  CUresult r = enc(m, tm_dtype(precision),
                    4, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                    swizzle_enum(swz), CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS)
@@ -127,7 +141,7 @@ int make_weight_map(CUtensorMap* m, const void* ptr, int precision, int cin_tota
   cuuint64_t strides[2] = {(cuuint64_t)cin_total * es, (cuuint64_t)rows * cin_total * es};
   cuuint32_t box[3] = {(cuuint32_t)(swz / es), (cuuint32_t)block_n, 1};
   cuuint32_t estr[3] = {1, 1, 1};
-  CUresult r = enc(m, precision == ITMO_PREC_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32,
+  CUresult r = enc(m, tm_dtype(precision),
                    3, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                    swizzle_enum(swz), CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS)
@@ -145,24 +159,54 @@ template <>
 __device__ __forceinline__ float to_elem<float>(float v) { return v; }
 template <>
 __device__ __forceinline__ __nv_bfloat16 to_elem<__nv_bfloat16>(float v) { return __float2bfloat16_rn(v); }
+template <>
+__device__ __forceinline__ __half to_elem<__half>(float v) { return __float2half_rn(fminf(fmaxf(v, -65504.f), 65504.f)); }
 
-// Keras Conv2D kernel [tap][cin][cout] (HWIO) -> K-major [tap][cout][cin]
+// fp32 weight element of K part `part` under the fp32-family modes:
+//   TF32: round to nearest TF32 (the tensor core would otherwise truncate: biased)
+//   FP32 (3xTF32): K is [w_hi | w_lo | w_hi], w_hi = trunc_tf32(w), w_lo = w - w_hi (exact)
+__device__ __forceinline__ float weight_part(float v, int precision, int part) {
+  if (precision == ITMO_PREC_TF32) return itmo::tf32_rna(v);
+  if (precision == ITMO_PREC_FP32) {
+    const float hi = itmo::tf32_trunc(v);
+    return part == 1 ? v - hi : hi;
+  }
+  return v;
+}
+
+// Keras Conv2D kernel [tap][cin][cout] (HWIO) -> K-major [tap][cout][kmult*cin]
 template <typename Elem>
 __global__ void pack_conv_weights_kernel(const float* __restrict__ src, Elem* __restrict__ dst, int taps, int cin,
-                                         int cout) {
-  const size_t total = size_t(taps) * cin * cout;
+                                         int cout, int precision, int kmult) {
+  const int ktot = kmult * cin;
+  const size_t total = size_t(taps) * ktot * cout;
   for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < total; i += size_t(gridDim.x) * blockDim.x) {
-    const int ci = int(i % cin);
-    const int co = int((i / cin) % cout);
-    const int tap = int(i / (size_t(cin) * cout));
-    dst[i] = to_elem<Elem>(src[(size_t(tap) * cin + ci) * cout + co]);
+    const int kk = int(i % ktot);
+    const int co = int((i / ktot) % cout);
+    const int tap = int(i / (size_t(ktot) * cout));
+    const int ci = kk % cin, part = kk / cin;
+    dst[i] = to_elem<Elem>(weight_part(src[(size_t(tap) * cin + ci) * cout + co], precision, part));
   }
 }
-// Keras Conv2DTranspose kernel [a][b][cout][cin] is already [(a*2+b)*cout + co][cin]: convert only
+// Keras Conv2DTranspose kernel [a][b][cout][cin] is already [(a*2+b)*cout + co][cin]: convert (and K-replicate)
 template <typename Elem>
-__global__ void convert_weights_kernel(const float* __restrict__ src, Elem* __restrict__ dst, size_t total) {
-  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < total; i += size_t(gridDim.x) * blockDim.x)
-    dst[i] = to_elem<Elem>(src[i]);
+__global__ void convert_weights_kernel(const float* __restrict__ src, Elem* __restrict__ dst, size_t rows, int cin,
+                                       int precision, int kmult) {
+  const int ktot = kmult * cin;
+  const size_t total = rows * ktot;
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < total; i += size_t(gridDim.x) * blockDim.x) {
+    const int kk = int(i % ktot);
+    const size_t row = i / ktot;
+    const int ci = kk % cin, part = kk / cin;
+    dst[i] = to_elem<Elem>(weight_part(src[row * cin + ci], precision, part));
+  }
+}
+// residual tensor of the fp32 mode: lo = x - trunc_tf32(x)
+__global__ void split_lo_kernel(const float* __restrict__ src, float* __restrict__ lo, size_t n) {
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n; i += size_t(gridDim.x) * blockDim.x) {
+    const float v = src[i];
+    lo[i] = v - itmo::tf32_trunc(v);
+  }
 }
 // BatchNormalization inference affine (Keras defaults, eps = 1e-3): s = g/sqrt(v+eps), t = b - m*s
 __global__ void bn_fold_kernel(const float* g, const float* b, const float* m, const float* v, float eps, int n,
@@ -184,7 +228,8 @@ __global__ void __launch_bounds__(256) conv3x3_rgb_kernel(const InT* __restrict_
                                                           const float* __restrict__ w_hwio,  // [27][32]
                                                           const float* __restrict__ bias,
                                                           const float* __restrict__ scale,
-                                                          const float* __restrict__ shift, int NB, int H, int W) {
+                                                          const float* __restrict__ shift, int NB, int H, int W,
+                                                          float* __restrict__ out_lo, int store_mode) {
   __shared__ float s_w[27 * 32];
   __shared__ float s_b[32], s_s[32], s_t[32];
   for (int i = threadIdx.x; i < 27 * 32; i += blockDim.x) s_w[i] = w_hwio[i];
@@ -235,20 +280,22 @@ __global__ void __launch_bounds__(256) conv3x3_rgb_kernel(const InT* __restrict_
 #pragma unroll
     for (int j = 0; j < 8; ++j) f[j] = fmaf(fmaxf(acc[j], 0.f), s_s[cg * 8 + j], s_t[cg * 8 + j]);
     if constexpr (sizeof(Elem) == 2) {
-      uint4 o = make_uint4(itmo::pack_bf16x2(f[0], f[1]), itmo::pack_bf16x2(f[2], f[3]), itmo::pack_bf16x2(f[4], f[5]),
-                           itmo::pack_bf16x2(f[6], f[7]));
+      uint4 o = make_uint4(itmo::pack2<Elem>(f[0], f[1]), itmo::pack2<Elem>(f[2], f[3]), itmo::pack2<Elem>(f[4], f[5]),
+                           itmo::pack2<Elem>(f[6], f[7]));
       *reinterpret_cast<uint4*>(out + pix * 32 + cg * 8) = o;
     } else {
-      float4* dst = reinterpret_cast<float4*>(out + pix * 32 + cg * 8);
-      dst[0] = make_float4(f[0], f[1], f[2], f[3]);
-      dst[1] = make_float4(f[4], f[5], f[6], f[7]);
+      float* dst = out + pix * 32 + cg * 8;
+      float* dst_lo = out_lo ? out_lo + pix * 32 + cg * 8 : nullptr;
+      itmo::store4_f32(dst, dst_lo, store_mode, f[0], f[1], f[2], f[3]);
+      itmo::store4_f32(dst + 4, dst_lo ? dst_lo + 4 : nullptr, store_mode, f[4], f[5], f[6], f[7]);
     }
   }
 }
 
-__global__ void bf16_to_f32_kernel(const __nv_bfloat16* __restrict__ src, float* __restrict__ dst, size_t n) {
+template <typename Elem>
+__global__ void half_to_f32_kernel(const Elem* __restrict__ src, float* __restrict__ dst, size_t n) {
   for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n; i += size_t(gridDim.x) * blockDim.x)
-    dst[i] = __bfloat162float(src[i]);
+    dst[i] = float(src[i]);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -266,27 +313,26 @@ int num_sms() {
 }
 
 template <typename Elem, int BLOCK_N, int SWZ>
-int launch_conv_t(const itmo::ConvParams& p, int total_tiles, cudaStream_t stream) {
-  using Cfg = itmo::ConvCfg<Elem, BLOCK_N, SWZ>;
+int launch_conv_t(const itmo::ConvParams& p, int total_tiles, int smem_bytes, cudaStream_t stream) {
   auto kern = itmo::conv_igemm_kernel<Elem, BLOCK_N, SWZ>;
   static bool configured = false;  // per template instantiation
   if (!configured) {
-    ITMO_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+    ITMO_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, itmo::kSmemLimit));
     configured = true;
   }
   const int grid = std::min(total_tiles, num_sms());
-  kern<<<grid, 256, Cfg::kSmemBytes, stream>>>(p);
+  kern<<<grid, itmo::kNumThreads, smem_bytes, stream>>>(p);
   ITMO_CUDA(cudaGetLastError());
   return ITMO_OK;
 }
 
 template <typename Elem, int SWZ>
-int launch_conv_n(int block_n, const itmo::ConvParams& p, int total_tiles, cudaStream_t stream) {
+int launch_conv_n(int block_n, const itmo::ConvParams& p, int total_tiles, int smem_bytes, cudaStream_t stream) {
   switch (block_n) {
-    case 32: return launch_conv_t<Elem, 32, SWZ>(p, total_tiles, stream);
-    case 64: return launch_conv_t<Elem, 64, SWZ>(p, total_tiles, stream);
-    case 128: return launch_conv_t<Elem, 128, SWZ>(p, total_tiles, stream);
-    case 256: return launch_conv_t<Elem, 256, SWZ>(p, total_tiles, stream);
+    case 32: return launch_conv_t<Elem, 32, SWZ>(p, total_tiles, smem_bytes, stream);
+    case 64: return launch_conv_t<Elem, 64, SWZ>(p, total_tiles, smem_bytes, stream);
+    case 128: return launch_conv_t<Elem, 128, SWZ>(p, total_tiles, smem_bytes, stream);
+    case 256: return launch_conv_t<Elem, 256, SWZ>(p, total_tiles, smem_bytes, stream);
   }
   return fail(ITMO_ERR_INVALID, "unsupported BLOCK_N %d", block_n);
 }
@@ -298,128 +344,210 @@ struct ConvArgs {
   int c0;
   const void* src1;
   int c1;
+  const void* src0_lo;   // fp32 mode: residual tensors of the sources
+  const void* src1_lo;
   int n, h, w;           // input batch / spatial
-  const void* wpacked;   // [taps][rows][c0+c1] in the element type
+  const void* wpacked;   // [taps][rows][k_mult*(c0+c1)] in the element type
   const float *bias, *scale, *shift;
   int cout;
   void* out;
+  void* out_lo;
   void* pooled;
+  void* pooled_lo;
   const float* head_w;  // device [3][64] + bias [3] or null
   const float* head_b;
   void* head_out;
   int head_dtype;  // itmo::HeadDtype
 };
 
-// Validates shapes, builds tensor maps and launches the implicit-GEMM kernel.
+// Debug / tuning overrides (environment, read once): ITMO_FORCE_NM = 1|2|4, ITMO_NO_RESIDENT = 1
+int env_int(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return v && *v ? atoi(v) : dflt;
+}
+
+// Validates shapes, plans the tile / pipeline, builds tensor maps and launches the implicit-GEMM kernel.
 int run_conv(const ConvArgs& a, cudaStream_t stream) {
+  static const int force_nm = env_int("ITMO_FORCE_NM", 0);
+  static const int no_resident = env_int("ITMO_NO_RESIDENT", 0);
   const size_t es = elem_size(a.precision);
-  if (a.h % itmo::kTileH || a.w % itmo::kTileW)
-    return fail(ITMO_ERR_INVALID, "spatial size %dx%d must be a multiple of %dx%d", a.h, a.w, itmo::kTileH,
-                itmo::kTileW);
+  if (a.h % itmo::kBlkH || a.w % itmo::kBlkW)
+    return fail(ITMO_ERR_INVALID, "spatial size %dx%d must be a multiple of %dx%d", a.h, a.w, itmo::kBlkH,
+                itmo::kBlkW);
   if (a.n <= 0) return fail(ITMO_ERR_INVALID, "batch must be positive");
   const int cin = a.c0 + a.c1;
   const int full_bk = int(128 / es), half_bk = int(64 / es);
   int swz;
   if (a.c0 % full_bk == 0 && a.c1 % full_bk == 0) {
     swz = 128;
-  } else if (a.precision == ITMO_PREC_BF16 && a.c0 % half_bk == 0 && a.c1 % half_bk == 0) {
+  } else if (prec_is16(a.precision) && a.c0 % half_bk == 0 && a.c1 % half_bk == 0) {
     swz = 64;
   } else {
     return fail(ITMO_ERR_INVALID, "input channels (%d,%d) must be multiples of %d", a.c0, a.c1,
-                a.precision == ITMO_PREC_BF16 ? half_bk : full_bk);
+                prec_is16(a.precision) ? half_bk : full_bk);
   }
-  if (a.cout > itmo::kMaxCout || a.cout % 16) return fail(ITMO_ERR_INVALID, "cout %d unsupported", a.cout);
-  const int taps = a.mode == itmo::kModeConv3x3 ? 9 : 1;
-  const int rows = a.mode == itmo::kModeConv3x3 ? a.cout : 4 * a.cout;
-  int block_n = std::min(rows, 256);
+  if (a.cout > itmo::kMaxCout || a.cout % 32) return fail(ITMO_ERR_INVALID, "cout %d unsupported", a.cout);
+  const bool conv = a.mode == itmo::kModeConv3x3;
+  const int taps = conv ? 9 : 1;
+  const int pad = conv ? 1 : 0;
+  const int rows = conv ? a.cout : 4 * a.cout;
+  // fp32 mode: 4 split accumulators per M block (see ConvParams::acc_split) -> narrow N tiles, one M block
+  const int acc_split = a.precision == ITMO_PREC_FP32 ? 4 : 1;
+  int block_n = std::min(rows, acc_split > 1 ? 64 : 256);
   if (block_n != 32 && block_n != 64 && block_n != 128 && block_n != 256)
     return fail(ITMO_ERR_INVALID, "weight rows %d not tileable", rows);
   if (rows % block_n) return fail(ITMO_ERR_INVALID, "weight rows %d not a multiple of %d", rows, block_n);
-  if (a.pooled && a.mode != itmo::kModeConv3x3) return fail(ITMO_ERR_INVALID, "pool fusion only on conv3x3");
-  if (a.head_dtype != itmo::kHeadNone && (a.cout != 64 || block_n != 64 || a.mode != itmo::kModeConv3x3))
+  if (a.pooled && !conv) return fail(ITMO_ERR_INVALID, "pool fusion only on conv3x3");
+  if (a.head_dtype != itmo::kHeadNone && (a.cout != 64 || block_n != 64 || !conv))
     return fail(ITMO_ERR_INVALID, "head fusion needs cout == 64");
+  if (a.precision == ITMO_PREC_FP32 && (!a.src0_lo || (a.c1 > 0 && !a.src1_lo)))
+    return fail(ITMO_ERR_INVALID, "fp32 mode needs the residual tensors of its sources");
+
+  // ---- tile: NM M blocks of 16x8 pixels side by side share each weight tile; 2*NM*BLOCK_N TMEM columns
+  int nm = block_n >= 256 ? 1 : block_n == 128 ? 2 : 4;
+  if (acc_split > 1) nm = 1;
+  if (force_nm > 0) nm = std::min(force_nm, nm);
+  while (nm > 1 && a.w % (itmo::kBlkW * nm)) nm >>= 1;
+  const int bk = int(swz / es);
+  const int halo_w = itmo::kBlkW * nm + 2 * pad, halo_h = itmo::kBlkH + 2 * pad;
+  const int a_stage = (swz * halo_w * halo_h + 1023) / 1024 * 1024;
+  const int b_stage = block_n * swz;
+  const int kmult = k_mult(a.precision);
+  const int kb_total = kmult * cin / bk;
+  const int budget = itmo::kSmemLimit - 1024 - itmo::kAuxBytes;
+  const int n_tiles = rows / block_n;
+  int n_a, n_b, resident = 0;
+  if (!no_resident && n_tiles == 1 && kb_total * taps * b_stage + 2 * a_stage <= budget) {
+    resident = 1;
+    n_b = kb_total * taps;
+    n_a = std::min(itmo::kMaxAStages, (budget - n_b * b_stage) / a_stage);
+  } else {
+    n_a = 2;
+    n_b = std::min(itmo::kMaxBStages, (budget - n_a * a_stage) / b_stage);
+    if (n_b < 2) return fail(ITMO_ERR_INVALID, "tile does not fit in shared memory");
+    const int left = budget - n_a * a_stage - n_b * b_stage;
+    if (left >= a_stage) n_a = 3;
+  }
+  const int smem_bytes = 1024 + n_a * a_stage + n_b * b_stage + itmo::kAuxBytes;
 
   itmo::ConvParams p;
   memset(&p, 0, sizeof(p));
-  int rc = make_act_map(&p.tmA0, a.src0, a.precision, a.c0, a.w, a.h, a.n, swz);
-  if (rc) return rc;
-  if (a.c1 > 0) {
-    rc = make_act_map(&p.tmA1, a.src1, a.precision, a.c1, a.w, a.h, a.n, swz);
+  const void* srcs[4] = {a.src0, a.c1 > 0 ? a.src1 : a.src0, a.src0_lo ? a.src0_lo : a.src0,
+                         (a.c1 > 0 && a.src1_lo) ? a.src1_lo : a.src0};
+  const int chans[4] = {a.c0, a.c1 > 0 ? a.c1 : a.c0, a.c0, a.c1 > 0 ? a.c1 : a.c0};
+  for (int i = 0; i < 4; ++i) {
+    int rc = make_act_map(&p.tmA[i], srcs[i], a.precision, chans[i], a.w, a.h, a.n, swz, halo_w, halo_h);
     if (rc) return rc;
-  } else {
-    p.tmA1 = p.tmA0;
   }
-  rc = make_weight_map(&p.tmB, a.wpacked, a.precision, cin, rows, taps, block_n, swz);
+  int rc = make_weight_map(&p.tmB, a.wpacked, a.precision, kmult * cin, rows, taps, block_n, swz);
   if (rc) return rc;
-  const int bk = int(swz / es);
+  // K segments, in the order the weights are packed: [src0 | src1] x {w_hi, w_lo, (x_lo) w_hi}
+  int ns = 0;
+  for (int part = 0; part < kmult; ++part) {
+    p.seg_map[ns] = part == 2 ? 2 : 0;
+    p.seg_kb[ns++] = a.c0 / bk;
+    if (a.c1 > 0) {
+      p.seg_map[ns] = part == 2 ? 3 : 1;
+      p.seg_kb[ns++] = a.c1 / bk;
+    }
+  }
+  p.n_seg = ns;
   p.H = a.h;
   p.W = a.w;
   p.NB = a.n;
-  p.kb0 = a.c0 / bk;
-  p.kb1 = a.c1 / bk;
   p.taps = taps;
-  p.n_tiles = rows / block_n;
+  p.pad = pad;
+  p.nm = nm;
+  p.n_tiles = n_tiles;
   p.cout = a.cout;
   p.mode = a.mode;
+  p.a_stage_bytes = a_stage;
+  p.n_a_stages = n_a;
+  p.n_b_stages = n_b;
+  p.b_resident = resident;
+  p.acc_split = acc_split;
+  p.kb_hi = cin / bk;
+  p.store_mode = a.precision == ITMO_PREC_TF32   ? itmo::kStoreTf32Rna
+                 : a.precision == ITMO_PREC_FP32 ? itmo::kStoreSplit
+                                                 : itmo::kStorePlain;
   p.bias = a.bias;
   p.bn_scale = a.scale;
   p.bn_shift = a.shift;
   p.out = a.out;
+  p.out_lo = a.out_lo;
   p.pooled = a.pooled;
+  p.pooled_lo = a.pooled_lo;
   p.head_w = a.head_w;
   p.head_b = a.head_b;
   p.head_out = a.head_out;
   p.head_dtype = a.head_dtype;
-  const int total_tiles = a.n * (a.h / itmo::kTileH) * (a.w / itmo::kTileW) * p.n_tiles;
+  const int total_tiles = a.n * (a.h / itmo::kBlkH) * (a.w / (itmo::kBlkW * nm)) * n_tiles;
   if (a.precision == ITMO_PREC_BF16) {
-    if (swz == 128) return launch_conv_n<__nv_bfloat16, 128>(block_n, p, total_tiles, stream);
-    return launch_conv_n<__nv_bfloat16, 64>(block_n, p, total_tiles, stream);
+    if (swz == 128) return launch_conv_n<__nv_bfloat16, 128>(block_n, p, total_tiles, smem_bytes, stream);
+    return launch_conv_n<__nv_bfloat16, 64>(block_n, p, total_tiles, smem_bytes, stream);
   }
-  return launch_conv_n<float, 128>(block_n, p, total_tiles, stream);
+  if (a.precision == ITMO_PREC_FP16) {
+    if (swz == 128) return launch_conv_n<__half, 128>(block_n, p, total_tiles, smem_bytes, stream);
+    return launch_conv_n<__half, 64>(block_n, p, total_tiles, smem_bytes, stream);
+  }
+  return launch_conv_n<float, 128>(block_n, p, total_tiles, smem_bytes, stream);
 }
 
 int pack_weights(int precision, int mode, const float* src_dev, void* dst_dev, int cin, int cout,
                  cudaStream_t stream) {
-  if (mode == itmo::kModeConv3x3) {
-    const size_t total = size_t(9) * cin * cout;
-    const int grid = int(std::min<size_t>((total + 255) / 256, 4096));
+  const int km = k_mult(precision);
+  const bool conv = mode == itmo::kModeConv3x3;
+  const size_t total = size_t(conv ? 9 : 4) * km * cin * cout;
+  const int grid = int(std::min<size_t>((total + 255) / 256, 4096));
+  if (conv) {
     if (precision == ITMO_PREC_BF16)
-      pack_conv_weights_kernel<__nv_bfloat16><<<grid, 256, 0, stream>>>(src_dev, (__nv_bfloat16*)dst_dev, 9, cin, cout);
+      pack_conv_weights_kernel<__nv_bfloat16><<<grid, 256, 0, stream>>>(src_dev, (__nv_bfloat16*)dst_dev, 9, cin, cout,
+                                                                          precision, km);
+    else if (precision == ITMO_PREC_FP16)
+      pack_conv_weights_kernel<__half><<<grid, 256, 0, stream>>>(src_dev, (__half*)dst_dev, 9, cin, cout, precision, km);
     else
-      pack_conv_weights_kernel<float><<<grid, 256, 0, stream>>>(src_dev, (float*)dst_dev, 9, cin, cout);
+      pack_conv_weights_kernel<float><<<grid, 256, 0, stream>>>(src_dev, (float*)dst_dev, 9, cin, cout, precision, km);
   } else {
-    const size_t total = size_t(4) * cin * cout;
-    const int grid = int(std::min<size_t>((total + 255) / 256, 4096));
+    const size_t rows = size_t(4) * cout;
     if (precision == ITMO_PREC_BF16)
-      convert_weights_kernel<__nv_bfloat16><<<grid, 256, 0, stream>>>(src_dev, (__nv_bfloat16*)dst_dev, total);
+      convert_weights_kernel<__nv_bfloat16><<<grid, 256, 0, stream>>>(src_dev, (__nv_bfloat16*)dst_dev, rows, cin,
+                                                                        precision, km);
+    else if (precision == ITMO_PREC_FP16)
+      convert_weights_kernel<__half><<<grid, 256, 0, stream>>>(src_dev, (__half*)dst_dev, rows, cin, precision, km);
     else
-      convert_weights_kernel<float><<<grid, 256, 0, stream>>>(src_dev, (float*)dst_dev, total);
+      convert_weights_kernel<float><<<grid, 256, 0, stream>>>(src_dev, (float*)dst_dev, rows, cin, precision, km);
   }
+  ITMO_CUDA(cudaGetLastError());
+  return ITMO_OK;
+}
+
+template <typename Elem>
+int run_rgb_conv_t(const void* in, int in_dtype, int n, int h, int w, const float* w_hwio, const float* bias,
+                   const float* scale, const float* shift, void* out, void* out_lo, int store_mode, int grid,
+                   cudaStream_t stream) {
+  if (in_dtype == ITMO_DT_U8)
+    conv3x3_rgb_kernel<Elem, uint8_t><<<grid, 256, 0, stream>>>((const uint8_t*)in, (Elem*)out, w_hwio, bias, scale,
+                                                                  shift, n, h, w, (float*)out_lo, store_mode);
+  else
+    conv3x3_rgb_kernel<Elem, float><<<grid, 256, 0, stream>>>((const float*)in, (Elem*)out, w_hwio, bias, scale, shift,
+                                                                n, h, w, (float*)out_lo, store_mode);
   ITMO_CUDA(cudaGetLastError());
   return ITMO_OK;
 }
 
 int run_rgb_conv(int precision, const void* in, int in_dtype, int n, int h, int w, const float* w_hwio,
-                 const float* bias, const float* scale, const float* shift, void* out, cudaStream_t stream) {
+                 const float* bias, const float* scale, const float* shift, void* out, void* out_lo,
+                 cudaStream_t stream) {
   const size_t total = size_t(n) * h * w * 4;
   const int grid = int(std::min<size_t>((total + 255) / 256, size_t(num_sms()) * 16));
-  if (precision == ITMO_PREC_BF16) {
-    if (in_dtype == ITMO_DT_U8)
-      conv3x3_rgb_kernel<__nv_bfloat16, uint8_t><<<grid, 256, 0, stream>>>((const uint8_t*)in, (__nv_bfloat16*)out,
-                                                                             w_hwio, bias, scale, shift, n, h, w);
-    else
-      conv3x3_rgb_kernel<__nv_bfloat16, float><<<grid, 256, 0, stream>>>((const float*)in, (__nv_bfloat16*)out, w_hwio,
-                                                                           bias, scale, shift, n, h, w);
-  } else {
-    if (in_dtype == ITMO_DT_U8)
-      conv3x3_rgb_kernel<float, uint8_t><<<grid, 256, 0, stream>>>((const uint8_t*)in, (float*)out, w_hwio, bias, scale,
-                                                                     shift, n, h, w);
-    else
-      conv3x3_rgb_kernel<float, float><<<grid, 256, 0, stream>>>((const float*)in, (float*)out, w_hwio, bias, scale,
-                                                                   shift, n, h, w);
-  }
-  ITMO_CUDA(cudaGetLastError());
-  return ITMO_OK;
+  const int sm = precision == ITMO_PREC_TF32   ? itmo::kStoreTf32Rna
+                 : precision == ITMO_PREC_FP32 ? itmo::kStoreSplit
+                                               : itmo::kStorePlain;
+  if (precision == ITMO_PREC_BF16)
+    return run_rgb_conv_t<__nv_bfloat16>(in, in_dtype, n, h, w, w_hwio, bias, scale, shift, out, nullptr, sm, grid, stream);
+  if (precision == ITMO_PREC_FP16)
+    return run_rgb_conv_t<__half>(in, in_dtype, n, h, w, w_hwio, bias, scale, shift, out, nullptr, sm, grid, stream);
+  return run_rgb_conv_t<float>(in, in_dtype, n, h, w, w_hwio, bias, scale, shift, out, out_lo, sm, grid, stream);
 }
 
 // Keras head kernel [64][3] -> [3][64] (tiny, host side)
@@ -457,6 +585,8 @@ struct itmo_ctx {
   size_t arena_bytes = 0;
   void* act[ITMO_NUM_LAYERS] = {};     // layer outputs (layer 17/18 not materialised)
   void* pooled[ITMO_NUM_LAYERS] = {};  // pooled copies of layers 1,3,5,7
+  void* act_lo[ITMO_NUM_LAYERS] = {};     // fp32 mode: residual tensors (x - trunc_tf32(x))
+  void* pooled_lo[ITMO_NUM_LAYERS] = {};
   size_t act_elems_per_img[ITMO_NUM_LAYERS] = {};
   size_t pooled_elems_per_img[ITMO_NUM_LAYERS] = {};
 
@@ -519,7 +649,7 @@ int forward_chunk(itmo_ctx* ctx, const void* in_dev, int in_dtype, void* out_dev
     LayerStamp stamp(ctx, li, stream);
     if (L.kind == kRgbConv) {
       int rc = run_rgb_conv(prec, in_dev, in_dtype, nb, L.hin, L.hin, (const float*)ctx->wpacked[li], ctx->bias[li],
-                            ctx->scale[li], ctx->shift[li], ctx->act[li], stream);
+                            ctx->scale[li], ctx->shift[li], ctx->act[li], ctx->act_lo[li], stream);
       if (rc) return rc;
       ctx->launches++;
       continue;
@@ -532,6 +662,8 @@ int forward_chunk(itmo_ctx* ctx, const void* in_dev, int in_dtype, void* out_dev
     a.c0 = L.cin0;
     a.src1 = L.src1 >= 0 ? ctx->act[L.src1] : nullptr;
     a.c1 = L.cin1;
+    a.src0_lo = L.src0_pooled ? ctx->pooled_lo[L.src0] : ctx->act_lo[L.src0];
+    a.src1_lo = L.src1 >= 0 ? ctx->act_lo[L.src1] : nullptr;
     a.n = nb;
     a.h = L.hin;
     a.w = L.hin;
@@ -541,10 +673,13 @@ int forward_chunk(itmo_ctx* ctx, const void* in_dev, int in_dtype, void* out_dev
     a.shift = ctx->shift[li];
     a.cout = L.cout;
     a.out = ctx->act[li];
+    a.out_lo = ctx->act_lo[li];
     a.pooled = L.pool ? ctx->pooled[li] : nullptr;
+    a.pooled_lo = L.pool ? ctx->pooled_lo[li] : nullptr;
     a.head_dtype = itmo::kHeadNone;
     if (li == 17) {
       a.out = nullptr;  // conv2d_14's activation only feeds the head: never written to HBM
+      a.out_lo = nullptr;
       a.head_w = (const float*)ctx->wpacked[18];
       a.head_b = ctx->bias[18];
       a.head_out = out_dev;
@@ -568,7 +703,7 @@ int itmo_abi_version(void) { return 1; }
 int itmo_create(itmo_ctx** out, int device, int precision, int max_batch) {
   if (!out) return fail(ITMO_ERR_INVALID, "out is null");
   *out = nullptr;
-  if (precision != ITMO_PREC_TF32 && precision != ITMO_PREC_BF16) return fail(ITMO_ERR_INVALID, "bad precision");
+  if (!prec_valid(precision)) return fail(ITMO_ERR_INVALID, "bad precision");
   if (max_batch <= 0) return fail(ITMO_ERR_INVALID, "max_batch must be positive");
   ITMO_CUDA(cudaSetDevice(device));
   cudaDeviceProp prop;
@@ -588,8 +723,8 @@ int itmo_create(itmo_ctx** out, int device, int precision, int max_batch) {
     const int cin = L.cin0 + L.cin1;
     size_t wbytes;
     if (L.kind == kRgbConv) wbytes = size_t(27) * L.cout * 4;
-    else if (L.kind == kConv) wbytes = size_t(9) * cin * L.cout * es;
-    else if (L.kind == kConvT) wbytes = size_t(4) * cin * L.cout * es;
+    else if (L.kind == kConv) wbytes = size_t(9) * k_mult(precision) * cin * L.cout * es;
+    else if (L.kind == kConvT) wbytes = size_t(4) * k_mult(precision) * cin * L.cout * es;
     else wbytes = size_t(3) * 64 * 4;
     cudaError_t e = cudaMalloc(&ctx->wpacked[li], wbytes);
     if (e == cudaSuccess) e = cudaMalloc((void**)&ctx->bias[li], L.cout * 4);
@@ -603,19 +738,29 @@ int itmo_create(itmo_ctx** out, int device, int precision, int max_batch) {
   // arena: every activation gets its own slot (256-byte aligned) — the skip tensors stay live until
   // the decoder consumes them, so there is little to alias.
   size_t off = 0;
-  size_t offs_act[ITMO_NUM_LAYERS], offs_pool[ITMO_NUM_LAYERS];
+  size_t offs_act[ITMO_NUM_LAYERS], offs_pool[ITMO_NUM_LAYERS], offs_act_lo[ITMO_NUM_LAYERS],
+      offs_pool_lo[ITMO_NUM_LAYERS];
+  const bool split = precision == ITMO_PREC_FP32;
   for (int li = 0; li < ITMO_NUM_LAYERS; ++li) {
     const LayerDef& L = kLayers[li];
-    offs_act[li] = offs_pool[li] = size_t(-1);
+    offs_act[li] = offs_pool[li] = offs_act_lo[li] = offs_pool_lo[li] = size_t(-1);
     if (L.kind == kHead || li == 17) continue;
     const int ho = out_hw(L);
     ctx->act_elems_per_img[li] = size_t(ho) * ho * L.cout;
     offs_act[li] = off;
     off += (ctx->act_elems_per_img[li] * es * max_batch + 255) / 256 * 256;
+    if (split) {
+      offs_act_lo[li] = off;
+      off += (ctx->act_elems_per_img[li] * es * max_batch + 255) / 256 * 256;
+    }
     if (L.pool) {
       ctx->pooled_elems_per_img[li] = size_t(ho / 2) * (ho / 2) * L.cout;
       offs_pool[li] = off;
       off += (ctx->pooled_elems_per_img[li] * es * max_batch + 255) / 256 * 256;
+      if (split) {
+        offs_pool_lo[li] = off;
+        off += (ctx->pooled_elems_per_img[li] * es * max_batch + 255) / 256 * 256;
+      }
     }
   }
   ctx->arena_bytes = off;
@@ -627,6 +772,8 @@ int itmo_create(itmo_ctx** out, int device, int precision, int max_batch) {
   for (int li = 0; li < ITMO_NUM_LAYERS; ++li) {
     if (offs_act[li] != size_t(-1)) ctx->act[li] = (char*)ctx->arena + offs_act[li];
     if (offs_pool[li] != size_t(-1)) ctx->pooled[li] = (char*)ctx->arena + offs_pool[li];
+    if (offs_act_lo[li] != size_t(-1)) ctx->act_lo[li] = (char*)ctx->arena + offs_act_lo[li];
+    if (offs_pool_lo[li] != size_t(-1)) ctx->pooled_lo[li] = (char*)ctx->arena + offs_pool_lo[li];
   }
   e = cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking);
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->h2d_stream, cudaStreamNonBlocking);
@@ -879,12 +1026,13 @@ int itmo_read_activation(itmo_ctx* ctx, int layer, int which, float* dst_host, s
   if (n > cap_elems) return fail(ITMO_ERR_INVALID, "destination too small: need %zu elements", n);
   ITMO_CUDA(cudaSetDevice(ctx->device));
   ITMO_CUDA(cudaDeviceSynchronize());
-  if (ctx->precision == ITMO_PREC_TF32) {
+  if (!prec_is16(ctx->precision)) {
     ITMO_CUDA(cudaMemcpy(dst_host, src, n * 4, cudaMemcpyDeviceToHost));
   } else {
     float* tmp = nullptr;
     ITMO_CUDA(cudaMalloc((void**)&tmp, n * 4));
-    bf16_to_f32_kernel<<<1024, 256>>>((const __nv_bfloat16*)src, tmp, n);
+    if (ctx->precision == ITMO_PREC_BF16) half_to_f32_kernel<__nv_bfloat16><<<1024, 256>>>((const __nv_bfloat16*)src, tmp, n);
+    else half_to_f32_kernel<__half><<<1024, 256>>>((const __half*)src, tmp, n);
     cudaError_t e = cudaMemcpy(dst_host, tmp, n * 4, cudaMemcpyDeviceToHost);
     cudaFree(tmp);
     if (e != cudaSuccess) return fail(ITMO_ERR_CUDA, "readback failed: %s", cudaGetErrorString(e));
@@ -898,16 +1046,30 @@ static int stateless_conv(int precision, int mode, const void* src0, int c0, con
                           int w, const float* kernel, const float* bias, const float* scale, const float* shift,
                           int cout, void* out, void* pooled, const float* head_kernel, const float* head_bias,
                           void* head_out, int head_dtype, void* stream) {
-  if (precision != ITMO_PREC_TF32 && precision != ITMO_PREC_BF16) return fail(ITMO_ERR_INVALID, "bad precision");
+  if (!prec_valid(precision)) return fail(ITMO_ERR_INVALID, "bad precision");
   if (!src0 || !kernel || !bias || !scale || !shift) return fail(ITMO_ERR_INVALID, "null argument");
   if (c1 > 0 && !src1) return fail(ITMO_ERR_INVALID, "src1 is null but c1 > 0");
+  if (n <= 0 || h <= 0 || w <= 0 || c0 <= 0 || c1 < 0 || cout <= 0) return fail(ITMO_ERR_INVALID, "bad shape");
   cudaStream_t s = (cudaStream_t)stream;
   const int cin = c0 + c1;
-  const size_t wbytes = size_t(mode == itmo::kModeConv3x3 ? 9 : 4) * cin * cout * elem_size(precision);
+  const size_t wbytes =
+      size_t(mode == itmo::kModeConv3x3 ? 9 : 4) * k_mult(precision) * cin * cout * elem_size(precision);
   void* wp = nullptr;
   float* hw = nullptr;
+  float *lo0 = nullptr, *lo1 = nullptr;  // fp32 mode: residuals of the caller's sources, computed here
   ITMO_CUDA(cudaMallocAsync(&wp, wbytes, s));
   int rc = pack_weights(precision, mode, kernel, wp, cin, cout, s);
+  if (rc == ITMO_OK && precision == ITMO_PREC_FP32) {
+    const size_t n0 = size_t(n) * h * w * c0, n1 = size_t(n) * h * w * c1;
+    cudaError_t e = cudaMallocAsync((void**)&lo0, n0 * 4, s);
+    if (e == cudaSuccess && c1 > 0) e = cudaMallocAsync((void**)&lo1, n1 * 4, s);
+    if (e != cudaSuccess) {
+      rc = fail(ITMO_ERR_NOMEM, "cudaMallocAsync failed: %s", cudaGetErrorString(e));
+    } else {
+      split_lo_kernel<<<1024, 256, 0, s>>>((const float*)src0, lo0, n0);
+      if (c1 > 0) split_lo_kernel<<<1024, 256, 0, s>>>((const float*)src1, lo1, n1);
+    }
+  }
   if (rc == ITMO_OK && head_dtype != itmo::kHeadNone) {
     cudaError_t e = cudaMallocAsync((void**)&hw, 192 * 4, s);
     if (e != cudaSuccess) rc = fail(ITMO_ERR_NOMEM, "cudaMallocAsync failed: %s", cudaGetErrorString(e));
@@ -922,6 +1084,8 @@ static int stateless_conv(int precision, int mode, const void* src0, int c0, con
     a.c0 = c0;
     a.src1 = src1;
     a.c1 = c1;
+    a.src0_lo = lo0;
+    a.src1_lo = lo1;
     a.n = n;
     a.h = h;
     a.w = w;
@@ -940,6 +1104,8 @@ static int stateless_conv(int precision, int mode, const void* src0, int c0, con
   }
   cudaFreeAsync(wp, s);
   if (hw) cudaFreeAsync(hw, s);
+  if (lo0) cudaFreeAsync(lo0, s);
+  if (lo1) cudaFreeAsync(lo1, s);
   return rc;
 }
 
@@ -970,11 +1136,12 @@ int itmo_conv3x3_bn_head(int precision, const void* src0, int c0, const void* sr
 
 int itmo_conv3x3_bn_rgb(int precision, const void* in, int in_dtype, int n, int h, int w, const float* kernel_hwio,
                         const float* bias, const float* scale, const float* shift, int cout, void* out, void* stream) {
-  if (precision != ITMO_PREC_TF32 && precision != ITMO_PREC_BF16) return fail(ITMO_ERR_INVALID, "bad precision");
+  if (!prec_valid(precision)) return fail(ITMO_ERR_INVALID, "bad precision");
   if (!in || !kernel_hwio || !bias || !scale || !shift || !out) return fail(ITMO_ERR_INVALID, "null argument");
   if (cout != 32) return fail(ITMO_ERR_INVALID, "first layer has 32 output channels (model.py:208)");
   if (in_dtype != ITMO_DT_U8 && in_dtype != ITMO_DT_F32) return fail(ITMO_ERR_INVALID, "bad in_dtype");
-  return run_rgb_conv(precision, in, in_dtype, n, h, w, kernel_hwio, bias, scale, shift, out, (cudaStream_t)stream);
+  return run_rgb_conv(precision, in, in_dtype, n, h, w, kernel_hwio, bias, scale, shift, out, nullptr,
+                      (cudaStream_t)stream);
 }
 
 }  // extern "C"

@@ -174,6 +174,23 @@ __device__ __forceinline__ uint64_t make_smem_desc_kmajor(uint32_t smem_addr) {
   return d;
 }
 
+// Same layout, but with the 8-row groups `sbo_bytes` apart instead of densely packed. The conv kernel
+// points this at a halo tile whose rows are pixels: group g = 8 consecutive pixels of output row g, one
+// halo row (pitch * SWZ bytes) further down. The start address may be any multiple of SWZ bytes (a whole
+// pixel shift): the hardware swizzle is a function of the shared-memory address bits, exactly like the
+// TMA write that produced the tile, so shifted reads see consistent data.
+template <int SWZ>
+__device__ __forceinline__ uint64_t make_smem_desc_kmajor_sbo(uint32_t smem_addr, uint32_t sbo_bytes) {
+  constexpr uint64_t layout = (SWZ == 128) ? 2ull : (SWZ == 64) ? 4ull : 6ull;
+  uint64_t d = 0;
+  d |= static_cast<uint64_t>((smem_addr & 0x3FFFFu) >> 4);
+  d |= static_cast<uint64_t>(1) << 16;
+  d |= static_cast<uint64_t>((sbo_bytes >> 4) & 0x3FFFu) << 32;
+  d |= 1ull << 46;
+  d |= layout << 61;
+  return d;
+}
+
 enum : uint32_t { kFmtF16 = 0, kFmtBF16 = 1, kFmtTF32 = 2 };
 // Instruction descriptor for kind::f16 / kind::tf32 with fp32 accumulate, both operands K-major.
 //   [4,6) c_format=1 (F32)  [7,10) a_format  [10,13) b_format  [15] a_major=0  [16] b_major=0
@@ -223,6 +240,17 @@ __device__ __forceinline__ void tmem_ld_32x32b_x16(uint32_t taddr, uint32_t (&v)
       "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];\n"
       : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
         "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+      : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_ld_32x32b_x32(uint32_t taddr, uint32_t (&v)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32"
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
+        "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
+        "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
       : "r"(taddr));
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }

@@ -20,7 +20,10 @@ import numpy as np
 
 from . import _lib, checkpoint, graph
 
-_PRECISIONS = {'bf16': _lib.PREC_BF16, 'tf32': _lib.PREC_TF32, 'fp32': _lib.PREC_TF32}
+# bf16 / fp16: 16-bit activations in HBM, tcgen05 kind::f16 (same speed; fp16 carries 3 more mantissa bits)
+# tf32: fp32 activations rounded to TF32, tcgen05 kind::tf32
+# fp32: 3xTF32 (x*w_hi + x*w_lo + x_lo*w_hi) — fp32-accurate, the strict-parity mode
+_PRECISIONS = {'bf16': _lib.PREC_BF16, 'fp16': _lib.PREC_FP16, 'tf32': _lib.PREC_TF32, 'fp32': _lib.PREC_FP32}
 
 
 def _default_precision() -> str:
@@ -89,7 +92,7 @@ class Model:
         self.name = graph.MODEL_NAME
         self.input_shape = (None,) + tuple(input_size)
         self.output_shape = (None, graph.IMG, graph.IMG, 3)
-        self.precision = 'tf32' if precision == 'fp32' else precision
+        self.precision = precision
         self.device = int(device)
         self.max_batch = int(max_batch)
         self.bn_epsilon = float(bn_epsilon)

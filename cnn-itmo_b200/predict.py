@@ -75,7 +75,7 @@ def main(argv=None) -> int:
     ap.add_argument('--input-dir', default='images_to_predict/input')
     ap.add_argument('--output-dir', default='images_to_predict/output')
     ap.add_argument('--batch', type=int, default=1, help='images per predict call (reference: 1)')
-    ap.add_argument('--precision', default=None, choices=['bf16', 'tf32'])
+    ap.add_argument('--precision', default=None, choices=['bf16', 'fp16', 'tf32', 'fp32'])
     ap.add_argument('--device', type=int, default=0)
     ap.add_argument('--faithful', action='store_true', help='float predict() per image like predict.py:59-64')
     a = ap.parse_args(argv)

@@ -35,8 +35,12 @@ enum itmo_status {
 
 /* arithmetic mode of the tensor-core layers (fp32 accumulation in TMEM in both) */
 enum itmo_precision {
-  ITMO_PREC_TF32 = 0, /* fp32 activations in HBM, tcgen05 kind::tf32   (parity: max-abs <= 1e-3) */
-  ITMO_PREC_BF16 = 1  /* bf16 activations in HBM, tcgen05 kind::f16/bf16 (parity: PSNR >= 45 dB) */
+  ITMO_PREC_TF32 = 0, /* fp32 activations in HBM rounded to TF32 (rna), tcgen05 kind::tf32 */
+  ITMO_PREC_BF16 = 1, /* bf16 activations in HBM, tcgen05 kind::f16 (bf16 operands) */
+  ITMO_PREC_FP32 = 2, /* fp32 activations as TF32 head + residual, 3xTF32 products: x*w_hi + x*w_lo + x_lo*w_hi
+                         (fp32-accurate; parity: max-abs <= 1e-3 against the fp32 reference) */
+  ITMO_PREC_FP16 = 3  /* fp16 activations in HBM (saturating), tcgen05 kind::f16 (fp16 operands): same speed as
+                         bf16 with 3 more mantissa bits (parity: PSNR >= 45 dB) */
 };
 
 enum itmo_dtype { ITMO_DT_U8 = 0, ITMO_DT_F32 = 1 };

@@ -34,17 +34,37 @@ def dev():
     return torch.device('cuda:0')
 
 
+PRECS = ['fp32', 'tf32', 'fp16', 'bf16']
+
+
 def _quant(t, prec):
-    """Round a float32 CPU tensor to what the device stores / the tensor core reads."""
+    """Round a float32 CPU tensor to what the device stores / the tensor core reads (fp32 mode: nothing —
+    the 3xTF32 path consumes full fp32 values)."""
     if prec == 'bf16':
         return t.to(torch.bfloat16).float()
-    return (t.contiguous().view(torch.int32) & ~0x1FFF).view(torch.float32)
+    if prec == 'fp16':
+        return t.to(torch.float16).float()
+    if prec == 'tf32':
+        return (t.contiguous().view(torch.int32) & ~0x1FFF).view(torch.float32)
+    return t
+
+
+def _dt(prec):
+    return {'bf16': torch.bfloat16, 'fp16': torch.float16}.get(prec, torch.float32)
+
+
+def _P(L, prec):
+    return {'bf16': L.PREC_BF16, 'fp16': L.PREC_FP16, 'tf32': L.PREC_TF32, 'fp32': L.PREC_FP32}[prec]
 
 
 def _tol(ref, prec):
+    """Per-layer tolerance with operands the device represents exactly: what is left is the rounding of the
+    stored result (bf16 2^-9, fp16 / tf32 2^-11 relative) plus fp32 accumulation noise; fp32 mode stores fp32."""
     if prec == 'bf16':
         return (2.0 ** -8) * np.abs(ref) + 1e-2
-    return np.full_like(ref, 1e-3)
+    if prec in ('fp16', 'tf32'):
+        return (2.0 ** -10) * np.abs(ref) + 1e-3
+    return np.full_like(ref, 2e-4)
 
 
 # every 3x3 ConvBN shape of the graph: (hin, c0, c1, cout, pool)   (layers.txt:6-136; SURVEY 8a table)
@@ -82,7 +102,7 @@ def _oracle_block(kind, x_nhwc, k, bias, bn):
     return y
 
 
-@pytest.mark.parametrize('prec', ['tf32', 'bf16'])
+@pytest.mark.parametrize('prec', PRECS)
 @pytest.mark.parametrize('shape', CONV_SHAPES, ids=lambda s: f'{s[0]}x{s[1]}+{s[2]}to{s[3]}{"p" if s[4] else ""}')
 def test_conv3x3_bn_every_shape(dev, prec, shape):
     """BASELINE config 2: every ConvBN channel width at its native spatial size (batch 2 here; the oracle is
@@ -91,8 +111,7 @@ def test_conv3x3_bn_every_shape(dev, prec, shape):
     h, c0, c1, cout, pool = shape
     n = 2
     g = torch.Generator().manual_seed(h * 1000 + c0 + c1 + cout)
-    dt = torch.bfloat16 if prec == 'bf16' else torch.float32
-    P = L.PREC_BF16 if prec == 'bf16' else L.PREC_TF32
+    dt, P = _dt(prec), _P(L, prec)
     cin = c0 + c1
     x0 = _quant(torch.randn(n, h, h, c0, generator=g), prec)
     x1 = _quant(torch.randn(n, h, h, c1, generator=g), prec) if c1 else None
@@ -120,15 +139,14 @@ def test_conv3x3_bn_every_shape(dev, prec, shape):
         assert (np.abs(gp - ref_pool) <= _tol(ref_pool, prec)).all(), float(np.abs(gp - ref_pool).max())
 
 
-@pytest.mark.parametrize('prec', ['tf32', 'bf16'])
+@pytest.mark.parametrize('prec', PRECS)
 @pytest.mark.parametrize('shape', CONVT_SHAPES, ids=lambda s: f'{s[0]}x{s[1]}to{s[2]}')
 def test_convT2x2_bn_every_shape(dev, prec, shape):
     L, lib = _lib()
     h, cin, cout = shape
     n = 2
     g = torch.Generator().manual_seed(h * 77 + cin + cout)
-    dt = torch.bfloat16 if prec == 'bf16' else torch.float32
-    P = L.PREC_BF16 if prec == 'bf16' else L.PREC_TF32
+    dt, P = _dt(prec), _P(L, prec)
     x = _quant(torch.randn(n, h, h, cin, generator=g), prec)
     k = _quant(torch.randn(2, 2, cout, cin, generator=g) * (2.0 / (4 * cin)) ** 0.5, prec)
     bias = torch.rand(cout, generator=g) * 0.2 - 0.1
@@ -145,15 +163,14 @@ def test_convT2x2_bn_every_shape(dev, prec, shape):
     assert (np.abs(got - ref) <= _tol(ref, prec)).all(), float(np.abs(got - ref).max())
 
 
-@pytest.mark.parametrize('prec', ['tf32', 'bf16'])
+@pytest.mark.parametrize('prec', PRECS)
 @pytest.mark.parametrize('in_dtype', ['u8', 'f32'])
 def test_first_layer_from_raw_pixels(dev, prec, in_dtype):
     """conv2d_1 (3 -> 32, model.py:208) with the /255 of predict.py:59 fused into the load."""
     L, lib = _lib()
     n, h = 2, 512
     g = torch.Generator().manual_seed(11)
-    dt = torch.bfloat16 if prec == 'bf16' else torch.float32
-    P = L.PREC_BF16 if prec == 'bf16' else L.PREC_TF32
+    dt, P = _dt(prec), _P(L, prec)
     if in_dtype == 'u8':
         xin = torch.randint(0, 256, (n, h, h, 3), generator=g, dtype=torch.uint8)
         xf = torch.from_numpy(R.preprocess_u8(xin.numpy()))
@@ -172,18 +189,17 @@ def test_first_layer_from_raw_pixels(dev, prec, in_dtype):
                                     None))
     torch.cuda.synchronize()
     got = out.float().cpu().double().numpy()
-    tol = _tol(ref, prec) if prec == 'bf16' else np.full_like(ref, 1e-5)   # layer 0 is plain fp32 FMA
+    tol = np.full_like(ref, 1e-5) if prec == 'fp32' else _tol(ref, prec)   # layer 0 is plain fp32 FMA
     assert (np.abs(got - ref) <= tol).all(), float(np.abs(got - ref).max())
 
 
-@pytest.mark.parametrize('prec', ['tf32', 'bf16'])
+@pytest.mark.parametrize('prec', PRECS)
 def test_last_conv_with_fused_head(dev, prec):
     """conv2d_14 + Conv2D(3,1,sigmoid) (model.py:262,276) + the uint8 truncation of predict.py:64."""
     L, lib = _lib()
     n, h, c0, c1 = 1, 512, 32, 64
     g = torch.Generator().manual_seed(5)
-    dt = torch.bfloat16 if prec == 'bf16' else torch.float32
-    P = L.PREC_BF16 if prec == 'bf16' else L.PREC_TF32
+    dt, P = _dt(prec), _P(L, prec)
     x0 = _quant(torch.randn(n, h, h, c0, generator=g), prec)
     x1 = _quant(torch.randn(n, h, h, c1, generator=g), prec)
     k = _quant(torch.randn(3, 3, 96, 64, generator=g) * (2.0 / (9 * 96)) ** 0.5, prec)
@@ -204,7 +220,45 @@ def test_last_conv_with_fused_head(dev, prec):
                                          o.data_ptr(), odt, None))
     torch.cuda.synchronize()
     gf = of.cpu().double().numpy()
-    assert np.abs(gf - ref).max() <= 1e-4          # the head runs in fp32 on fp32 accumulators in both modes
+    assert np.abs(gf - ref).max() <= 1e-4          # the head runs in fp32 on fp32 accumulators in every mode
     want = R.postprocess_u8(ref.astype(np.float32)).astype(np.int32)
     du = np.abs(ou.cpu().numpy().astype(np.int32) - want)
     assert du.max() <= 1 and (du != 0).mean() < 1e-3
+
+
+# ragged / minimum tiles: one 16x8 M block, tiles narrower than the preferred 4-block width, odd tile counts
+SMALL_SHAPES = [(1, 16, 8, 64, 0, 64, False), (1, 16, 16, 32, 0, 32, True), (3, 16, 24, 64, 0, 128, False),
+                (1, 32, 8, 128, 0, 256, True), (2, 16, 40, 32, 64, 64, False), (1, 48, 16, 128, 256, 512, False)]
+
+
+@pytest.mark.parametrize('prec', PRECS)
+@pytest.mark.parametrize('shape', SMALL_SHAPES, ids=lambda s: 'x'.join(str(v) for v in s[:6]))
+def test_conv3x3_bn_small_and_ragged(dev, prec, shape):
+    L, lib = _lib()
+    n, h, w, c0, c1, cout, pool = shape
+    g = torch.Generator().manual_seed(h * 31 + w * 7 + c0 + c1 + cout)
+    dt, P = _dt(prec), _P(L, prec)
+    cin = c0 + c1
+    x0 = _quant(torch.randn(n, h, w, c0, generator=g), prec)
+    x1 = _quant(torch.randn(n, h, w, c1, generator=g), prec) if c1 else None
+    k = _quant(torch.randn(3, 3, cin, cout, generator=g) * (2.0 / (9 * cin)) ** 0.5, prec)
+    bias = torch.rand(cout, generator=g) * 0.2 - 0.1
+    bn, scale, shift = _bn_params(cout, g)
+    ref = _oracle_block('conv', torch.cat([x0, x1], 3) if c1 else x0, k, bias, bn)
+    ref_pool = torch.nn.functional.max_pool2d(ref, 2, 2).permute(0, 2, 3, 1).numpy() if pool else None
+    ref = ref.permute(0, 2, 3, 1).numpy()
+    d = lambda t: t.to(dev).contiguous()
+    x0d, x1d = d(x0.to(dt)), (d(x1.to(dt)) if c1 else None)
+    kd, bd, sd, td = d(k), d(bias), d(scale), d(shift)
+    out = torch.full((n, h, w, cout), float('nan'), dtype=dt, device=dev)
+    pooled = torch.full((n, h // 2, w // 2, cout), float('nan'), dtype=dt, device=dev) if pool else None
+    L.check(lib.itmo_conv3x3_bn(P, x0d.data_ptr(), c0, x1d.data_ptr() if c1 else None, c1, n, h, w, kd.data_ptr(),
+                                bd.data_ptr(), sd.data_ptr(), td.data_ptr(), cout, out.data_ptr(),
+                                pooled.data_ptr() if pool else None, None))
+    torch.cuda.synchronize()
+    got = out.float().cpu().double().numpy()
+    assert not np.isnan(got).any()
+    assert (np.abs(got - ref) <= _tol(ref, prec)).all(), float(np.abs(got - ref).max())
+    if pool:
+        gp = pooled.float().cpu().double().numpy()
+        assert (np.abs(gp - ref_pool) <= _tol(ref_pool, prec)).all(), float(np.abs(gp - ref_pool).max())

@@ -18,8 +18,8 @@ sys.path.insert(0, ROOT)
 CASES = []
 for prec in ('bf16', 'tf32'):
     CASES += [
-        (f'{prec}_tiny_center', prec, 'conv', 1, 8, 16, 64, 0, 64, False, 'center'),
-        (f'{prec}_tiny', prec, 'conv', 1, 8, 16, 64, 0, 64, False, 'rand'),
+        (f'{prec}_tiny_center', prec, 'conv', 1, 16, 16, 64, 0, 64, False, 'center'),
+        (f'{prec}_tiny', prec, 'conv', 1, 16, 16, 64, 0, 64, False, 'rand'),
         (f'{prec}_small_k2', prec, 'conv', 2, 16, 32, 128, 0, 128, False, 'rand'),
         (f'{prec}_small_pool', prec, 'conv', 2, 16, 32, 64, 0, 64, True, 'rand'),
         (f'{prec}_small_2src', prec, 'conv', 1, 16, 32, 64, 128, 128, False, 'rand'),
@@ -27,7 +27,7 @@ for prec in ('bf16', 'tf32'):
         (f'{prec}_small_n512', prec, 'conv', 1, 16, 16, 256, 0, 512, False, 'rand'),
         (f'{prec}_small_c32', prec, 'conv', 1, 16, 32, 32, 0, 32, True, 'rand'),
         (f'{prec}_small_c32_64', prec, 'conv', 1, 16, 32, 32, 64, 64, False, 'rand'),
-        (f'{prec}_convT_small', prec, 'convT', 1, 8, 16, 128, 0, 64, False, 'rand'),
+        (f'{prec}_convT_small', prec, 'convT', 1, 16, 16, 128, 0, 64, False, 'rand'),
         (f'{prec}_convT_512', prec, 'convT', 1, 16, 16, 512, 0, 512, False, 'rand'),
         (f'{prec}_head', prec, 'head', 1, 16, 32, 32, 64, 64, False, 'rand'),
         (f'{prec}_rgb_u8', prec, 'rgb', 2, 32, 32, 3, 0, 32, False, 'u8'),
