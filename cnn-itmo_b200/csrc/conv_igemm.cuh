@@ -72,6 +72,7 @@ struct ConvParams {
                        // tensor core adds into its fp32 accumulator with truncation, a bias that grows with the
                        // number of chained MMAs; the fp32 mode spreads the x*w_hi products round-robin over S-1
                        // accumulators and keeps the two small cross terms in the last one.
+  int dbg;             // timing experiments only (results wrong): 1 = 1024B-aligned A descriptors for every tap
   int kb_hi;           // channel blocks of the leading (x*w_hi) part; the rest go to accumulator S-1
   const float* bias;      // [cout]
   const float* bn_scale;  // [cout]  gamma / sqrt(var + eps)
@@ -299,7 +300,7 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
     // ===== MMA issuer (one thread) =====
     if (lane == 0) {
       constexpr uint32_t idesc = sm100::make_idesc(ElemTraits<Elem>::kFmt, kTileM, BLOCK_N);
-      const uint32_t sbo = uint32_t(halo_w) * SWZ;          // 8-pixel groups are one halo row apart
+      const uint32_t sbo = p.dbg == 2 ? 8u * SWZ : uint32_t(halo_w) * SWZ;  // 8-pixel groups are one halo row apart
       int sa = 0, sb = 0;
       uint32_t pa = 0, pb = 0;
       int acc = 0;
@@ -329,7 +330,9 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
             }
             const int ty_ = (p.taps == 9) ? tap / 3 : 0;    // halo row / column of the tap's first pixel
             const int tx_ = (p.taps == 9) ? tap % 3 : 0;
-            const uint32_t a_tap = a_base + uint32_t(ty_ * halo_w + tx_) * SWZ;
+            uint32_t a_tap = a_base + uint32_t(ty_ * halo_w + tx_) * SWZ;
+            if (p.dbg == 1) a_tap = a_base + uint32_t(ty_) * 1024u;
+            if (p.dbg == 2) a_tap = a_base;
             const int sacc = S == 1 ? 0 : (kb < p.kb_hi ? (it_hi++ % (S - 1)) : S - 1);
             const uint32_t have = (used >> sacc) & 1u;
             used |= 1u << sacc;
@@ -381,7 +384,8 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
       const int img = m / tiles_y;
       const int y = ty * kBlkH + r;
 
-      sm100::mbar_wait(&tmem_full_bar[acc], acc_phase);
+      if (p.dbg == 4) sm100::mbar_wait(&tmem_full_bar[acc], acc_phase);
+      else sm100::mbar_wait_relaxed(&tmem_full_bar[acc], acc_phase, 200);
       sm100::tc_fence_after_sync();
       const uint32_t taddr = tmem_base + (uint32_t(32 * q) << 16) + uint32_t(acc) * buf_cols;
 

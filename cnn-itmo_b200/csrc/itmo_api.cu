@@ -18,6 +18,7 @@
 
 #include "../../include/itmo_b200.h"
 #include "conv_igemm.cuh"
+#include "rgb_conv_tc.cuh"
 
 namespace {
 
@@ -465,6 +466,8 @@ int run_conv(const ConvArgs& a, cudaStream_t stream) {
   p.n_a_stages = n_a;
   p.n_b_stages = n_b;
   p.b_resident = resident;
+  static const int dbg = env_int("ITMO_DBG", 0);
+  p.dbg = dbg;
   p.acc_split = acc_split;
   p.kb_hi = cin / bk;
   p.store_mode = a.precision == ITMO_PREC_TF32   ? itmo::kStoreTf32Rna
@@ -535,9 +538,31 @@ int run_rgb_conv_t(const void* in, int in_dtype, int n, int h, int w, const floa
   return ITMO_OK;
 }
 
+template <typename Elem>
+int run_rgb_tc_t(const void* in, int in_dtype, int n, int h, int w, const float* w_hwio, const float* bias,
+                 const float* scale, const float* shift, void* out, cudaStream_t stream) {
+  const int tiles = n * (h / itmo::kRgbTileH) * (w / itmo::kRgbTileW);
+  const int grid = std::min(tiles, num_sms() * 8);
+  if (in_dtype == ITMO_DT_U8)
+    itmo::rgb_conv_tc_kernel<Elem, uint8_t><<<grid, 128, 0, stream>>>((const uint8_t*)in, (Elem*)out, w_hwio, bias,
+                                                                       scale, shift, n, h, w, 1.0f / 255.0f);
+  else
+    itmo::rgb_conv_tc_kernel<Elem, float><<<grid, 128, 0, stream>>>((const float*)in, (Elem*)out, w_hwio, bias, scale,
+                                                                     shift, n, h, w, 1.0f);
+  ITMO_CUDA(cudaGetLastError());
+  return ITMO_OK;
+}
+
 int run_rgb_conv(int precision, const void* in, int in_dtype, int n, int h, int w, const float* w_hwio,
                  const float* bias, const float* scale, const float* shift, void* out, void* out_lo,
                  cudaStream_t stream) {
+  static const int use_tc = env_int("ITMO_RGB_TC", 1);
+  if (use_tc && prec_is16(precision) && h % itmo::kRgbTileH == 0 && w % itmo::kRgbTileW == 0) {
+    // 16-bit modes: tensor-core im2col kernel (rgb_conv_tc.cuh)
+    if (precision == ITMO_PREC_BF16)
+      return run_rgb_tc_t<__nv_bfloat16>(in, in_dtype, n, h, w, w_hwio, bias, scale, shift, out, stream);
+    return run_rgb_tc_t<__half>(in, in_dtype, n, h, w, w_hwio, bias, scale, shift, out, stream);
+  }
   const size_t total = size_t(n) * h * w * 4;
   const int grid = int(std::min<size_t>((total + 255) / 256, size_t(num_sms()) * 16));
   const int sm = precision == ITMO_PREC_TF32   ? itmo::kStoreTf32Rna

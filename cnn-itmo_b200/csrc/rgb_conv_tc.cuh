@@ -1,0 +1,162 @@
+// rgb_conv_tc.cuh — the first ConvBN of the U-Net (conv2d_1, 3 -> 32 channels, model.py:208) on the
+// tensor cores, for the 16-bit modes.
+//
+// K = 3*3*3 = 27 is far too thin for the TMA-fed implicit GEMM (a 6-byte pixel is not a TMA box) and a
+// CUDA-core FMA loop needs 864 FMAs per pixel, ~8x over the layer's HBM time. Here the 128 threads of a
+// CTA build the im2col rows of a 4 x 32 pixel tile in shared memory themselves — one thread = one pixel =
+// one 128-byte K-major row of 64 elements in the SWIZZLE_128B layout tcgen05 reads — and one thread issues
+// four tcgen05.mma (M=128, N=32, K=16). The K axis is [27 taps, 5 zeros | the same 27 taps, 5 zeros] against
+// weight rows [w_hi | w_lo] (w_hi = the 16-bit rounding of w, w_lo = the rounding of the remainder), so the
+// weights enter with ~2x the significand of the storage type: this layer's rounding error would otherwise be
+// amplified by all 18 layers behind it. Raw uint8 pixels are exact in bf16 / fp16, so the operand is the
+// integer pixel value and the /255 of predict.py:59 is applied to the fp32 accumulator.
+// Epilogue: TMEM -> registers -> (+bias, ReLU, BN affine) -> 64 contiguous bytes per pixel, 2 KB per warp.
+// Several CTAs share an SM (23 KB of shared memory, 32 TMEM columns each) and hide each other's latencies.
+#pragma once
+#include "conv_igemm.cuh"
+
+namespace itmo {
+
+constexpr int kRgbTileH = 4, kRgbTileW = 32;    // 128 pixels = UMMA M
+constexpr int kRgbHaloH = kRgbTileH + 2, kRgbHaloW = kRgbTileW + 2;
+
+// in:  [NB,H,W,3] uint8 (raw pixels) or float (already /255); out: [NB,H,W,32] Elem
+// w_hwio: [27][32] fp32 (Keras HWIO flattened), in_scale: 1/255 for uint8 input, 1 for float input
+template <typename Elem, typename InT>
+__global__ void __launch_bounds__(128) rgb_conv_tc_kernel(const InT* __restrict__ in, Elem* __restrict__ out,
+                                                          const float* __restrict__ w_hwio,
+                                                          const float* __restrict__ bias,
+                                                          const float* __restrict__ scale,
+                                                          const float* __restrict__ shift, int NB, int H, int W,
+                                                          float in_scale) {
+  __shared__ __align__(1024) uint8_t s_a[128 * 128];  // im2col tile, 128 rows x 128 B, SWIZZLE_128B
+  __shared__ __align__(1024) uint8_t s_b[32 * 128];   // weights, 32 rows (cout) x 128 B (K), SWIZZLE_128B
+  __shared__ float s_halo[kRgbHaloH][kRgbHaloW * 3 + 2];
+  __shared__ float s_bias[32], s_scale[32], s_shift[32];
+  __shared__ __align__(8) uint64_t s_bar;
+  __shared__ uint32_t s_tmem;
+
+  const int tid = threadIdx.x;
+  const int warp = tid >> 5;
+
+  // ---- one-time setup: weights -> K-major swizzled B tile, epilogue vectors, barrier, TMEM
+  if (tid < 32) {
+    // row n = tid of B: B[n][k] = hi(w[k][n]) for k < 32, lo(w[k-32][n]) for k >= 32; taps >= 27 -> 0
+#pragma unroll
+    for (int c8 = 0; c8 < 8; ++c8) {
+      uint32_t pk[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int k0 = (c8 & 3) * 8 + 2 * i;
+        float a = k0 < 27 ? w_hwio[k0 * 32 + tid] : 0.f;
+        float b = k0 + 1 < 27 ? w_hwio[(k0 + 1) * 32 + tid] : 0.f;
+        if (c8 >= 4) {  // remainder after the 16-bit rounding
+          a -= float(Elem(a));
+          b -= float(Elem(b));
+        }
+        pk[i] = pack2<Elem>(a, b);
+      }
+      const int pos = c8 ^ (tid & 7);
+      *reinterpret_cast<uint4*>(s_b + tid * 128 + pos * 16) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+    }
+    s_bias[tid] = bias[tid];
+    s_scale[tid] = scale[tid];
+    s_shift[tid] = shift[tid];
+  }
+  if (tid == 0) {
+    sm100::mbar_init(&s_bar, 1);
+    sm100::fence_barrier_init();
+  }
+  if (warp == 1) sm100::tmem_alloc(&s_tmem, 32);
+  sm100::fence_proxy_async_smem();
+  sm100::tc_fence_before_sync();
+  __syncthreads();
+  sm100::tc_fence_after_sync();
+  const uint32_t tmem = s_tmem;
+
+  const int tiles_x = W / kRgbTileW, tiles_y = H / kRgbTileH;
+  const int total = NB * tiles_y * tiles_x;
+  const int r = tid >> 5, c = tid & 31;     // this thread's pixel inside the tile (M row = tid)
+  uint32_t phase = 0;
+  constexpr uint32_t idesc = sm100::make_idesc(ElemTraits<Elem>::kFmt, 128, 32);
+
+  for (int tile = blockIdx.x; tile < total; tile += gridDim.x) {
+    const int tx = tile % tiles_x;
+    const int ty = (tile / tiles_x) % tiles_y;
+    const int img = tile / (tiles_x * tiles_y);
+    const int x0 = tx * kRgbTileW, y0 = ty * kRgbTileH;
+
+    // ---- halo tile -> shared memory as floats (zero outside the image = 'same' padding)
+    for (int i = tid; i < kRgbHaloH * kRgbHaloW * 3; i += 128) {
+      const int hy = i / (kRgbHaloW * 3), rem = i - hy * (kRgbHaloW * 3);
+      const int hx = rem / 3;
+      const int yy = y0 + hy - 1, xx = x0 + hx - 1;
+      float v = 0.f;
+      if (yy >= 0 && yy < H && xx >= 0 && xx < W)
+        v = float(in[((size_t(img) * H + yy) * W + x0 - 1) * 3 + rem]);
+      s_halo[hy][rem] = v;
+    }
+    __syncthreads();
+
+    // ---- im2col: k = dy*9 + dx*3 + ch = dy*9 + (9 consecutive halo values starting at pixel c)
+    {
+      float a[32];
+#pragma unroll
+      for (int dy = 0; dy < 3; ++dy)
+#pragma unroll
+        for (int j = 0; j < 9; ++j) a[dy * 9 + j] = s_halo[r + dy][c * 3 + j];
+#pragma unroll
+      for (int j = 27; j < 32; ++j) a[j] = 0.f;
+      const int sw = tid & 7;
+#pragma unroll
+      for (int c4 = 0; c4 < 4; ++c4) {
+        const uint4 v = make_uint4(pack2<Elem>(a[c4 * 8 + 0], a[c4 * 8 + 1]), pack2<Elem>(a[c4 * 8 + 2], a[c4 * 8 + 3]),
+                                   pack2<Elem>(a[c4 * 8 + 4], a[c4 * 8 + 5]), pack2<Elem>(a[c4 * 8 + 6], a[c4 * 8 + 7]));
+        *reinterpret_cast<uint4*>(s_a + tid * 128 + ((c4 ^ sw) * 16)) = v;        // pairs with w_hi
+        *reinterpret_cast<uint4*>(s_a + tid * 128 + (((c4 + 4) ^ sw) * 16)) = v;  // pairs with w_lo
+      }
+    }
+    sm100::fence_proxy_async_smem();   // generic-proxy writes -> visible to the tensor core (async proxy)
+    sm100::tc_fence_before_sync();     // orders the previous tile's tcgen05.ld before this tile's MMA
+    __syncthreads();
+
+    if (tid == 0) {
+      sm100::tc_fence_after_sync();
+      const uint32_t a_addr = sm100::smem_u32(s_a), b_addr = sm100::smem_u32(s_b);
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+        sm100::umma_ss<false>(tmem, sm100::make_smem_desc_kmajor<128>(a_addr + k * 32),
+                              sm100::make_smem_desc_kmajor<128>(b_addr + k * 32), idesc, k);
+      sm100::umma_commit(&s_bar);
+    }
+    sm100::mbar_wait(&s_bar, phase);
+    phase ^= 1;
+    sm100::tc_fence_after_sync();
+
+    // ---- epilogue: one pixel per thread, 32 channels = 64 contiguous bytes
+    uint32_t v[32];
+    sm100::tmem_ld_32x32b_x32(tmem + (uint32_t(32 * warp) << 16), v);
+    sm100::tmem_ld_wait();
+    uint32_t pk[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      const float f0 = fmaf(fmaxf(fmaf(__uint_as_float(v[2 * i]), in_scale, s_bias[2 * i]), 0.f), s_scale[2 * i],
+                            s_shift[2 * i]);
+      const float f1 = fmaf(fmaxf(fmaf(__uint_as_float(v[2 * i + 1]), in_scale, s_bias[2 * i + 1]), 0.f),
+                            s_scale[2 * i + 1], s_shift[2 * i + 1]);
+      pk[i] = pack2<Elem>(f0, f1);
+    }
+    uint4* dst = reinterpret_cast<uint4*>(out + ((size_t(img) * H + y0 + r) * W + x0 + c) * 32);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) dst[i] = make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
+  }
+
+  sm100::tc_fence_before_sync();
+  __syncthreads();
+  if (warp == 1) {
+    sm100::tc_fence_after_sync();
+    sm100::tmem_dealloc(tmem, 32);
+  }
+}
+
+}  // namespace itmo

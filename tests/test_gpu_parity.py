@@ -175,7 +175,7 @@ def test_first_layer_from_raw_pixels(dev, prec, in_dtype):
         xin = torch.randint(0, 256, (n, h, h, 3), generator=g, dtype=torch.uint8)
         xf = torch.from_numpy(R.preprocess_u8(xin.numpy()))
     else:
-        xin = torch.rand(n, h, h, 3, generator=g)
+        xin = _quant(torch.rand(n, h, h, 3, generator=g), prec)   # 16-bit modes read the floats as 16-bit operands
         xf = xin
     k = torch.randn(3, 3, 3, 32, generator=g) * (2.0 / 27) ** 0.5
     bias = torch.rand(32, generator=g) * 0.2 - 0.1
