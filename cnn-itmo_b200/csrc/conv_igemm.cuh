@@ -190,7 +190,9 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
   float* s_shift = s_scale + kMaxCout;
   float* s_head = s_shift + kMaxCout;                       // [3*64 weights][3 bias]
 
-  const int warp_idx = threadIdx.x >> 5;
+  // warp index made provably warp-uniform: with a uniform role branch and elect.sync the compiler issues
+  // UTCHMMA / UBLKCP straight from uniform registers instead of a per-thread ELECT/BRA loop around every one
+  const int warp_idx = __shfl_sync(0xFFFFFFFFu, threadIdx.x >> 5, 0);
   const int lane = threadIdx.x & 31;
 
   const int tile_w = kBlkW * nm;
@@ -247,8 +249,8 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
 
   // ---------------------------------------------------------------- warp roles
   if (warp_idx == 0) {
-    // ===== TMA producer (one thread) =====
-    if (lane == 0) {
+    // ===== TMA producer (one elected thread) =====
+    if (sm100::elect_one()) {
       const uint32_t a_bytes = uint32_t(SWZ) * halo_w * halo_h;
       if (p.b_resident) {
         // all weight tiles of the layer, once (n_tiles == 1 in this mode)
@@ -297,8 +299,8 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
       }
     }
   } else if (warp_idx == 1) {
-    // ===== MMA issuer (one thread) =====
-    if (lane == 0) {
+    // ===== MMA issuer (one elected thread) =====
+    if (sm100::elect_one()) {
       constexpr uint32_t idesc = sm100::make_idesc(ElemTraits<Elem>::kFmt, kTileM, BLOCK_N);
       const uint32_t sbo = p.dbg == 2 ? 8u * SWZ : uint32_t(halo_w) * SWZ;  // 8-pixel groups are one halo row apart
       int sa = 0, sb = 0;
