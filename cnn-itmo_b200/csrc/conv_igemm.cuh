@@ -72,7 +72,7 @@ struct ConvParams {
                        // tensor core adds into its fp32 accumulator with truncation, a bias that grows with the
                        // number of chained MMAs; the fp32 mode spreads the x*w_hi products round-robin over S-1
                        // accumulators and keeps the two small cross terms in the last one.
-  int dbg;             // timing experiments only (results wrong): 1 = 1024B-aligned A descriptors for every tap
+  int dbg;             // timing experiments only (results wrong): 16 no activation TMA, 32 no epilogue, 64 no MMAs
   int kb_hi;           // channel blocks of the leading (x*w_hi) part; the rest go to accumulator S-1
   const float* bias;      // [cout]
   const float* bn_scale;  // [cout]  gamma / sqrt(var + eps)
@@ -163,6 +163,65 @@ struct ConvCfg {
   static constexpr int kChunk = 32;                       // accumulator columns per tcgen05.ld
 };
 
+// The NM * KSTEPS MMAs of one (channel block, tap). Their shared-memory descriptors differ from the tap's first one
+// only by compile-time constants in the start-address field (units of 16 bytes), so each MMA costs the issuing
+// thread two integer adds: at N <= 64 the tensor pipe retires an MMA every 40-48 clocks (tools/ubench/umma_rate.cu)
+// and a longer issue sequence per MMA becomes the bottleneck of the whole kernel. K step outer, M block inner.
+template <bool TF32, int NM, int KSTEPS, int SWZ, int BLOCK_N>
+__device__ __forceinline__ void issue_tap(uint32_t tmem_d, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo, uint32_t b_hi,
+                                          uint32_t idesc, uint32_t have) {
+#pragma unroll
+  for (int k = 0; k < KSTEPS; ++k) {
+    const uint64_t db = (uint64_t(b_hi) << 32) | uint64_t(b_lo + uint32_t((k * 32) >> 4));
+#pragma unroll
+    for (int j = 0; j < NM; ++j) {
+      const uint64_t da = (uint64_t(a_hi) << 32) | uint64_t(a_lo + uint32_t((j * kBlkW * SWZ + k * 32) >> 4));
+      sm100::umma_ss<TF32>(tmem_d + uint32_t(j * BLOCK_N), da, db, idesc, k == 0 ? have : 1u);
+    }
+  }
+}
+
+// All taps of one channel block, fully unrolled for the tile shape the layer planner picks for this BLOCK_N
+// (NM M blocks, 3x3 or single tap): every descriptor is "stage base + compile-time constant". The issuing thread's
+// instructions between two MMAs are NOT hidden behind the tensor pipe beyond a few queued MMAs (measured: a 25-instruction
+// tap prologue cost ~40 clocks per MMA at N = 64), so the stream has to be this dense.
+template <bool TF32, int NM, int KSTEPS, int SWZ, int BLOCK_N, bool CONV>
+__device__ __forceinline__ void issue_kb(uint32_t tmem_d, uint32_t a_lo, uint32_t a_hi, uint32_t b_hi, uint32_t idesc,
+                                         uint32_t have_first, bool resident, uint32_t b_res_lo, uint32_t b_lo0,
+                                         uint64_t* b_full, uint64_t* b_empty, int& sb, uint32_t& pb, int n_b) {
+  constexpr int kT = CONV ? 3 : 1;
+  constexpr int kHaloW = kBlkW * NM + (CONV ? 2 : 0);
+  constexpr uint32_t kB16 = uint32_t(BLOCK_N * SWZ) >> 4;
+#pragma unroll
+  for (int ty = 0; ty < kT; ++ty) {
+#pragma unroll
+    for (int tx = 0; tx < kT; ++tx) {
+      const int tap = ty * kT + tx;
+      uint32_t b_lo;
+      if (resident) {
+        b_lo = b_res_lo + uint32_t(tap) * kB16;
+      } else {
+        sm100::mbar_wait(&b_full[sb], pb);
+        sm100::tc_fence_after_sync();
+        b_lo = b_lo0 + uint32_t(sb) * kB16;
+      }
+      issue_tap<TF32, NM, KSTEPS, SWZ, BLOCK_N>(tmem_d, a_lo + (uint32_t((ty * kHaloW + tx) * SWZ) >> 4), a_hi, b_lo, b_hi,
+                                                 idesc, tap == 0 ? have_first : 1u);
+      if (!resident) {
+        sm100::umma_commit(&b_empty[sb]);  // frees this weight stage once the MMAs retire
+        if (++sb == n_b) {
+          sb = 0;
+          pb ^= 1;
+        }
+      }
+    }
+  }
+}
+
+// M blocks per CTA tile the planner uses for a given N tile (run_conv in itmo_api.cu); other values (narrow test
+// images, the fp32 mode's split accumulators) take the generic issue loop.
+__host__ __device__ constexpr int natural_nm(int block_n) { return block_n >= 256 ? 1 : block_n == 128 ? 2 : 4; }
+
 template <typename Elem, int BLOCK_N, int SWZ>
 __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid_constant__ ConvParams p) {
   using Cfg = ConvCfg<Elem, BLOCK_N, SWZ>;
@@ -250,7 +309,7 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
   // ---------------------------------------------------------------- warp roles
   if (warp_idx == 0) {
     // ===== TMA producer (one elected thread) =====
-    if (sm100::elect_one()) {
+    if (sm100::elect_one() && !(p.dbg & 512)) {  // 512: timing experiment without the producer
       const uint32_t a_bytes = uint32_t(SWZ) * halo_w * halo_h;
       if (p.b_resident) {
         // all weight tiles of the layer, once (n_tiles == 1 in this mode)
@@ -260,7 +319,7 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
             sm100::tma_load_3d(smem_b + (kb * p.taps + tap) * Cfg::kBBytes, &p.tmB, &b_full[0], kb * Cfg::kBK, 0, tap,
                                sm100::kEvictLast);
       }
-      int sa = 0, sb = 0;
+      int sa = 0, sb = 0, a_loads = 0;
       uint32_t pa = 0, pb = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
         const int n_tile = tile % p.n_tiles;
@@ -275,9 +334,14 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
           const CUtensorMap* tmA = &p.tmA[p.seg_map[s]];
           for (int kb = 0; kb < p.seg_kb[s]; ++kb, ++kb_glob) {
             sm100::mbar_wait(&a_empty[sa], pa ^ 1);
-            sm100::mbar_arrive_expect_tx(&a_full[sa], a_bytes);
-            sm100::tma_load_4d(smem_a + sa * p.a_stage_bytes, tmA, &a_full[sa], kb * Cfg::kBK, x0, y0, img,
-                               sm100::kEvictNormal);
+            if ((p.dbg & 16) && a_loads >= n_a) {   // timing experiment: no activation traffic after the ring filled
+              sm100::mbar_arrive(&a_full[sa]);
+            } else {
+              sm100::mbar_arrive_expect_tx(&a_full[sa], a_bytes);
+              sm100::tma_load_4d(smem_a + sa * p.a_stage_bytes, tmA, &a_full[sa], kb * Cfg::kBK, x0, y0, img,
+                                 sm100::kEvictNormal);
+            }
+            ++a_loads;
             if (++sa == n_a) {
               sa = 0;
               pa ^= 1;
@@ -302,56 +366,80 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
     // ===== MMA issuer (one elected thread) =====
     if (sm100::elect_one()) {
       constexpr uint32_t idesc = sm100::make_idesc(ElemTraits<Elem>::kFmt, kTileM, BLOCK_N);
-      const uint32_t sbo = p.dbg == 2 ? 8u * SWZ : uint32_t(halo_w) * SWZ;  // 8-pixel groups are one halo row apart
+      // descriptor high words are constant; the low words (start address >> 4) advance by whole pixels / rows
+      const uint32_t a_hi = sm100::smem_desc_hi<SWZ>(uint32_t(halo_w) * SWZ);  // 8-pixel groups one halo row apart
+      const uint32_t b_hi = sm100::smem_desc_hi<SWZ>(8u * SWZ);
+      const uint32_t row16 = (uint32_t(halo_w) * SWZ) >> 4;                    // one halo row, in descriptor units
+      const uint32_t b_lo0 = sm100::smem_desc_lo(sm100::smem_u32(smem_b));
+      const int taps_y = p.taps == 9 ? 3 : 1, taps_x = taps_y;
       int sa = 0, sb = 0;
       uint32_t pa = 0, pb = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      if (p.b_resident) {
+      const bool fast = S == 1 && nm == natural_nm(BLOCK_N) && !(p.dbg & (64 | 1024));  // 1024: force the generic loop
+      const bool nowait = (p.dbg & 128) != 0;   // timing experiment: the issuing thread never waits on a barrier
+      if (p.b_resident && !nowait) {
         sm100::mbar_wait(&b_full[0], 0);
         sm100::tc_fence_after_sync();
       }
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        sm100::mbar_wait(&tmem_empty_bar[acc], acc_phase ^ 1);
+        if (!nowait) sm100::mbar_wait(&tmem_empty_bar[acc], acc_phase ^ 1);
         sm100::tc_fence_after_sync();
         const uint32_t tmem_d = tmem_base + uint32_t(acc) * buf_cols;
         uint32_t used = 0;   // accumulators that already hold a partial sum in this tile
-        int it_hi = 0;
+        int rr = 0;
+        uint32_t b_res_lo = b_lo0;  // resident weights: tiles follow each other in (channel block, tap) order
         for (int kb = 0; kb < kb_total; ++kb) {
-          sm100::mbar_wait(&a_full[sa], pa);
+          if (!nowait) sm100::mbar_wait(&a_full[sa], pa);
           sm100::tc_fence_after_sync();
-          const uint32_t a_base = sm100::smem_u32(smem_a + sa * p.a_stage_bytes);
-          for (int tap = 0; tap < p.taps; ++tap) {
-            uint32_t b_addr;
-            if (p.b_resident) {
-              b_addr = sm100::smem_u32(smem_b + (kb * p.taps + tap) * Cfg::kBBytes);
-            } else {
-              sm100::mbar_wait(&b_full[sb], pb);
-              sm100::tc_fence_after_sync();
-              b_addr = sm100::smem_u32(smem_b + sb * Cfg::kBBytes);
-            }
-            const int ty_ = (p.taps == 9) ? tap / 3 : 0;    // halo row / column of the tap's first pixel
-            const int tx_ = (p.taps == 9) ? tap % 3 : 0;
-            uint32_t a_tap = a_base + uint32_t(ty_ * halo_w + tx_) * SWZ;
-            if (p.dbg == 1) a_tap = a_base + uint32_t(ty_) * 1024u;
-            if (p.dbg == 2) a_tap = a_base;
-            const int sacc = S == 1 ? 0 : (kb < p.kb_hi ? (it_hi++ % (S - 1)) : S - 1);
-            const uint32_t have = (used >> sacc) & 1u;
-            used |= 1u << sacc;
-            for (int j = 0; j < nm; ++j) {
-              const uint32_t a_blk = a_tap + uint32_t(j * kBlkW) * SWZ;
-#pragma unroll
-              for (int k = 0; k < Cfg::kKSteps; ++k) {
-                const uint64_t da = sm100::make_smem_desc_kmajor_sbo<SWZ>(a_blk + k * 32, sbo);
-                const uint64_t db = sm100::make_smem_desc_kmajor<SWZ>(b_addr + k * 32);
-                sm100::umma_ss<kTF32>(tmem_d + uint32_t((sacc * nm + j) * BLOCK_N), da, db, idesc, (have | k) != 0 ? 1u : 0u);
+          uint32_t a_row_lo = sm100::smem_desc_lo(sm100::smem_u32(smem_a + sa * p.a_stage_bytes));
+          if (fast) {
+            constexpr int kNM = natural_nm(BLOCK_N);
+            if (p.taps == 9)
+              issue_kb<kTF32, kNM, Cfg::kKSteps, SWZ, BLOCK_N, true>(tmem_d, a_row_lo, a_hi, b_hi, idesc, kb != 0, p.b_resident != 0,
+                                                                     b_res_lo, b_lo0, b_full, b_empty, sb, pb, n_b);
+            else
+              issue_kb<kTF32, kNM, Cfg::kKSteps, SWZ, BLOCK_N, false>(tmem_d, a_row_lo, a_hi, b_hi, idesc, kb != 0, p.b_resident != 0,
+                                                                      b_res_lo, b_lo0, b_full, b_empty, sb, pb, n_b);
+            b_res_lo += uint32_t(p.taps) * (Cfg::kBBytes >> 4);
+          } else
+          for (int ty_ = 0; ty_ < taps_y; ++ty_, a_row_lo += row16) {
+            uint32_t a_tap_lo = a_row_lo;   // halo row / column of the tap's first pixel
+            for (int tx_ = 0; tx_ < taps_x; ++tx_, a_tap_lo += SWZ >> 4) {
+              uint32_t b_lo;
+              if (p.b_resident) {
+                b_lo = b_res_lo;
+                b_res_lo += Cfg::kBBytes >> 4;
+              } else {
+                sm100::mbar_wait(&b_full[sb], pb);
+                sm100::tc_fence_after_sync();
+                b_lo = b_lo0 + uint32_t(sb) * (Cfg::kBBytes >> 4);
               }
-            }
-            if (!p.b_resident) {
-              sm100::umma_commit(&b_empty[sb]);  // frees this weight stage once the MMAs retire
-              if (++sb == n_b) {
-                sb = 0;
-                pb ^= 1;
+              // accumulator of this tap: always 0 unless the fp32 mode splits the sum (round-robin, no division:
+              // everything in this loop is on the single issuing thread's critical path)
+              int sacc = 0;
+              if (S > 1) {
+                if (kb < p.kb_hi) {
+                  sacc = rr;
+                  if (++rr == S - 1) rr = 0;
+                } else {
+                  sacc = S - 1;
+                }
+              }
+              const uint32_t have = (used >> sacc) & 1u;
+              used |= 1u << sacc;
+              const uint32_t d0 = tmem_d + uint32_t(sacc * nm) * BLOCK_N;
+              if (!(p.dbg & 64)) {  // 64: timing experiment without the MMAs (TMA + epilogue only)
+                if (nm == 4) issue_tap<kTF32, 4, Cfg::kKSteps, SWZ, BLOCK_N>(d0, a_tap_lo, a_hi, b_lo, b_hi, idesc, have);
+                else if (nm == 2) issue_tap<kTF32, 2, Cfg::kKSteps, SWZ, BLOCK_N>(d0, a_tap_lo, a_hi, b_lo, b_hi, idesc, have);
+                else issue_tap<kTF32, 1, Cfg::kKSteps, SWZ, BLOCK_N>(d0, a_tap_lo, a_hi, b_lo, b_hi, idesc, have);
+              }
+              if (!p.b_resident) {
+                sm100::umma_commit(&b_empty[sb]);  // frees this weight stage once the MMAs retire
+                if (++sb == n_b) {
+                  sb = 0;
+                  pb ^= 1;
+                }
               }
             }
           }
@@ -366,7 +454,7 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
         if (acc == 0) acc_phase ^= 1;
       }
     }
-  } else if (warp_idx >= 4) {
+  } else if (warp_idx >= 4 && !(p.dbg & 256)) {  // 256: timing experiment without the epilogue warps
     // ===== epilogue warps: TMEM -> registers -> bias/ReLU/BN (-> pool / head) -> global =====
     const int ew = warp_idx - 4;            // 0..7
     const int q = warp_idx & 3;             // TMEM lane quarter this warp may read
@@ -394,7 +482,7 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
       // the two warp sets split the tile: by M block when there are several, else by column chunk; a fused
       // head needs every channel of a pixel in one thread, so a lone block then stays with set 0
       const bool split_by_chunk = nm == 1 && kChunksPerBlk > 1 && p.head_dtype == kHeadNone;
-      for (int j = 0; j < nm; ++j) {
+      for (int j = 0; j < ((p.dbg & 32) ? 0 : nm); ++j) {  // dbg 32: timing experiment without the epilogue
         if (nm > 1 ? (j & 1) != ws : (!split_by_chunk && ws != 0)) continue;
         const int x = tx * tile_w + j * kBlkW + c;
         float h0 = 0.f, h1 = 0.f, h2 = 0.f;

@@ -207,6 +207,16 @@ __device__ __forceinline__ uint64_t make_smem_desc_kmajor_sbo(uint32_t smem_addr
   return d;
 }
 
+// The same descriptor as two 32-bit words, for issue loops that only advance the start address:
+// low word = (address >> 4) | LBO field 1; adding (bytes >> 4) to it moves the start (shared memory is < 256 KB,
+// so the 14-bit field cannot carry into the LBO field).
+__device__ __forceinline__ uint32_t smem_desc_lo(uint32_t smem_addr) { return ((smem_addr & 0x3FFFFu) >> 4) | (1u << 16); }
+template <int SWZ>
+__device__ __forceinline__ uint32_t smem_desc_hi(uint32_t sbo_bytes) {
+  constexpr uint32_t layout = (SWZ == 128) ? 2u : (SWZ == 64) ? 4u : 6u;
+  return ((sbo_bytes >> 4) & 0x3FFFu) | (1u << 14) | (layout << 29);
+}
+
 enum : uint32_t { kFmtF16 = 0, kFmtBF16 = 1, kFmtTF32 = 2 };
 // Instruction descriptor for kind::f16 / kind::tf32 with fp32 accumulate, both operands K-major.
 //   [4,6) c_format=1 (F32)  [7,10) a_format  [10,13) b_format  [15] a_major=0  [16] b_major=0
