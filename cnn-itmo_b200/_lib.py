@@ -7,13 +7,14 @@ from __future__ import annotations
 
 import ctypes
 import os
-from ctypes import POINTER, c_char_p, c_float, c_int, c_longlong, c_size_t, c_uint, c_void_p
+from ctypes import POINTER, c_char_p, c_double, c_float, c_int, c_longlong, c_size_t, c_uint, c_void_p
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, 'libitmo_b200.so')
 
 PREC_TF32, PREC_BF16, PREC_FP32, PREC_FP16 = 0, 1, 2, 3
 DT_U8, DT_F32 = 0, 1
+OUT_U8, OUT_F32, OUT_HDR_INTENDED, OUT_HDR_AS_WRITTEN = 0, 1, 2, 3
 NUM_LAYERS = 19
 
 
@@ -43,6 +44,9 @@ SIGNATURES = {
     'itmo_set_profiling': (c_int, [c_void_p, c_int]),
     'itmo_layer_times': (c_int, [c_void_p, POINTER(ctypes.c_double), POINTER(c_longlong), c_int]),
     'itmo_read_activation': (c_int, [c_void_p, c_int, c_int, POINTER(c_float), c_size_t, POINTER(c_size_t)]),
+    'itmo_tile_axis_plan': (c_int, [c_int, POINTER(c_int), POINTER(c_int), POINTER(c_int), c_int]),
+    'itmo_predict_frames': (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_int, c_double, c_void_p]),
+    'itmo_inverse_reinhard': (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_double, c_void_p, c_void_p]),
     'itmo_conv3x3_bn': (c_int, [c_int, c_void_p, c_int, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p,
                                 c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
     'itmo_convT2x2_bn': (c_int, [c_int, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p,

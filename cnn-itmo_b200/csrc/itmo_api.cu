@@ -18,6 +18,7 @@
 
 #include "../../include/itmo_b200.h"
 #include "conv_igemm.cuh"
+#include "frame_ops.cuh"
 #include "rgb_conv_tc.cuh"
 
 namespace {
@@ -624,6 +625,16 @@ struct itmo_ctx {
   cudaStream_t d2h_stream = nullptr;
   cudaEvent_t ev_in_ready[2] = {}, ev_compute_done[2] = {}, ev_out_free[2] = {};
 
+  // itmo_predict_frames workspaces (tiles of the current chunk, uint8 frame for the HDR stage, plan, statistics)
+  void* frm_tiles_in = nullptr;
+  void* frm_tiles_out = nullptr;
+  size_t frm_tiles_out_bytes = 0;
+  void* frm_u8 = nullptr;
+  size_t frm_u8_bytes = 0;
+  itmo::TileRect* frm_rects = nullptr;
+  int frm_rects_cap = 0;
+  itmo::FrameStats* frm_stats = nullptr;
+
   // per-layer device timing (itmo_set_profiling): event pairs recorded around every layer launch
   bool profiling = false;
   struct Stamp { int layer; cudaEvent_t beg, end; };
@@ -723,7 +734,7 @@ int forward_chunk(itmo_ctx* ctx, const void* in_dev, int in_dtype, void* out_dev
 extern "C" {
 
 const char* itmo_last_error(void) { return g_last_error.c_str(); }
-int itmo_abi_version(void) { return 1; }
+int itmo_abi_version(void) { return 2; }
 
 int itmo_create(itmo_ctx** out, int device, int precision, int max_batch) {
   if (!out) return fail(ITMO_ERR_INVALID, "out is null");
@@ -827,6 +838,11 @@ void itmo_destroy(itmo_ctx* ctx) {
     cudaFree(ctx->shift[li]);
   }
   cudaFree(ctx->arena);
+  cudaFree(ctx->frm_tiles_in);
+  cudaFree(ctx->frm_tiles_out);
+  cudaFree(ctx->frm_u8);
+  cudaFree(ctx->frm_rects);
+  cudaFree(ctx->frm_stats);
   for (int b = 0; b < 2; ++b) {
     cudaFree(ctx->dev_in[b]);
     cudaFree(ctx->dev_out[b]);
@@ -993,6 +1009,128 @@ int itmo_predict_host(itmo_ctx* ctx, const void* in_host, int in_dtype, void* ou
   ITMO_CUDA(cudaStreamSynchronize(ctx->h2d_stream));
   ITMO_CUDA(cudaStreamSynchronize(ctx->own_stream));
   ITMO_CUDA(cudaStreamSynchronize(ctx->d2h_stream));
+  return ITMO_OK;
+}
+
+int itmo_tile_axis_plan(int extent, int* origin, int* valid_lo, int* valid_hi, int cap) {
+  int o[64], lo[64], hi[64];
+  const int n = itmo::plan_axis(extent, o, lo, hi, 64);
+  if (n < 0) return fail(ITMO_ERR_INVALID, "frame extent %d must be a multiple of 16 and at least %d", extent, itmo::kTile);
+  if (n > 64) return fail(ITMO_ERR_INVALID, "frame extent %d too large", extent);
+  for (int i = 0; i < n && i < cap; ++i) {
+    if (origin) origin[i] = o[i];
+    if (valid_lo) valid_lo[i] = lo[i];
+    if (valid_hi) valid_hi[i] = hi[i];
+  }
+  return n;
+}
+
+int itmo_inverse_reinhard(const void* frames_u8_dev, void* hdr_f32_dev, int n_frames, int h, int w, int as_written,
+                          double key, void* stats_scratch_dev, void* stream) {
+  if (!frames_u8_dev || !hdr_f32_dev || !stats_scratch_dev) return fail(ITMO_ERR_INVALID, "null argument");
+  if (n_frames < 0 || h <= 0 || w <= 0) return fail(ITMO_ERR_INVALID, "bad frame shape");
+  cudaStream_t s = (cudaStream_t)stream;
+  const size_t n_pix = size_t(h) * w;
+  itmo::FrameStats* st = (itmo::FrameStats*)stats_scratch_dev;
+  ITMO_CUDA(cudaMemsetAsync(st, 0, sizeof(itmo::FrameStats) * n_frames, s));
+  const int grid = int(std::min<size_t>((n_pix + 255) / 256, size_t(num_sms()) * 8));
+  for (int f = 0; f < n_frames; ++f) {
+    const uint8_t* src = (const uint8_t*)frames_u8_dev + size_t(f) * n_pix * 3;
+    itmo::frame_stats_kernel<<<grid, 256, 0, s>>>(src, n_pix, st + f, as_written);
+    itmo::inverse_reinhard_kernel<<<grid, 256, 0, s>>>(src, (float*)hdr_f32_dev + size_t(f) * n_pix * 3, n_pix, st + f,
+                                                       as_written, key);
+  }
+  ITMO_CUDA(cudaGetLastError());
+  return ITMO_OK;
+}
+
+int itmo_predict_frames(itmo_ctx* ctx, const void* frames_dev, int n_frames, int h, int w, void* out_dev, int out_kind,
+                        double key, void* stream) {
+  if (!ctx || !frames_dev || !out_dev) return fail(ITMO_ERR_INVALID, "null argument");
+  if (!ctx->weights_loaded) return fail(ITMO_ERR_STATE, "itmo_predict_frames before itmo_load_weights");
+  if (out_kind < ITMO_OUT_U8 || out_kind > ITMO_OUT_HDR_AS_WRITTEN) return fail(ITMO_ERR_INVALID, "bad out_kind");
+  if (n_frames < 0) return fail(ITMO_ERR_INVALID, "negative frame count");
+  int oy[64], ylo[64], yhi[64], ox[64], xlo[64], xhi[64];
+  const int ny = itmo::plan_axis(h, oy, ylo, yhi, 64), nx = itmo::plan_axis(w, ox, xlo, xhi, 64);
+  if (ny < 0 || nx < 0 || ny > 64 || nx > 64)
+    return fail(ITMO_ERR_INVALID, "frame %dx%d: both sides must be multiples of 16, at least %d", h, w, itmo::kTile);
+  ITMO_CUDA(cudaSetDevice(ctx->device));
+  cudaStream_t s = (cudaStream_t)stream;
+  const int nt = ny * nx;
+  const bool hdr = out_kind >= ITMO_OUT_HDR_INTENDED;
+  const bool as_written = out_kind == ITMO_OUT_HDR_AS_WRITTEN;
+  const bool f32 = out_kind == ITMO_OUT_F32;
+  const size_t tile_in = size_t(itmo::kTile) * itmo::kTile * 3, tile_out = tile_in * (f32 ? 4 : 1);
+  // workspaces
+  if (!ctx->frm_tiles_in) ITMO_CUDA(cudaMalloc(&ctx->frm_tiles_in, tile_in * ctx->cap));
+  if (ctx->frm_tiles_out_bytes < tile_out * ctx->cap) {
+    cudaFree(ctx->frm_tiles_out);
+    ctx->frm_tiles_out = nullptr;
+    ctx->frm_tiles_out_bytes = 0;
+    ITMO_CUDA(cudaMalloc(&ctx->frm_tiles_out, tile_out * ctx->cap));
+    ctx->frm_tiles_out_bytes = tile_out * ctx->cap;
+  }
+  if (ctx->frm_rects_cap < nt) {
+    cudaFree(ctx->frm_rects);
+    ctx->frm_rects = nullptr;
+    ctx->frm_rects_cap = 0;
+    ITMO_CUDA(cudaMalloc((void**)&ctx->frm_rects, sizeof(itmo::TileRect) * nt));
+    ctx->frm_rects_cap = nt;
+  }
+  const size_t frame_px = size_t(h) * w;
+  if (hdr && ctx->frm_u8_bytes < frame_px * 3) {
+    cudaFree(ctx->frm_u8);
+    ctx->frm_u8 = nullptr;
+    ctx->frm_u8_bytes = 0;
+    ITMO_CUDA(cudaMalloc(&ctx->frm_u8, frame_px * 3));
+    ctx->frm_u8_bytes = frame_px * 3;
+  }
+  if (!ctx->frm_stats) ITMO_CUDA(cudaMalloc((void**)&ctx->frm_stats, sizeof(itmo::FrameStats)));
+  std::vector<itmo::TileRect> rects(nt);
+  for (int j = 0; j < ny; ++j)
+    for (int i = 0; i < nx; ++i) rects[j * nx + i] = {oy[j], ox[i], ylo[j], yhi[j], xlo[i], xhi[i]};
+  // the plan is tiny; a synchronous copy on the caller's stream keeps the host vector's lifetime simple
+  ITMO_CUDA(cudaMemcpyAsync(ctx->frm_rects, rects.data(), sizeof(itmo::TileRect) * nt, cudaMemcpyHostToDevice, s));
+  ITMO_CUDA(cudaStreamSynchronize(s));
+
+  for (int f = 0; f < n_frames; ++f) {
+    const uint8_t* frame = (const uint8_t*)frames_dev + size_t(f) * frame_px * 3;
+    if (hdr) ITMO_CUDA(cudaMemsetAsync(ctx->frm_stats, 0, sizeof(itmo::FrameStats), s));
+    for (int t0 = 0; t0 < nt; t0 += ctx->cap) {
+      const int nb = std::min(ctx->cap, nt - t0);
+      const size_t vecs = size_t(nb) * itmo::kTile * (itmo::kTile * 3 / 16);
+      itmo::tile_gather_kernel<<<int(std::min<size_t>((vecs + 255) / 256, size_t(num_sms()) * 16)), 256, 0, s>>>(
+          frame, w, (uint8_t*)ctx->frm_tiles_in, ctx->frm_rects + t0, nb);
+      ITMO_CUDA(cudaGetLastError());
+      ctx->launches++;
+      int rc = forward_chunk(ctx, ctx->frm_tiles_in, ITMO_DT_U8, ctx->frm_tiles_out, f32 ? ITMO_DT_F32 : ITMO_DT_U8, nb, s);
+      if (rc) return rc;
+      const dim3 grid(64, nb);
+      if (f32) {
+        itmo::tile_scatter_kernel<float, false><<<grid, 256, 0, s>>>((const float*)ctx->frm_tiles_out,
+                                                                     (float*)out_dev + size_t(f) * frame_px * 3, w,
+                                                                     ctx->frm_rects + t0, nb, nullptr, 0);
+      } else if (hdr) {
+        itmo::tile_scatter_kernel<uint8_t, true><<<grid, 256, 0, s>>>((const uint8_t*)ctx->frm_tiles_out,
+                                                                      (uint8_t*)ctx->frm_u8, w, ctx->frm_rects + t0, nb,
+                                                                      ctx->frm_stats, as_written ? 1 : 0);
+      } else {
+        itmo::tile_scatter_kernel<uint8_t, false><<<grid, 256, 0, s>>>((const uint8_t*)ctx->frm_tiles_out,
+                                                                       (uint8_t*)out_dev + size_t(f) * frame_px * 3, w,
+                                                                       ctx->frm_rects + t0, nb, nullptr, 0);
+      }
+      ITMO_CUDA(cudaGetLastError());
+      ctx->launches++;
+    }
+    if (hdr) {
+      const int grid = int(std::min<size_t>((frame_px + 255) / 256, size_t(num_sms()) * 8));
+      itmo::inverse_reinhard_kernel<<<grid, 256, 0, s>>>((const uint8_t*)ctx->frm_u8,
+                                                         (float*)out_dev + size_t(f) * frame_px * 3, frame_px,
+                                                         ctx->frm_stats, as_written ? 1 : 0, key);
+      ITMO_CUDA(cudaGetLastError());
+      ctx->launches++;
+    }
+  }
   return ITMO_OK;
 }
 

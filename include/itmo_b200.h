@@ -141,6 +141,28 @@ int itmo_conv3x3_bn_rgb(int precision, const void* in, int in_dtype, int n, int 
                         const float* bias, const float* scale, const float* shift, int cout, void* out,
                         void* stream);
 
+/* ---- frames larger than the native input (BASELINE config 4) and the inverse-Reinhard output stage ------------
+ * The reference has no tiling (fixed 512x512 Input, model.py:204,207). A frame [h,w,3] (both sides multiples of 16,
+ * >= 512) is cut into 512x512 tiles that all lie inside the frame, start on the 16-pixel grid of the four 2x2 pools
+ * and overlap by >= 96 pixels (the receptive field of this graph reaches 92), so the stitched result equals the
+ * fully-convolutional network on the whole frame. */
+enum itmo_out_kind {
+  ITMO_OUT_U8 = 0,            /* trunc(p*255) uint8, what predict.py:64 writes */
+  ITMO_OUT_F32 = 1,           /* sigmoid output float32 */
+  ITMO_OUT_HDR_INTENDED = 2,  /* float32 linear HDR: m-files/inverse_Reinhard.m with its sign error repaired */
+  ITMO_OUT_HDR_AS_WRITTEN = 3 /* float32: m-files/inverse_Reinhard.m:2-23 literally (degenerate) */
+};
+/* Tile plan along one axis: returns the tile count, fills origin / valid range [lo,hi) per tile (up to cap). */
+int itmo_tile_axis_plan(int extent, int* origin, int* valid_lo, int* valid_hi, int cap);
+/* frames_dev: [n_frames,h,w,3] uint8 on the device; out_dev: same shape, uint8 or float32 by out_kind.
+ * `key` is the geometric-mean luminance the repaired inverse normalises to (Reinhard.m:20 uses 0.18). */
+int itmo_predict_frames(itmo_ctx* ctx, const void* frames_dev, int n_frames, int h, int w, void* out_dev, int out_kind,
+                        double key, void* stream);
+/* Replaces m-files/inverse_Reinhard.m on its own: uint8 CNN output frames -> float32 HDR.
+ * stats_scratch_dev: 32 bytes per frame of device scratch. */
+int itmo_inverse_reinhard(const void* frames_u8_dev, void* hdr_f32_dev, int n_frames, int h, int w, int as_written,
+                          double key, void* stats_scratch_dev, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

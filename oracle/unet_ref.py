@@ -530,3 +530,75 @@ def calibrated_weights(seed: int = 218, calib_size: int = 128, calib_n: int = 4)
             if s.pool:
                 pooled[s.index] = F.max_pool2d(y, 2, 2)
     return ws
+
+
+# --------------------------------------------------------------------------------------------
+# frames larger than 512x512 (BASELINE config 4) and m-files/inverse_Reinhard.m
+# --------------------------------------------------------------------------------------------
+TILE = 512
+TILE_HALO = 96   # >= 92 = receptive-field reach of the graph (3x3 convs and 2x2 pools of model.py:208-262)
+
+
+def plan_axis_ref(extent: int) -> List[Tuple[int, int, int]]:
+    """Independent restatement of the tile plan along one axis: [(origin, valid_lo, valid_hi)].
+    Tiles stay inside the frame (so the frame border sees the network's own 'same' zero padding), start on
+    the 16-pixel grid of the four 2x2 pools, and keep TILE_HALO pixels between a valid range and an interior cut."""
+    assert extent >= TILE and extent % 16 == 0
+    out, covered = [], 0
+    while covered < extent:
+        o = 0 if covered == 0 else covered - TILE_HALO
+        o = min(o, extent - TILE)
+        hi = extent if o + TILE == extent else o + TILE - TILE_HALO
+        out.append((o, covered, hi))
+        covered = hi
+    return out
+
+
+def predict_tiled_torch(tw: 'TorchWeights', frame_f32: np.ndarray) -> np.ndarray:
+    """Whole frame [H,W,3] through 512x512 tiles of the plan, stitched (CPU). The reference itself cannot do this
+    (fixed 512x512 Input, model.py:204); the property tested is tiled == fully-convolutional whole frame."""
+    h, w, _ = frame_f32.shape
+    out = np.empty((h, w, 3), dtype=np.float32)
+    for (oy, y0, y1) in plan_axis_ref(h):
+        for (ox, x0, x1) in plan_axis_ref(w):
+            t = forward_torch(tw, frame_f32[None, oy:oy + TILE, ox:ox + TILE])[0]
+            out[y0:y1, x0:x1] = t[y0 - oy:y1 - oy, x0 - ox:x1 - ox]
+    return out
+
+
+def inverse_reinhard_np(img_u8: np.ndarray, as_written: bool = False, key: float = 0.18) -> np.ndarray:
+    """m-files/inverse_Reinhard.m:2-23 in numpy float64 on one uint8 image [H,W,3] (the script reads the PNG that
+    predict.py:70 wrote). Returns float64 [H,W,3].
+
+    as_written=True follows the script line by line, IEEE semantics of its degenerate cases included:
+      :2  ImgIn = (u8/255)^2.2          :3  I = RGB2Lum(ImgIn)  (HDR-Toolbox, Rec.709: .2126 .7152 .0722)
+      :4  X = I/(I-1)                   (sign error: the inverse of Reinhard.m:22 L = X/(1+X) is X = L/(1-L))
+      :5-11 G_X = exp(mean(log(max(X, realmin))))
+      :12-16 G_E = exp(P log(G_X)/PB1 - PB2 log(a)/PB1), PB1 = #(I==0), PB2 = #(I~=0)  (divides by the count of
+             zero-luminance pixels)     :17 E = G_E X / a     :18 NaN -> realmin     :19 clamp at 2^32
+      :20-23 out_c = ImgIn_c * E / I
+    as_written=False is the repaired form implemented as the product's default: X = I/(1-I), E = key * X / G_X
+    (the recovered luminance is normalised to geometric mean `key`, mirroring Reinhard.m:19-21), zero-luminance
+    pixels stay black instead of NaN."""
+    realmin = np.finfo(np.float64).tiny
+    img = (img_u8.astype(np.float64) / 255.0) ** 2.2
+    I = 0.2126 * img[..., 0] + 0.7152 * img[..., 1] + 0.0722 * img[..., 2]
+    with np.errstate(divide='ignore', invalid='ignore', over='ignore'):
+        X = I / (I - 1.0) if as_written else I / (1.0 - I)
+        Xc = np.where(np.isnan(X), realmin, np.maximum(X, realmin))   # MATLAB max(NaN, realmin) = realmin
+        P = float(I.size)
+        G_X = np.exp(np.log(Xc).sum() / P)
+        if as_written:
+            PB1 = float((I == 0).sum())
+            PB2 = P - PB1
+            a = 0.18
+            G_E = np.exp(np.float64(P) * np.log(G_X) / np.float64(PB1) - np.float64(PB2) * np.log(a) / np.float64(PB1))
+            E = G_E / a * X
+        else:
+            E = key / G_X * X
+        E = np.where(np.isnan(E), realmin, E)
+        E = np.where(E >= 2.0 ** 32, 2.0 ** 32, E)
+        q = E / I
+        if not as_written:
+            q = np.where(I == 0, 0.0, q)
+        return img * q[..., None]
