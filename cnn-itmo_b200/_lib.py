@@ -16,6 +16,8 @@ PREC_TF32, PREC_BF16, PREC_FP32, PREC_FP16 = 0, 1, 2, 3
 DT_U8, DT_F32 = 0, 1
 OUT_U8, OUT_F32, OUT_HDR_INTENDED, OUT_HDR_AS_WRITTEN = 0, 1, 2, 3
 NUM_LAYERS = 19
+TRAIN_NO_DROPOUT, TRAIN_FREEZE_MOVING = 1, 2
+OPT_RMSPROP, OPT_ADAM = 0, 1
 
 
 class LayerWeights(ctypes.Structure):
@@ -55,6 +57,27 @@ SIGNATURES = {
                                      c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
     'itmo_conv3x3_bn_rgb': (c_int, [c_int, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
                                     c_void_p, c_int, c_void_p, c_void_p]),
+    # training step
+    'itmo_train_param_count': (c_longlong, []),
+    'itmo_train_bn_count': (c_longlong, []),
+    'itmo_train_layout': (c_int, [c_int, c_int, POINTER(c_longlong), POINTER(c_longlong)]),
+    'itmo_trainer_create': (c_int, [POINTER(c_void_p), c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
+                                    c_void_p]),
+    'itmo_trainer_destroy': (None, [c_void_p]),
+    'itmo_trainer_sync_weights': (c_int, [c_void_p, c_void_p]),
+    'itmo_train_zero_grad': (c_int, [c_void_p, c_void_p]),
+    'itmo_train_backward': (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_int, c_double, c_uint, c_uint,
+                                    c_void_p]),
+    'itmo_train_dropout_seed': (c_int, [c_uint, c_int, POINTER(c_uint)]),
+    'itmo_train_metrics': (c_int, [c_void_p, POINTER(c_double), POINTER(c_double), c_int, c_void_p]),
+    'itmo_train_update': (c_int, [c_void_p, c_int, c_float, c_float, c_float, c_float, c_float, c_void_p]),
+    'itmo_train_read_activation': (c_int, [c_void_p, c_int, c_int, c_int, POINTER(c_float), c_size_t,
+                                           POINTER(c_size_t)]),
+    'itmo_train_set_profiling': (c_int, [c_void_p, c_int]),
+    'itmo_train_phase_times': (c_int, [c_void_p, POINTER(c_double), POINTER(c_longlong), c_int]),
+    'itmo_train_launch_count': (c_longlong, [c_void_p]),
+    'itmo_wgrad3x3': (c_int, [c_void_p, c_int, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
+    'itmo_dgrad3x3': (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_int, c_void_p, c_void_p]),
 }
 
 

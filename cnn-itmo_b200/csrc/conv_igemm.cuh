@@ -74,6 +74,7 @@ struct ConvParams {
                        // accumulators and keeps the two small cross terms in the last one.
   int dbg;             // timing experiments only (results wrong): 16 no activation TMA, 32 no epilogue, 64 no MMAs
   int kb_hi;           // channel blocks of the leading (x*w_hi) part; the rest go to accumulator S-1
+  int no_relu;         // 1: y = (acc + bias) * scale + shift without the ReLU (data-gradient convolutions of the training step)
   const float* bias;      // [cout]
   const float* bn_scale;  // [cout]  gamma / sqrt(var + eps)
   const float* bn_shift;  // [cout]  beta - mean * scale
@@ -519,7 +520,7 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
 #pragma unroll
           for (int i = 0; i < kChunk; ++i) {
             const float a = __uint_as_float(v[i]) + s_bias[co0 + i];
-            f[i] = fmaf(fmaxf(a, 0.f), s_scale[co0 + i], s_shift[co0 + i]);
+            f[i] = fmaf(p.no_relu ? a : fmaxf(a, 0.f), s_scale[co0 + i], s_shift[co0 + i]);
           }
           if (p.head_dtype != kHeadNone) {
 #pragma unroll

@@ -116,12 +116,14 @@ CUtensorMapSwizzle swizzle_enum(int swz) {
 // NHWC activation tensor [N,H,W,C] viewed as (C, W, H, N); box = (bk channels, box_w, box_h, 1): the halo tile
 // of one CTA tile. Out-of-bounds pixels are zero-filled ('same' padding).
 int make_act_map(CUtensorMap* m, const void* ptr, int precision, int C, int W, int H, int N, int swz, int box_w,
-                 int box_h) {
+                 int box_h, long long row_stride = 0, long long img_stride = 0) {
   auto enc = get_encode_fn();
   if (!enc) return fail(ITMO_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
   const size_t es = elem_size(precision);
   cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
-  cuuint64_t strides[3] = {(cuuint64_t)C * es, (cuuint64_t)W * C * es, (cuuint64_t)H * W * C * es};
+  // row_stride / img_stride (elements, 0 = dense) describe strided views, e.g. every other row of a gradient tensor
+  cuuint64_t strides[3] = {(cuuint64_t)C * es, (cuuint64_t)(row_stride ? row_stride : (long long)W * C) * es,
+                           (cuuint64_t)(img_stride ? img_stride : (long long)H * W * C) * es};
   cuuint32_t box[4] = {(cuuint32_t)(swz / es), (cuuint32_t)box_w, (cuuint32_t)box_h, 1};
   cuuint32_t estr[4] = {1, 1, 1, 1};
   CUresult r = enc(m, tm_dtype(precision),
@@ -135,12 +137,13 @@ int make_act_map(CUtensorMap* m, const void* ptr, int precision, int C, int W, i
 
 // Packed weights [taps][rows][cin_total] viewed as (cin_total, rows, taps); box = (bk, block_n, 1).
 int make_weight_map(CUtensorMap* m, const void* ptr, int precision, int cin_total, int rows, int taps, int block_n,
-                    int swz) {
+                    int swz, int tap_stride_rows = 0) {
   auto enc = get_encode_fn();
   if (!enc) return fail(ITMO_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
   const size_t es = elem_size(precision);
   cuuint64_t dims[3] = {(cuuint64_t)cin_total, (cuuint64_t)rows, (cuuint64_t)taps};
-  cuuint64_t strides[2] = {(cuuint64_t)cin_total * es, (cuuint64_t)rows * cin_total * es};
+  cuuint64_t strides[2] = {(cuuint64_t)cin_total * es,
+                           (cuuint64_t)(tap_stride_rows ? tap_stride_rows : rows) * cin_total * es};
   cuuint32_t box[3] = {(cuuint32_t)(swz / es), (cuuint32_t)block_n, 1};
   cuuint32_t estr[3] = {1, 1, 1};
   CUresult r = enc(m, tm_dtype(precision),
@@ -360,6 +363,12 @@ struct ConvArgs {
   const float* head_b;
   void* head_out;
   int head_dtype;  // itmo::HeadDtype
+  // training step extensions (data-gradient convolutions)
+  int one_tap;               // conv mode with a single tap and no padding (1x1 convolution)
+  int no_relu;               // linear epilogue
+  long long row_stride[2];   // source 0 / 1 viewed with these row / image strides (elements, 0 = dense)
+  long long img_stride[2];
+  int w_tap_stride_rows;     // rows between two taps of the packed weights (0 = the rows this launch uses)
 };
 
 // Debug / tuning overrides (environment, read once): ITMO_FORCE_NM = 1|2|4, ITMO_NO_RESIDENT = 1
@@ -390,8 +399,8 @@ int run_conv(const ConvArgs& a, cudaStream_t stream) {
   }
   if (a.cout > itmo::kMaxCout || a.cout % 32) return fail(ITMO_ERR_INVALID, "cout %d unsupported", a.cout);
   const bool conv = a.mode == itmo::kModeConv3x3;
-  const int taps = conv ? 9 : 1;
-  const int pad = conv ? 1 : 0;
+  const int taps = (conv && !a.one_tap) ? 9 : 1;
+  const int pad = (conv && !a.one_tap) ? 1 : 0;
   const int rows = conv ? a.cout : 4 * a.cout;
   // fp32 mode: 4 split accumulators per M block (see ConvParams::acc_split) -> narrow N tiles, one M block
   const int acc_split = a.precision == ITMO_PREC_FP32 ? 4 : 1;
@@ -438,10 +447,11 @@ int run_conv(const ConvArgs& a, cudaStream_t stream) {
                          (a.c1 > 0 && a.src1_lo) ? a.src1_lo : a.src0};
   const int chans[4] = {a.c0, a.c1 > 0 ? a.c1 : a.c0, a.c0, a.c1 > 0 ? a.c1 : a.c0};
   for (int i = 0; i < 4; ++i) {
-    int rc = make_act_map(&p.tmA[i], srcs[i], a.precision, chans[i], a.w, a.h, a.n, swz, halo_w, halo_h);
+    int rc = make_act_map(&p.tmA[i], srcs[i], a.precision, chans[i], a.w, a.h, a.n, swz, halo_w, halo_h,
+                          a.row_stride[i & 1], a.img_stride[i & 1]);
     if (rc) return rc;
   }
-  int rc = make_weight_map(&p.tmB, a.wpacked, a.precision, kmult * cin, rows, taps, block_n, swz);
+  int rc = make_weight_map(&p.tmB, a.wpacked, a.precision, kmult * cin, rows, taps, block_n, swz, a.w_tap_stride_rows);
   if (rc) return rc;
   // K segments, in the order the weights are packed: [src0 | src1] x {w_hi, w_lo, (x_lo) w_hi}
   int ns = 0;
@@ -470,6 +480,7 @@ int run_conv(const ConvArgs& a, cudaStream_t stream) {
   static const int dbg = env_int("ITMO_DBG", 0);
   p.dbg = dbg;
   p.acc_split = acc_split;
+  p.no_relu = a.no_relu;
   p.kb_hi = cin / bk;
   p.store_mode = a.precision == ITMO_PREC_TF32   ? itmo::kStoreTf32Rna
                  : a.precision == ITMO_PREC_FP32 ? itmo::kStoreSplit
@@ -734,7 +745,7 @@ int forward_chunk(itmo_ctx* ctx, const void* in_dev, int in_dtype, void* out_dev
 extern "C" {
 
 const char* itmo_last_error(void) { return g_last_error.c_str(); }
-int itmo_abi_version(void) { return 2; }
+int itmo_abi_version(void) { return 3; }
 
 int itmo_create(itmo_ctx** out, int device, int precision, int max_batch) {
   if (!out) return fail(ITMO_ERR_INVALID, "out is null");
@@ -1308,3 +1319,5 @@ int itmo_conv3x3_bn_rgb(int precision, const void* in, int in_dtype, int n, int 
 }
 
 }  // extern "C"
+
+#include "train_api.cuh"

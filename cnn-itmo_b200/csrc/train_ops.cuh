@@ -1,0 +1,505 @@
+// train_ops.cuh — the HBM-bound stages of the training step (main.py:126-132 + model.py:281) around the
+// implicit-GEMM kernels: BatchNormalization in training mode (batch statistics over N,H,W of the ReLU output,
+// model.py:196,200), Dropout(0.5) (model.py:226,239), MaxPooling2D forward/backward, the 1x1 sigmoid head with the
+// 'mse' loss (model.py:276,281) and the optimizer update (RMSprop as compiled at model.py:281; the Adam variant of
+// the comments at model.py:280,282). Activations and activation gradients are bf16 NHWC, parameters, statistics
+// and parameter gradients fp32; every kernel moves 16 bytes (8 channels) per thread and access.
+#pragma once
+#include <cuda_bf16.h>
+#include <stdint.h>
+
+namespace itmo {
+
+struct Bf8 {
+  uint4 raw;
+  __device__ __forceinline__ void get(float (&f)[8]) const {
+    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&raw);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const float2 v = __bfloat1622float2(h[i]);
+      f[2 * i] = v.x;
+      f[2 * i + 1] = v.y;
+    }
+  }
+  __device__ __forceinline__ void set(const float (&f)[8]) {
+    __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&raw);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+  }
+};
+__device__ __forceinline__ Bf8 ld8(const __nv_bfloat16* p) {
+  Bf8 v;
+  v.raw = *reinterpret_cast<const uint4*>(p);
+  return v;
+}
+__device__ __forceinline__ void st8(__nv_bfloat16* p, const Bf8& v) { *reinterpret_cast<uint4*>(p) = v.raw; }
+
+// Dropout keep decision of element `e` (flat NHWC index, 32-bit wrap) under `seed`: murmur3 finaliser. The CPU oracle
+// (oracle/unet_train_ref.py: dropout_keep_mask) restates exactly this so both sides drop the same units.
+__device__ __forceinline__ bool drop_keep(uint32_t e, uint32_t seed) {
+  uint32_t h = (e * 0x9E3779B1u) ^ seed;
+  h ^= h >> 16;
+  h *= 0x85EBCA6Bu;
+  h ^= h >> 13;
+  h *= 0xC2B2AE35u;
+  h ^= h >> 16;
+  return (h >> 15) & 1u;
+}
+
+// ---- BN training statistics: sum / sum of squares per channel of z = ReLU(conv + b) ------------------------------
+// grid-stride over pixels; blockDim = 256; thread -> (pixel lane, 8-channel group). stats[0..C) = sum, [C..2C) = sumsq.
+__global__ void __launch_bounds__(256) bn_stats_kernel(const __nv_bfloat16* __restrict__ z, size_t npix, int C,
+                                                       double* __restrict__ stats) {
+  __shared__ float s_sum[512], s_sq[512];
+  for (int i = threadIdx.x; i < C; i += blockDim.x) s_sum[i] = s_sq[i] = 0.f;
+  __syncthreads();
+  const int groups = C >> 3;
+  const int cg = threadIdx.x % groups;
+  const int lanes = blockDim.x / groups;   // pixels per block iteration (C <= 512 -> groups <= 64 -> lanes >= 4)
+  const int pl = threadIdx.x / groups;
+  float a[8] = {}, q[8] = {};
+  if (pl < lanes) {
+    for (size_t pix = size_t(blockIdx.x) * lanes + pl; pix < npix; pix += size_t(gridDim.x) * lanes) {
+      float f[8];
+      ld8(z + pix * C + cg * 8).get(f);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        a[i] += f[i];
+        q[i] = fmaf(f[i], f[i], q[i]);
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      atomicAdd(&s_sum[cg * 8 + i], a[i]);
+      atomicAdd(&s_sq[cg * 8 + i], q[i]);
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < C; i += blockDim.x) {
+    atomicAdd(&stats[i], double(s_sum[i]));
+    atomicAdd(&stats[C + i], double(s_sq[i]));
+  }
+}
+
+// mean / biased variance -> the affine bn_apply uses, the values backward needs, and the moving statistics
+// (Keras BatchNormalization: momentum 0.99; the moving variance takes the sample variance var * M / (M - (1 + eps))).
+__global__ void bn_finalize_kernel(const double* __restrict__ stats, int C, double M, float eps, float momentum,
+                                   const float* __restrict__ gamma, const float* __restrict__ beta,
+                                   float* __restrict__ mean, float* __restrict__ invstd, float* __restrict__ scale,
+                                   float* __restrict__ shift, float* __restrict__ moving_mean,
+                                   float* __restrict__ moving_var) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= C) return;
+  const double m = stats[i] / M;
+  double v = stats[C + i] / M - m * m;
+  if (v < 0) v = 0;
+  const float is = float(1.0 / sqrt(v + double(eps)));
+  mean[i] = float(m);
+  invstd[i] = is;
+  const float s = gamma[i] * is;
+  scale[i] = s;
+  shift[i] = beta[i] - float(m) * s;
+  if (moving_mean) {
+    moving_mean[i] = momentum * moving_mean[i] + (1.f - momentum) * float(m);
+    const double vs = v * (M / (M - (1.0 + double(eps))));
+    moving_var[i] = momentum * moving_var[i] + (1.f - momentum) * float(vs);
+  }
+}
+
+// ---- BN apply (+ Dropout) (+ MaxPool): one thread = one 2x2 pixel window x 8 channels --------------------------------
+// a = z*scale + shift; with dropout a = keep ? 2a : 0 (inverted dropout, rate 0.5); pooled = max over the window of a.
+__global__ void __launch_bounds__(256) bn_apply_kernel(const __nv_bfloat16* __restrict__ z, __nv_bfloat16* __restrict__ a,
+                                                       __nv_bfloat16* __restrict__ pooled, int NB, int H, int W, int C,
+                                                       const float* __restrict__ scale, const float* __restrict__ shift,
+                                                       uint32_t drop_seed, int dropout) {
+  const int groups = C >> 3;
+  const int Hp = H >> 1, Wp = W >> 1;
+  const size_t total = size_t(NB) * Hp * Wp * groups;
+  for (size_t gid = blockIdx.x * size_t(blockDim.x) + threadIdx.x; gid < total; gid += size_t(gridDim.x) * blockDim.x) {
+    const int cg = int(gid % groups);
+    size_t w = gid / groups;
+    const int xp = int(w % Wp);
+    w /= Wp;
+    const int yp = int(w % Hp);
+    const int img = int(w / Hp);
+    float sc[8], sh[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      sc[i] = scale[cg * 8 + i];
+      sh[i] = shift[cg * 8 + i];
+    }
+    float mx[8];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const size_t pix = (size_t(img) * H + 2 * yp + (k >> 1)) * W + 2 * xp + (k & 1);
+      const size_t e0 = pix * C + cg * 8;
+      float f[8];
+      ld8(z + e0).get(f);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        f[i] = fmaf(f[i], sc[i], sh[i]);
+        if (dropout) f[i] = drop_keep(uint32_t(e0 + i), drop_seed) ? 2.f * f[i] : 0.f;
+      }
+      Bf8 o;
+      o.set(f);
+      st8(a + e0, o);
+      o.get(f);   // pool over the stored (rounded) values: what the next layer and the backward see
+#pragma unroll
+      for (int i = 0; i < 8; ++i) mx[i] = k == 0 ? f[i] : fmaxf(mx[i], f[i]);
+    }
+    if (pooled) {
+      Bf8 o;
+      o.set(mx);
+      st8(pooled + ((size_t(img) * Hp + yp) * Wp + xp) * C + cg * 8, o);
+    }
+  }
+}
+
+// ---- head: Conv2D(3, 1, sigmoid) (model.py:276) + mse (model.py:281), forward and backward in one pass -----------------
+// One warp = 32 consecutive pixels. acc[0] += sum (p-y)^2, acc[1] += #pixels with argmax_k p == argmax_k y (Keras
+// 'accuracy' resolves to categorical_accuracy for this output). d_a = (2/count) (p-y) p (1-p) W; dW[k][c], db[k] accumulate.
+// y: target in [0,1], float32 [P,3]. pred (optional): float32 [P,3].
+__global__ void __launch_bounds__(128) head_train_kernel(const __nv_bfloat16* __restrict__ a, const float* __restrict__ y,
+                                                         const float* __restrict__ wh,   // [3][64]
+                                                         const float* __restrict__ bh, size_t npix, float inv_count,
+                                                         __nv_bfloat16* __restrict__ d_a, float* __restrict__ pred,
+                                                         double* __restrict__ acc, float* __restrict__ dwh,
+                                                         float* __restrict__ dbh) {
+  __shared__ float s_w[3 * 64 + 3];
+  __shared__ float s_a[4][32][65];
+  __shared__ float s_dl[4][32][3];
+  __shared__ float s_dw[3 * 64 + 3];
+  for (int i = threadIdx.x; i < 195; i += blockDim.x) {
+    s_w[i] = i < 192 ? wh[i] : bh[i - 192];
+    s_dw[i] = 0.f;
+  }
+  __syncthreads();
+  const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float g[6] = {};      // this lane's 6 of the 192 weight gradients: index j*32 + lane -> (k = idx / 64, c = idx % 64)
+  float gb = 0.f;       // lanes 0..2: bias gradient
+  float loss = 0.f, hits = 0.f;
+  const size_t nwarps = size_t(gridDim.x) * 4;
+  for (size_t base = (size_t(blockIdx.x) * 4 + wid) * 32; base < npix; base += nwarps * 32) {
+    const size_t pix = base + lane;
+    const bool ok = pix < npix;
+    float av[64];
+    if (ok) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float f[8];
+        ld8(a + pix * 64 + j * 8).get(f);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) av[j * 8 + i] = f[i];
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < 64; ++i) av[i] = 0.f;
+    }
+    float z0 = s_w[192], z1 = s_w[193], z2 = s_w[194];
+#pragma unroll
+    for (int c = 0; c < 64; ++c) {
+      z0 = fmaf(av[c], s_w[c], z0);
+      z1 = fmaf(av[c], s_w[64 + c], z1);
+      z2 = fmaf(av[c], s_w[128 + c], z2);
+    }
+    const float p0 = 1.f / (1.f + expf(-z0)), p1 = 1.f / (1.f + expf(-z1)), p2 = 1.f / (1.f + expf(-z2));
+    float dl0 = 0.f, dl1 = 0.f, dl2 = 0.f;
+    if (ok) {
+      const float y0 = y[pix * 3], y1 = y[pix * 3 + 1], y2 = y[pix * 3 + 2];
+      const float e0 = p0 - y0, e1 = p1 - y1, e2 = p2 - y2;
+      loss += e0 * e0 + e1 * e1 + e2 * e2;
+      const int ap = p0 >= p1 ? (p0 >= p2 ? 0 : 2) : (p1 >= p2 ? 1 : 2);   // first maximum, like argmax
+      const int ay = y0 >= y1 ? (y0 >= y2 ? 0 : 2) : (y1 >= y2 ? 1 : 2);
+      hits += ap == ay ? 1.f : 0.f;
+      dl0 = 2.f * inv_count * e0 * p0 * (1.f - p0);
+      dl1 = 2.f * inv_count * e1 * p1 * (1.f - p1);
+      dl2 = 2.f * inv_count * e2 * p2 * (1.f - p2);
+      if (pred) {
+        pred[pix * 3] = p0;
+        pred[pix * 3 + 1] = p1;
+        pred[pix * 3 + 2] = p2;
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float f[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int c = j * 8 + i;
+          f[i] = dl0 * s_w[c] + dl1 * s_w[64 + c] + dl2 * s_w[128 + c];
+        }
+        Bf8 o;
+        o.set(f);
+        st8(d_a + pix * 64 + j * 8, o);
+      }
+    }
+    // weight gradient: stage this warp's 32 pixels, then every lane reduces its 6 (k, c) pairs over them
+#pragma unroll
+    for (int c = 0; c < 64; ++c) s_a[wid][lane][c] = av[c];
+    s_dl[wid][lane][0] = dl0;
+    s_dl[wid][lane][1] = dl1;
+    s_dl[wid][lane][2] = dl2;
+    __syncwarp();
+#pragma unroll
+    for (int j = 0; j < 6; ++j) {
+      const int idx = j * 32 + lane;
+      const int k = idx >> 6, c = idx & 63;
+      float s = 0.f;
+      for (int q = 0; q < 32; ++q) s = fmaf(s_dl[wid][q][k], s_a[wid][q][c], s);
+      g[j] += s;
+    }
+    if (lane < 3) {
+      float s = 0.f;
+      for (int q = 0; q < 32; ++q) s += s_dl[wid][q][lane];
+      gb += s;
+    }
+    __syncwarp();
+  }
+#pragma unroll
+  for (int j = 0; j < 6; ++j) atomicAdd(&s_dw[j * 32 + lane], g[j]);
+  if (lane < 3) atomicAdd(&s_dw[192 + lane], gb);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    loss += __shfl_xor_sync(0xFFFFFFFFu, loss, o);
+    hits += __shfl_xor_sync(0xFFFFFFFFu, hits, o);
+  }
+  if (lane == 0) {
+    atomicAdd(&acc[0], double(loss));
+    atomicAdd(&acc[1], double(hits));
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < 195; i += blockDim.x) {
+    if (i < 192) atomicAdd(&dwh[(i & 63) * 3 + (i >> 6)], s_dw[i]);   // Keras head kernel layout [64][3]
+    else atomicAdd(&dbh[i - 192], s_dw[i]);
+  }
+}
+
+// ---- BN backward, pass 1: per-channel sums of dA' and dA' * zhat (dA' = dA through the dropout mask) ---------------
+// sums[0..C) = sum dA', sums[C..2C) = sum dA' * (z - mean) * invstd
+__global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dA,
+                                                            const __nv_bfloat16* __restrict__ z, size_t npix, int C,
+                                                            const float* __restrict__ mean, const float* __restrict__ invstd,
+                                                            uint32_t drop_seed, int dropout, double* __restrict__ sums) {
+  __shared__ float s_a[512], s_b[512];
+  for (int i = threadIdx.x; i < C; i += blockDim.x) s_a[i] = s_b[i] = 0.f;
+  __syncthreads();
+  const int groups = C >> 3;
+  const int cg = threadIdx.x % groups;
+  const int lanes = blockDim.x / groups;
+  const int pl = threadIdx.x / groups;
+  if (pl < lanes) {
+    float mu[8], is[8], sa[8] = {}, sb[8] = {};
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      mu[i] = mean[cg * 8 + i];
+      is[i] = invstd[cg * 8 + i];
+    }
+    for (size_t pix = size_t(blockIdx.x) * lanes + pl; pix < npix; pix += size_t(gridDim.x) * lanes) {
+      const size_t e0 = pix * C + cg * 8;
+      float d[8], f[8];
+      ld8(dA + e0).get(d);
+      ld8(z + e0).get(f);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        float dv = d[i];
+        if (dropout) dv = drop_keep(uint32_t(e0 + i), drop_seed) ? 2.f * dv : 0.f;
+        sa[i] += dv;
+        sb[i] = fmaf(dv, (f[i] - mu[i]) * is[i], sb[i]);
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      atomicAdd(&s_a[cg * 8 + i], sa[i]);
+      atomicAdd(&s_b[cg * 8 + i], sb[i]);
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < C; i += blockDim.x) {
+    atomicAdd(&sums[i], double(s_a[i]));
+    atomicAdd(&sums[C + i], double(s_b[i]));
+  }
+}
+
+// ---- BN backward, pass 2 (+ ReLU backward): dpre = [z > 0] * gamma*invstd * (dA' - mean(dA') - zhat * mean(dA' zhat)) --
+// also accumulates the bias gradient sum(dpre) per channel (of the bf16-rounded dpre the GEMMs consume).
+__global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dA,
+                                                           const __nv_bfloat16* __restrict__ z,
+                                                           __nv_bfloat16* __restrict__ dpre, size_t npix, int C,
+                                                           const float* __restrict__ gamma, const float* __restrict__ mean,
+                                                           const float* __restrict__ invstd, const double* __restrict__ sums,
+                                                           double M, uint32_t drop_seed, int dropout,
+                                                           float* __restrict__ dbias) {
+  __shared__ float s_db[512];
+  for (int i = threadIdx.x; i < C; i += blockDim.x) s_db[i] = 0.f;
+  __syncthreads();
+  const int groups = C >> 3;
+  const int cg = threadIdx.x % groups;
+  const int lanes = blockDim.x / groups;
+  const int pl = threadIdx.x / groups;
+  if (pl < lanes) {
+    float mu[8], is[8], gs[8], m1[8], m2[8], db[8] = {};
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int c = cg * 8 + i;
+      mu[i] = mean[c];
+      is[i] = invstd[c];
+      gs[i] = gamma[c] * is[i];
+      m1[i] = float(sums[c] / M);
+      m2[i] = float(sums[C + c] / M);
+    }
+    for (size_t pix = size_t(blockIdx.x) * lanes + pl; pix < npix; pix += size_t(gridDim.x) * lanes) {
+      const size_t e0 = pix * C + cg * 8;
+      float d[8], f[8], o[8];
+      ld8(dA + e0).get(d);
+      ld8(z + e0).get(f);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        float dv = d[i];
+        if (dropout) dv = drop_keep(uint32_t(e0 + i), drop_seed) ? 2.f * dv : 0.f;
+        const float zh = (f[i] - mu[i]) * is[i];
+        const float dz = gs[i] * (dv - m1[i] - zh * m2[i]);
+        o[i] = f[i] > 0.f ? dz : 0.f;
+      }
+      Bf8 ov;
+      ov.set(o);
+      st8(dpre + e0, ov);
+      ov.get(o);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) db[i] += o[i];
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) atomicAdd(&s_db[cg * 8 + i], db[i]);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < C; i += blockDim.x) atomicAdd(&dbias[i], s_db[i]);
+}
+
+// dgamma += sum dA' zhat, dbeta += sum dA'
+__global__ void bn_param_grad_kernel(const double* __restrict__ sums, int C, float* __restrict__ dgamma,
+                                     float* __restrict__ dbeta) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < C) {
+    dbeta[i] += float(sums[i]);
+    dgamma[i] += float(sums[C + i]);
+  }
+}
+
+// ---- MaxPool backward + skip add: dA = dSkip + route(dPooled -> first maximum of the 2x2 window of a) -----------------
+__global__ void __launch_bounds__(256) pool_bwd_add_kernel(const __nv_bfloat16* __restrict__ d_skip,
+                                                           const __nv_bfloat16* __restrict__ d_pooled,
+                                                           const __nv_bfloat16* __restrict__ a,
+                                                           __nv_bfloat16* __restrict__ dA, int NB, int H, int W, int C) {
+  const int groups = C >> 3;
+  const int Hp = H >> 1, Wp = W >> 1;
+  const size_t total = size_t(NB) * Hp * Wp * groups;
+  for (size_t gid = blockIdx.x * size_t(blockDim.x) + threadIdx.x; gid < total; gid += size_t(gridDim.x) * blockDim.x) {
+    const int cg = int(gid % groups);
+    size_t w = gid / groups;
+    const int xp = int(w % Wp);
+    w /= Wp;
+    const int yp = int(w % Hp);
+    const int img = int(w / Hp);
+    float dp[8];
+    ld8(d_pooled + ((size_t(img) * Hp + yp) * Wp + xp) * C + cg * 8).get(dp);
+    float av[4][8];
+    size_t e[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      e[k] = ((size_t(img) * H + 2 * yp + (k >> 1)) * W + 2 * xp + (k & 1)) * C + cg * 8;
+      ld8(a + e[k]).get(av[k]);
+    }
+    int arg[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      int b = 0;
+      float m = av[0][i];
+#pragma unroll
+      for (int k = 1; k < 4; ++k)
+        if (av[k][i] > m) {
+          m = av[k][i];
+          b = k;
+        }
+      arg[i] = b;
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      float o[8];
+      if (d_skip) ld8(d_skip + e[k]).get(o);
+      else {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) o[i] = 0.f;
+      }
+#pragma unroll
+      for (int i = 0; i < 8; ++i) o[i] += arg[i] == k ? dp[i] : 0.f;
+      Bf8 ov;
+      ov.set(o);
+      st8(dA + e[k], ov);
+    }
+  }
+}
+
+// ---- first layer input as a 32-channel bf16 tensor (channels 3..31 zero) so its weight gradient runs on the same GEMM
+template <typename InT>
+__global__ void __launch_bounds__(256) rgb_to_c32_kernel(const InT* __restrict__ in, __nv_bfloat16* __restrict__ out,
+                                                         size_t npix, float mul) {
+  for (size_t gid = blockIdx.x * size_t(blockDim.x) + threadIdx.x; gid < npix * 4; gid += size_t(gridDim.x) * blockDim.x) {
+    const size_t pix = gid >> 2;
+    const int cg = int(gid & 3);
+    float f[8] = {};
+    if (cg == 0) {
+      if constexpr (sizeof(InT) == 1) {
+        f[0] = __fdiv_rn(float(in[pix * 3]), 255.f);
+        f[1] = __fdiv_rn(float(in[pix * 3 + 1]), 255.f);
+        f[2] = __fdiv_rn(float(in[pix * 3 + 2]), 255.f);
+      } else {
+        f[0] = float(in[pix * 3]) * mul;
+        f[1] = float(in[pix * 3 + 1]) * mul;
+        f[2] = float(in[pix * 3 + 2]) * mul;
+      }
+    }
+    Bf8 o;
+    o.set(f);
+    st8(out + pix * 32 + cg * 8, o);
+  }
+}
+
+// ---- optimizer over the flat parameter buffer -----------------------------------------------------------------------
+// Keras RMSprop (model.py:281 'rmsprop': lr 1e-3, rho 0.9, eps 1e-7):  a = rho a + (1-rho) g^2;  p -= lr g / (sqrt(a) + eps)
+__global__ void rmsprop_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ a, size_t n,
+                               float lr, float rho, float eps, float gscale) {
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n; i += size_t(gridDim.x) * blockDim.x) {
+    const float gi = g[i] * gscale;
+    const float ai = rho * a[i] + (1.f - rho) * gi * gi;
+    a[i] = ai;
+    p[i] -= lr * gi / (sqrtf(ai) + eps);
+  }
+}
+// Keras Adam (model.py:280,282 comments: lr 1e-3 / 2e-3, beta_1 0.5):  lr_t = lr sqrt(1-b2^t)/(1-b1^t);
+// m = b1 m + (1-b1) g; v = b2 v + (1-b2) g^2; p -= lr_t m / (sqrt(v) + eps)
+__global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
+                            float* __restrict__ v, size_t n, float lr_t, float b1, float b2, float eps, float gscale) {
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n; i += size_t(gridDim.x) * blockDim.x) {
+    const float gi = g[i] * gscale;
+    const float mi = b1 * m[i] + (1.f - b1) * gi;
+    const float vi = b2 * v[i] + (1.f - b2) * gi * gi;
+    m[i] = mi;
+    v[i] = vi;
+    p[i] -= lr_t * mi / (sqrtf(vi) + eps);
+  }
+}
+
+// ---- weights for the data-gradient convolution: dX = conv3x3(dpre, W') with W'[tap'][ci][co] = W[8 - tap'][ci][co] --
+// Keras HWIO [tap][ci][co] already has co (the dgrad K) contiguous: only the tap order reverses. rows [r0, r0+nr) of ci.
+__global__ void pack_dgrad_weights_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ dst, int cin, int cout) {
+  const size_t total = size_t(9) * cin * cout;
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < total; i += size_t(gridDim.x) * blockDim.x) {
+    const size_t tap = i / (size_t(cin) * cout);
+    const size_t rem = i - tap * size_t(cin) * cout;
+    dst[i] = __float2bfloat16_rn(w[(8 - tap) * size_t(cin) * cout + rem]);
+  }
+}
+
+__global__ void fill_kernel(float* __restrict__ p, size_t n, float v) {
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n; i += size_t(gridDim.x) * blockDim.x) p[i] = v;
+}
+
+}  // namespace itmo

@@ -1,0 +1,198 @@
+// wgrad_igemm.cuh — weight-gradient implicit GEMM of the training step (main.py:126-132, model.py:281) on sm_100a.
+//
+// For a 3x3 'same' convolution (ConvBN, model.py:195-196)
+//     dW[ky][kx][ci][co] = sum over (n, y, x) of  X[n, y+ky-1, x+kx-1, ci] * G[n, y, x, co]
+// and for the 2x2 stride-2 transposed convolution (ConvBNTranspose, model.py:199-200), per kernel row a,
+//     dW[a][b][co][ci]   = sum over (n, i, j) of  G[n, 2i+a, 2j+b, co] * X[n, i, j, ci]
+// Both are GEMMs whose reduction (K) dimension is the PIXEL index: D[m][n] = sum_p A[p][m] * B[p][n]. In NHWC
+// memory the channels of a pixel are contiguous, so both operands are "MN-major" for the tensor core: the kernel
+// feeds tcgen05.mma straight from the TMA-written pixel tiles with MN-major shared-memory descriptors (SWIZZLE_128B:
+// one 128-byte row = 64 bf16 channels of one pixel, 8 pixels = one swizzle atom), no transposition pass.
+//
+//   A (M side, 128 rows) : the tensor that is read SHIFTED per tap (X for the 3x3 conv; for the transposed conv the
+//                          gradient viewed as [n, H, W, (b,co)] has a single tap). One TMA box per 64 channels brings a
+//                          16 x (8+2*pad) pixel tile; the taps of one kernel row are start-address shifts of whole
+//                          pixels inside that tile (zero fill outside the image = 'same' padding).
+//   B (N side, BN columns): the unshifted tensor, 16 x 8 pixel tile.
+//   K block              : 128 pixels (16 rows x 8 columns) = 8 MMAs of K = 16 (two pixel rows each).
+//
+// A CTA owns one output tile (128 A-channels x BN B-channels x the TG taps of one kernel row: TG accumulators of
+// BN fp32 columns in TMEM) and one slice of the pixel range (split-K over CTAs so that tiles x slices ~ SM count);
+// it adds its partial tile into the fp32 gradient tensor with red.global.add. The gradient buffer therefore
+// accumulates across launches (micro-batches) until the optimizer step zeroes it.
+#pragma once
+#include <cuda_bf16.h>
+#include "sm100_ptx.cuh"
+
+namespace itmo {
+
+constexpr int kWgThreads = 192;   // warp 0 TMA, warp 1 MMA + TMEM alloc, warps 2..5 epilogue
+constexpr int kWgMaxStages = 4;
+constexpr int kWgBoxPixB = 16 * 8;           // pixels of a B box
+constexpr int kWgRowBytes = 128;             // 64 bf16 channels
+
+struct WgradParams {
+  CUtensorMap tmA;   // dims (Ca, W, H, N), box (64, 8 + 2*pad, 16, 1), SWIZZLE_128B
+  CUtensorMap tmB;   // dims (Cb, W, H, N), box (64, 8, 16, 1), SWIZZLE_128B
+  int H, W, NB;      // spatial size / batch of the (common) pixel grid
+  int pad;           // 1: 3x3 conv (taps shift A by -1..1), 0: single tap
+  int tg;            // taps per tile = accumulators (3 or 1)
+  int n_groups;      // kernel rows (3 or 1)
+  int m_blocks;      // ceil(Ca / 128)
+  int n_blocks;      // Cb / BN
+  int a_boxes;       // 64-channel boxes of A per stage (1 or 2)
+  int b_boxes;       // 64-channel boxes of B per stage (ceil(BN / 64))
+  int a_box_bytes;   // 16 * (8 + 2*pad) * 128
+  int stage_bytes;
+  int n_stages;
+  int ksplit;        // pixel-range slices
+  int ca;            // valid A channels (rows written)
+  float* dw;         // [n_groups*tg][ld_m][ld_n] fp32, accumulated
+  int ld_m, ld_n;    // rows / columns of one tap's matrix
+  int m_off, n_off;  // where this launch's (A-channel, B-channel) block starts inside it
+};
+
+__device__ __forceinline__ uint32_t wg_desc_lo(uint32_t smem_addr, uint32_t lbo_bytes) {
+  return ((smem_addr & 0x3FFFFu) >> 4) | (((lbo_bytes >> 4) & 0x3FFFu) << 16);
+}
+__device__ __forceinline__ uint32_t wg_desc_hi(uint32_t sbo_bytes) {
+  return ((sbo_bytes >> 4) & 0x3FFFu) | (1u << 14) | (2u << 29);   // version 1, SWIZZLE_128B
+}
+
+template <int BN>
+__global__ void __launch_bounds__(kWgThreads, 1) wgrad_igemm_kernel(const __grid_constant__ WgradParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw_addr = sm100::smem_u32(smem_raw);
+  uint8_t* smem = smem_raw + (((raw_addr + 1023u) & ~1023u) - raw_addr);
+  uint8_t* aux = smem + p.n_stages * p.stage_bytes;
+  uint64_t* full = reinterpret_cast<uint64_t*>(aux);
+  uint64_t* empty = full + kWgMaxStages;
+  uint64_t* tmem_full = empty + kWgMaxStages;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_full + 1);
+
+  const int warp_idx = __shfl_sync(0xFFFFFFFFu, threadIdx.x >> 5, 0);
+  const int lane = threadIdx.x & 31;
+
+  // tile / slice of this CTA
+  const int split = blockIdx.x % p.ksplit;
+  int tile = blockIdx.x / p.ksplit;
+  const int nb = tile % p.n_blocks;
+  tile /= p.n_blocks;
+  const int mb = tile % p.m_blocks;
+  const int g = tile / p.m_blocks;
+
+  const int tiles_x = p.W / 8, tiles_y = p.H / 16;
+  const long long pb_total = (long long)p.NB * tiles_y * tiles_x;
+  const int pb_beg = int(pb_total * split / p.ksplit);
+  const int pb_end = int(pb_total * (split + 1) / p.ksplit);
+  const int halo_w = 8 + 2 * p.pad;
+  uint32_t tmem_cols = 32;
+  while (tmem_cols < uint32_t(p.tg * BN)) tmem_cols <<= 1;
+
+  if (warp_idx == 0 && lane == 0) {
+    sm100::tma_prefetch_desc(&p.tmA);
+    sm100::tma_prefetch_desc(&p.tmB);
+    for (int i = 0; i < kWgMaxStages; ++i) {
+      sm100::mbar_init(&full[i], 1);
+      sm100::mbar_init(&empty[i], 1);
+    }
+    sm100::mbar_init(tmem_full, 1);
+    sm100::fence_barrier_init();
+  }
+  if (warp_idx == 1) sm100::tmem_alloc(tmem_ptr_smem, tmem_cols);
+  sm100::tc_fence_before_sync();
+  __syncthreads();
+  sm100::tc_fence_after_sync();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  if (warp_idx == 0) {
+    if (sm100::elect_one()) {
+      const uint32_t bytes = uint32_t(p.a_boxes * p.a_box_bytes + p.b_boxes * kWgBoxPixB * kWgRowBytes);
+      int s = 0;
+      uint32_t ph = 0;
+      for (int pb = pb_beg; pb < pb_end; ++pb) {
+        const int tx = pb % tiles_x;
+        const int t2 = pb / tiles_x;
+        const int ty = t2 % tiles_y;
+        const int img = t2 / tiles_y;
+        sm100::mbar_wait(&empty[s], ph ^ 1);
+        uint8_t* st = smem + s * p.stage_bytes;
+        sm100::mbar_arrive_expect_tx(&full[s], bytes);
+        for (int j = 0; j < p.a_boxes; ++j)
+          sm100::tma_load_4d(st + j * p.a_box_bytes, &p.tmA, &full[s], mb * 128 + j * 64, tx * 8 - p.pad,
+                             ty * 16 + g - p.pad, img, sm100::kEvictNormal);
+        uint8_t* sb = st + p.a_boxes * p.a_box_bytes;
+        for (int j = 0; j < p.b_boxes; ++j)
+          sm100::tma_load_4d(sb + j * kWgBoxPixB * kWgRowBytes, &p.tmB, &full[s], nb * BN + j * 64, tx * 8, ty * 16, img,
+                             sm100::kEvictNormal);
+        if (++s == p.n_stages) {
+          s = 0;
+          ph ^= 1;
+        }
+      }
+    }
+  } else if (warp_idx == 1) {
+    if (sm100::elect_one()) {
+      // both operands MN-major (bits 15, 16)
+      constexpr uint32_t idesc = sm100::make_idesc(sm100::kFmtBF16, 128, BN) | (1u << 15) | (1u << 16);
+      const uint32_t a_hi = wg_desc_hi(uint32_t(halo_w) * kWgRowBytes);   // next 8 pixels of K: one tile row down
+      const uint32_t b_hi = wg_desc_hi(8u * kWgRowBytes);
+      const uint32_t a_lbo = uint32_t(p.a_box_bytes);                      // next 64 channels: the next box
+      const uint32_t b_lbo = uint32_t(kWgBoxPixB * kWgRowBytes);
+      int s = 0;
+      uint32_t ph = 0;
+      for (int pb = pb_beg; pb < pb_end; ++pb) {
+        sm100::mbar_wait(&full[s], ph);
+        sm100::tc_fence_after_sync();
+        const uint32_t a_addr = sm100::smem_u32(smem + s * p.stage_bytes);
+        const uint32_t b_addr = a_addr + uint32_t(p.a_boxes * p.a_box_bytes);
+        const uint32_t a_lo = wg_desc_lo(a_addr, a_lbo);
+        const uint32_t b_lo = wg_desc_lo(b_addr, b_lbo);
+        for (int t = 0; t < p.tg; ++t) {
+#pragma unroll
+          for (int ks = 0; ks < 8; ++ks) {
+            const uint64_t da =
+                (uint64_t(a_hi) << 32) | uint64_t(a_lo + ((uint32_t((2 * ks * halo_w + t) * kWgRowBytes)) >> 4));
+            const uint64_t db = (uint64_t(b_hi) << 32) | uint64_t(b_lo + ((uint32_t(2 * ks * 8 * kWgRowBytes)) >> 4));
+            sm100::umma_ss<false>(tmem_base + uint32_t(t * BN), da, db, idesc, (pb != pb_beg || ks != 0) ? 1u : 0u);
+          }
+        }
+        sm100::umma_commit(&empty[s]);
+        if (++s == p.n_stages) {
+          s = 0;
+          ph ^= 1;
+        }
+      }
+      sm100::umma_commit(tmem_full);
+    }
+  } else if (pb_end > pb_beg) {
+    // epilogue: TMEM lane = A channel (row of dW), column = tap * BN + B channel
+    const int q = warp_idx & 3;
+    sm100::mbar_wait_relaxed(tmem_full, 0, 500);
+    sm100::tc_fence_after_sync();
+    const int row = mb * 128 + 32 * q + lane;
+    const uint32_t taddr = tmem_base + (uint32_t(32 * q) << 16);
+    for (int t = 0; t < p.tg; ++t) {
+      const int tap = g * p.tg + t;
+#pragma unroll 1
+      for (int chunk = 0; chunk < BN / 32; ++chunk) {
+        uint32_t v[32];
+        sm100::tmem_ld_32x32b_x32(taddr + uint32_t(t * BN + chunk * 32), v);
+        sm100::tmem_ld_wait();
+        if (row < p.ca) {
+          float* dst = p.dw + (size_t(tap) * p.ld_m + p.m_off + row) * p.ld_n + p.n_off + nb * BN + chunk * 32;
+#pragma unroll
+          for (int i = 0; i < 32; ++i) atomicAdd(dst + i, __uint_as_float(v[i]));
+        }
+      }
+    }
+  }
+  sm100::tc_fence_before_sync();
+  __syncthreads();
+  if (warp_idx == 1) {
+    sm100::tc_fence_after_sync();
+    sm100::tmem_dealloc(tmem_base, tmem_cols);
+  }
+}
+
+}  // namespace itmo

@@ -283,16 +283,89 @@ class Model:
         """model.save (what ModelCheckpoint calls every epoch, main.py:123-124): full Keras HDF5 layout."""
         if not overwrite and os.path.exists(filepath):
             raise OSError(f'{filepath} exists')
+        if getattr(self, '_trainer', None) is not None:
+            self._pull_trained_weights()
         checkpoint.write_checkpoint(filepath, self._weights, weights_only=False)
 
     # ---- training (main.py:126-132) -----------------------------------------------------------------
-    def train_on_batch(self, x, y):
-        raise NotImplementedError('the training step (forward + dgrad/wgrad + RMSprop, main.py:126-132) is not built '
-                                  'yet in this round; inference is complete')
+    def _ensure_trainer(self, micro_batch: Optional[int] = None):
+        """The training engine (train.Trainer over itmo_train_*), created on first use with the model's weights."""
+        from . import train
+        if getattr(self, '_trainer', None) is None:
+            if self.optimizer is None:
+                raise RuntimeError('You must compile a model before training/testing. Use `model.compile(optimizer, loss)`.')
+            opt = self.optimizer if isinstance(self.optimizer, str) else self.optimizer.get('name', 'rmsprop')
+            kw = {} if isinstance(self.optimizer, str) else {k: v for k, v in self.optimizer.items() if k != 'name'}
+            self._trainer = train.Trainer(self._weights, micro_batch=micro_batch or self.train_micro_batch,
+                                          device=self.device, optimizer=opt, **kw)
+        return self._trainer
+
+    train_micro_batch = 8
+
+    def _pull_trained_weights(self):
+        """Bring the trainer's parameters back into the host copy predict()/save() use."""
+        if getattr(self, '_trainer', None) is not None:
+            self._weights = self._trainer.get_weights()
+            self._uploaded = False
+
+    def train_on_batch(self, x, y, sample_weight=None, class_weight=None):
+        """One optimizer step on x [N,512,512,3] (floats in [0,1] like main.py:71's rescale=1./255, or raw uint8) and
+        the target y [N,512,512,3]; returns [loss, accuracy] like Keras with metrics=['accuracy']."""
+        x = self._check_input(x)
+        y = np.asarray(y)
+        if y.shape != x.shape:
+            raise ValueError(f'Error when checking target: expected conv2d_15 to have shape {x.shape[1:]} but got '
+                             f'array with shape {y.shape[1:]}')
+        out = self._ensure_trainer().train_on_batch(x, y)
+        self._trained_dirty = True
+        return out
 
     def fit_generator(self, generator, steps_per_epoch=None, epochs=1, verbose=1, callbacks=None,
                       validation_data=None, validation_steps=None, **kwargs):
-        raise NotImplementedError('fit_generator needs train_on_batch, which is not built yet in this round')
+        """model.fit_generator(train_generator, steps_per_epoch, epochs, validation_data, validation_steps, callbacks)
+        (main.py:126-132). `generator` yields (x, y) batches (main.py:111's zip of two flows). Callbacks: objects with
+        on_epoch_end(epoch, logs) (ModelCheckpoint / CSVLogger stand-ins). Returns {'loss': [...], 'acc': [...],
+        'val_loss': [...], 'val_acc': [...]} per epoch like History.history."""
+        if steps_per_epoch is None:
+            raise ValueError('steps_per_epoch is required for a generator')
+        history: Dict[str, List[float]] = {'loss': [], 'acc': []}
+        it = iter(generator)
+        for epoch in range(int(epochs)):
+            ls, ac = [], []
+            for _ in range(int(steps_per_epoch)):
+                x, y = next(it)
+                l, a = self.train_on_batch(x, y)
+                ls.append(l)
+                ac.append(a)
+            logs = {'loss': float(np.mean(ls)), 'acc': float(np.mean(ac))}
+            if validation_data is not None:
+                vit = iter(validation_data)
+                vl, va = [], []
+                for _ in range(int(validation_steps or 1)):
+                    vx, vy = next(vit)
+                    l, a = self.test_on_batch(vx, vy)
+                    vl.append(l)
+                    va.append(a)
+                logs['val_loss'], logs['val_acc'] = float(np.mean(vl)), float(np.mean(va))
+            for k, v in logs.items():
+                history.setdefault(k, []).append(v)
+            if verbose:
+                print(f'Epoch {epoch + 1}/{epochs} - ' + ' - '.join(f'{k}: {v:.4f}' for k, v in logs.items()))
+            for cb in callbacks or []:
+                if hasattr(cb, 'on_epoch_end'):
+                    cb.on_epoch_end(epoch, logs)
+        self._pull_trained_weights()
+        return history
+
+    def test_on_batch(self, x, y):
+        """[loss, accuracy] in inference mode (moving statistics), like Keras' test_on_batch."""
+        self._pull_trained_weights()
+        x = self._check_input(x)
+        y = np.asarray(y, np.float32)
+        pred = self.predict(np.asarray(x, np.float32) / (255.0 if np.asarray(x).dtype == np.uint8 else 1.0))
+        loss = float(np.mean((pred - y) ** 2))
+        acc = float(np.mean(pred.argmax(-1) == y.argmax(-1)))
+        return [loss, acc]
 
 
 def U_net(pretrained_weights=None, input_size=(512, 512, 3), precision: Optional[str] = None, device: int = 0,

@@ -1,0 +1,232 @@
+"""Training step of the U-Net behind the Keras surface the reference uses.
+
+    model = U_net()                                   # model.py:204, compiled rmsprop / mse / accuracy (model.py:281)
+    model.fit_generator(gen, steps_per_epoch=..., epochs=...)        # main.py:126-132
+    loss, acc = model.train_on_batch(x, y)
+
+``Trainer`` owns the flat fp32 parameter / gradient / optimizer-state buffers (torch CUDA tensors: PyTorch is used for
+device allocation, streams and torch.distributed only) and drives libitmo_b200.so's itmo_train_* entry points; every
+kernel of the step is in the library. Data parallel: one process per GPU, each rank runs its share of the batch
+(micro-batched), then ONE NCCL all-reduce (sum) of the flat gradient buffer over NVLink, then the same optimizer step on
+every rank. There is no CPU fallback.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+
+from . import _lib, graph
+
+_OPTIMIZERS = {'rmsprop': _lib.OPT_RMSPROP, 'adam': _lib.OPT_ADAM}
+# Keras defaults: RMSprop(lr=1e-3, rho=0.9, epsilon=1e-7) (model.py:281); Adam of the comments: beta_1=0.5 (model.py:280,282)
+_OPT_DEFAULTS = {'rmsprop': dict(lr=1e-3, beta1=0.9, beta2=0.0, eps=1e-7),
+                 'adam': dict(lr=1e-3, beta1=0.5, beta2=0.999, eps=1e-7)}
+WHICH = {'kernel': 0, 'bias': 1, 'gamma': 2, 'beta': 3}
+
+
+def param_layout() -> List[Dict[str, Tuple[int, int]]]:
+    """Per layer {field: (offset, count)} inside the flat parameter buffer; 'bn' = offset inside one half of bn_moving."""
+    lib = _lib.load()
+    out = []
+    for li, l in enumerate(graph.LAYERS):
+        d = {}
+        for name, which in (('kernel', 0), ('bias', 1), ('gamma', 2), ('beta', 3), ('bn', 4)):
+            if l.kind == 'head' and which >= 2:
+                continue
+            off, cnt = ctypes.c_longlong(), ctypes.c_longlong()
+            _lib.check(lib.itmo_train_layout(li, which, ctypes.byref(off), ctypes.byref(cnt)))
+            d[name] = (off.value, cnt.value)
+        out.append(d)
+    return out
+
+
+class Trainer:
+    def __init__(self, weights: Sequence[Dict[str, np.ndarray]], micro_batch: int = 8, image_hw=(512, 512),
+                 device: int = 0, optimizer: str = 'rmsprop', lr: Optional[float] = None, **opt_kwargs):
+        import torch
+        if not torch.cuda.is_available():
+            raise _lib.ItmoError('the training step needs an sm_100a GPU: there is no CPU fallback')
+        lib = _lib.load()
+        optimizer = optimizer.lower()
+        if optimizer not in _OPTIMIZERS:
+            raise ValueError(f'optimizer must be one of {sorted(_OPTIMIZERS)}, got {optimizer!r}')
+        self.optimizer = optimizer
+        self.opt = dict(_OPT_DEFAULTS[optimizer])
+        if lr is not None:
+            self.opt['lr'] = float(lr)
+        self.opt.update({k: float(v) for k, v in opt_kwargs.items() if k in self.opt})
+        self.device = int(device)
+        self.micro_batch = int(micro_batch)
+        self.h, self.w = int(image_hw[0]), int(image_hw[1])
+        self.layout = param_layout()
+        self.n_params = int(lib.itmo_train_param_count())
+        self.n_bn = int(lib.itmo_train_bn_count())
+        dev = torch.device('cuda', self.device)
+        self._torch = torch
+        self._dev = dev
+        self.params = torch.zeros(self.n_params, dtype=torch.float32, device=dev)
+        self.grads = torch.zeros(self.n_params, dtype=torch.float32, device=dev)
+        self.opt_state = torch.zeros(2 * self.n_params, dtype=torch.float32, device=dev)
+        self.bn_moving = torch.zeros(2 * self.n_bn, dtype=torch.float32, device=dev)
+        self._h = ctypes.c_void_p()
+        torch.cuda.synchronize(dev)
+        _lib.check(lib.itmo_trainer_create(ctypes.byref(self._h), self.device, self.micro_batch, self.h, self.w,
+                                           self.params.data_ptr(), self.grads.data_ptr(), self.opt_state.data_ptr(),
+                                           self.bn_moving.data_ptr()))
+        self.set_weights(weights)
+        self.step_index = 0
+
+    # ---- plumbing ---------------------------------------------------------------------------------------------
+    def _stream(self) -> int:
+        return self._torch.cuda.current_stream(self._dev).cuda_stream
+
+    def close(self):
+        if getattr(self, '_h', None):
+            _lib.load().itmo_trainer_destroy(self._h)
+            self._h = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:  # noqa: BLE001
+            pass
+
+    def set_weights(self, weights: Sequence[Dict[str, np.ndarray]]):
+        flat = np.zeros(self.n_params, np.float32)
+        mov = np.zeros(2 * self.n_bn, np.float32)
+        for li, lay in enumerate(self.layout):
+            w = weights[li]
+            for name in ('kernel', 'bias', 'gamma', 'beta'):
+                if name in lay:
+                    off, cnt = lay[name]
+                    flat[off:off + cnt] = np.asarray(w[name], np.float32).reshape(-1)
+            if 'bn' in lay:
+                off, cnt = lay['bn']
+                mov[off:off + cnt] = np.asarray(w['moving_mean'], np.float32)
+                mov[self.n_bn + off:self.n_bn + off + cnt] = np.asarray(w['moving_variance'], np.float32)
+        self.params.copy_(self._torch.from_numpy(flat))
+        self.bn_moving.copy_(self._torch.from_numpy(mov))
+        _lib.check(_lib.load().itmo_trainer_sync_weights(self._h, self._stream()))
+
+    def _unflatten(self, flat: np.ndarray, with_moving: bool) -> List[Dict[str, np.ndarray]]:
+        mov = self.bn_moving.cpu().numpy() if with_moving else None
+        out = []
+        for li, lay in enumerate(self.layout):
+            l = graph.LAYERS[li]
+            d = {}
+            for name in ('kernel', 'bias', 'gamma', 'beta'):
+                if name in lay:
+                    off, cnt = lay[name]
+                    a = flat[off:off + cnt].copy()
+                    d[name] = a.reshape(graph.kernel_shape(l)) if name == 'kernel' else a
+            if with_moving and 'bn' in lay:
+                off, cnt = lay['bn']
+                d['moving_mean'] = mov[off:off + cnt].copy()
+                d['moving_variance'] = mov[self.n_bn + off:self.n_bn + off + cnt].copy()
+            out.append(d)
+        return out
+
+    def get_weights(self) -> List[Dict[str, np.ndarray]]:
+        """Per-layer dicts in the Keras layouts (what checkpoint.write_checkpoint / Model take)."""
+        self._torch.cuda.synchronize(self._dev)
+        return self._unflatten(self.params.cpu().numpy(), True)
+
+    def get_grads(self) -> List[Dict[str, np.ndarray]]:
+        self._torch.cuda.synchronize(self._dev)
+        return self._unflatten(self.grads.cpu().numpy(), False)
+
+    # ---- the step ---------------------------------------------------------------------------------------------
+    def zero_grad(self):
+        _lib.check(_lib.load().itmo_train_zero_grad(self._h, self._stream()))
+
+    def backward(self, x_dev, y_dev, loss_count: float, seed: int = 0, dropout: bool = True,
+                 freeze_moving: bool = False, pred_dev=None):
+        """Forward (training mode) + backward of one micro-batch of DEVICE tensors: x uint8 or float32 [n,h,w,3],
+        y float32 [n,h,w,3]; gradients are added into self.grads."""
+        torch = self._torch
+        n = int(x_dev.shape[0])
+        if tuple(x_dev.shape[1:]) != (self.h, self.w, 3) or tuple(y_dev.shape) != tuple(x_dev.shape):
+            raise ValueError(f'expected x, y of shape (n, {self.h}, {self.w}, 3), got {tuple(x_dev.shape)} / '
+                             f'{tuple(y_dev.shape)}')
+        if x_dev.dtype not in (torch.uint8, torch.float32) or y_dev.dtype != torch.float32:
+            raise ValueError('x must be uint8 or float32 and y float32')
+        flags = (0 if dropout else _lib.TRAIN_NO_DROPOUT) | (_lib.TRAIN_FREEZE_MOVING if freeze_moving else 0)
+        _lib.check(_lib.load().itmo_train_backward(
+            self._h, x_dev.data_ptr(), _lib.DT_U8 if x_dev.dtype == torch.uint8 else _lib.DT_F32, y_dev.data_ptr(),
+            pred_dev.data_ptr() if pred_dev is not None else None, n, float(loss_count), int(seed) & 0xFFFFFFFF, flags,
+            self._stream()))
+
+    def allreduce_grads(self):
+        """The one exchange step of data-parallel training: sum of the flat gradient buffer over all ranks
+        (NCCL over NVLink when the process group's backend is nccl)."""
+        import torch.distributed as dist
+        if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+            dist.all_reduce(self.grads, op=dist.ReduceOp.SUM)
+
+    def update(self, grad_scale: float = 1.0):
+        o = self.opt
+        _lib.check(_lib.load().itmo_train_update(self._h, _OPTIMIZERS[self.optimizer], o['lr'], o['beta1'], o['beta2'],
+                                                 o['eps'], float(grad_scale), self._stream()))
+        self.step_index += 1
+
+    def metrics(self, reset: bool = True) -> Tuple[float, float]:
+        sq, hits = ctypes.c_double(), ctypes.c_double()
+        _lib.check(_lib.load().itmo_train_metrics(self._h, ctypes.byref(sq), ctypes.byref(hits), int(reset),
+                                                  self._stream()))
+        return sq.value, hits.value
+
+    def train_on_batch(self, x, y, seed: Optional[int] = None, dropout: bool = True) -> List[float]:
+        """One optimizer step on HOST arrays x [N,h,w,3] (uint8, or float in [0,1]) and y [N,h,w,3] (float target): this
+        rank's share of the batch. Returns [loss, accuracy] of the whole (all-rank) batch, like Keras' train_on_batch
+        with metrics=['accuracy']."""
+        import torch
+        import torch.distributed as dist
+        x = np.ascontiguousarray(x if np.asarray(x).dtype == np.uint8 else np.asarray(x, np.float32))
+        y = np.ascontiguousarray(np.asarray(y, np.float32))
+        n = x.shape[0]
+        world = dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
+        n_global = n * world
+        loss_count = float(n_global) * self.h * self.w * 3
+        seed = self.step_index if seed is None else seed
+        self.zero_grad()
+        for i0 in range(0, n, self.micro_batch):
+            xs = torch.from_numpy(x[i0:i0 + self.micro_batch]).to(self._dev, non_blocking=True)
+            ys = torch.from_numpy(y[i0:i0 + self.micro_batch]).to(self._dev, non_blocking=True)
+            self.backward(xs, ys, loss_count, seed=seed * 7919 + i0, dropout=dropout)
+        self.allreduce_grads()
+        self.update()
+        sq, hits = self.metrics()
+        if world > 1:
+            t = torch.tensor([sq, hits], dtype=torch.float64, device=self._dev)
+            dist.all_reduce(t)
+            sq, hits = float(t[0]), float(t[1])
+        return [sq / loss_count, hits / (n_global * self.h * self.w)]
+
+    def read_activation(self, layer: int, which: str, n: int) -> np.ndarray:
+        """z (ReLU output), a (BN/dropout output) or pooled tensor of the last micro-batch as float32 NHWC."""
+        l = graph.LAYERS[layer]
+        scale = 2 if l.kind == 'convT' else 1
+        ho, wo = scale * l.hin * self.h // 512, scale * l.hin * self.w // 512
+        idx = {'z': 0, 'a': 1, 'pooled': 2}[which]
+        if idx == 2:
+            ho, wo = ho // 2, wo // 2
+        buf = np.empty((n, ho, wo, l.cout), np.float32)
+        cnt = ctypes.c_size_t(0)
+        _lib.check(_lib.load().itmo_train_read_activation(self._h, layer, idx, n,
+                                                          buf.ctypes.data_as(ctypes.POINTER(ctypes.c_float)), buf.size,
+                                                          ctypes.byref(cnt)))
+        return buf
+
+    def set_profiling(self, enable: bool = True):
+        _lib.check(_lib.load().itmo_train_set_profiling(self._h, int(bool(enable))))
+
+    def phase_times(self, reset: bool = True) -> Dict[str, Tuple[float, int]]:
+        ms = (ctypes.c_double * 4)()
+        calls = (ctypes.c_longlong * 4)()
+        _lib.check(_lib.load().itmo_train_phase_times(self._h, ms, calls, int(reset)))
+        return {k: (float(ms[i]), int(calls[i])) for i, k in enumerate(('fwd_conv', 'dgrad', 'wgrad', 'other'))}
+
+    def launch_count(self) -> int:
+        return int(_lib.load().itmo_train_launch_count(self._h))

@@ -163,6 +163,63 @@ int itmo_predict_frames(itmo_ctx* ctx, const void* frames_dev, int n_frames, int
 int itmo_inverse_reinhard(const void* frames_u8_dev, void* hdr_f32_dev, int n_frames, int h, int w, int as_written,
                           double key, void* stats_scratch_dev, void* stream);
 
+/* ---- training step (BASELINE config 5) --------------------------------------------------------------
+ * Replaces the step Keras runs inside model.fit_generator(...) (main.py:126-132) for the model compiled at model.py:281
+ * (optimizer 'rmsprop', loss 'mse', metrics ['accuracy']): forward in training mode (BatchNormalization on batch
+ * statistics, Dropout(0.5) at model.py:226,239), mse, backward, optimizer update, BN moving statistics.
+ * bf16 activations / activation gradients with fp32 accumulation; fp32 parameters, gradients and optimizer state in
+ * FLAT buffers owned by the caller (device memory), laid out per layer as kernel (Keras layout), bias, gamma, beta —
+ * itmo_train_layout() gives the offsets — so a data-parallel run all-reduces ONE buffer (itmo_train_param_count()
+ * floats = 11,159,011, layers.txt "Trainable params"). bn_moving = [moving_mean | moving_variance], itmo_train_bn_count()
+ * floats each (2 x 3,904 = layers.txt "Non-trainable params: 7,808"). opt_state = 2 x itmo_train_param_count() floats. */
+typedef struct itmo_trainer itmo_trainer;
+enum itmo_train_flags {
+  ITMO_TRAIN_NO_DROPOUT = 1,   /* Dropout layers act as identity (parity tests against a deterministic oracle) */
+  ITMO_TRAIN_FREEZE_MOVING = 2 /* do not update moving_mean / moving_variance */
+};
+enum itmo_optimizer {
+  ITMO_OPT_RMSPROP = 0, /* model.py:281; Keras defaults lr 1e-3, rho 0.9, eps 1e-7 */
+  ITMO_OPT_ADAM = 1     /* model.py:280,282 (commented variants): beta_1 0.5 */
+};
+long long itmo_train_param_count(void);
+long long itmo_train_bn_count(void);
+/* which: 0 kernel, 1 bias, 2 gamma, 3 beta (offsets into params / grads), 4 = offset into one half of bn_moving */
+int itmo_train_layout(int layer, int which, long long* offset, long long* count);
+/* micro_batch images of h x w (h multiple of 256, w of 128; the reference trains at 512x512, main.py:96) fit the arena */
+int itmo_trainer_create(itmo_trainer** out, int device, int micro_batch, int h, int w, float* params_dev,
+                        float* grads_dev, float* opt_state_dev, float* bn_moving_dev);
+void itmo_trainer_destroy(itmo_trainer* t);
+/* Rebuild the tensor-core operand copies after the caller wrote params_dev (itmo_train_update does it itself). */
+int itmo_trainer_sync_weights(itmo_trainer* t, void* stream);
+int itmo_train_zero_grad(itmo_trainer* t, void* stream);
+/* Forward + backward of one micro-batch, gradients ADDED into grads_dev.
+ *  x: [n,h,w,3] uint8 (raw SDR, /255 fused) or float32 in [0,1]; y: [n,h,w,3] float32 target in [0,1];
+ *  pred (optional): float32 [n,h,w,3] network output; loss_count: number of output elements of the WHOLE batch the mse
+ *  averages over (all micro-batches of all ranks x h x w x 3), so summed gradients are the gradient of the batch mean;
+ *  seed: dropout seed of this micro-batch. Asynchronous on `stream`. */
+int itmo_train_backward(itmo_trainer* t, const void* x_dev, int x_dtype, const float* y_dev, float* pred_dev_or_null,
+                        int n, double loss_count, unsigned seed, unsigned flags, void* stream);
+/* The per-layer dropout seed itmo_train_backward derives from `seed` (layer 7 = conv2d_8/drop4, 9 = conv2d_10/drop5). */
+int itmo_train_dropout_seed(unsigned seed, int layer, unsigned* out);
+/* Sum of squared errors and number of 'accurate' pixels accumulated since the last reset (synchronises `stream`). */
+int itmo_train_metrics(itmo_trainer* t, double* sq_err_sum, double* hits, int reset, void* stream);
+/* Optimizer step on the flat buffers (gradients multiplied by grad_scale first), then itmo_trainer_sync_weights.
+ * RMSprop: beta1_or_rho = rho, beta2 unused. Adam: bias-corrected with the trainer's step counter. */
+int itmo_train_update(itmo_trainer* t, int optimizer, float lr, float beta1_or_rho, float beta2, float eps,
+                      float grad_scale, void* stream);
+/* Debug / parity: activation of the last micro-batch as float32; which 0 = ReLU(conv+b), 1 = BN(+dropout) output, 2 = pooled */
+int itmo_train_read_activation(itmo_trainer* t, int layer, int which, int n, float* dst_host, size_t cap_elems,
+                               size_t* n_elems);
+/* Device timing per phase: 0 forward convs, 1 data-gradient convs, 2 weight-gradient GEMMs, 3 everything else */
+int itmo_train_set_profiling(itmo_trainer* t, int enable);
+int itmo_train_phase_times(itmo_trainer* t, double* ms_sum4, long long* calls4, int reset);
+long long itmo_train_launch_count(const itmo_trainer* t);
+/* Stateless gradient operators of one ConvBN layer (bf16 NHWC device tensors, fp32 Keras-layout kernel on the device):
+ * dw [3][3][cin][cout] += sum_p x[p + tap] g[p];   dx = full correlation of g with the kernel. */
+int itmo_wgrad3x3(const void* x, int cin, const void* g, int cout, int n, int h, int w, float* dw, void* stream);
+int itmo_dgrad3x3(const void* g, int cout, int n, int h, int w, const float* kernel_hwio, int cin, void* dx,
+                  void* stream);
+
 #ifdef __cplusplus
 }
 #endif

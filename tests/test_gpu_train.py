@@ -1,0 +1,245 @@
+"""GPU parity tests of the training step (run with ``-m gpu`` on a B200): the CUDA path through the C ABI
+(itmo_train_* / itmo_wgrad3x3 / itmo_dgrad3x3 of include/itmo_b200.h) against the CPU oracle
+(oracle/unet_train_ref.py: torch-CPU autograd over the graph of model.py:204-278 in training mode, main.py:126-132).
+
+Tolerances. The device keeps activations and activation gradients in bf16 (8 mantissa bits) with fp32 accumulation, so:
+  * stateless wgrad / dgrad on bf16-exact inputs: fp32-accumulation error only, relative L2 <= 2e-3 (dgrad output is
+    stored in bf16: <= 6e-3);
+  * whole step against the fp32 oracle: loss within 2 %, every parameter-gradient tensor relative L2 error <= 0.12 and
+    cosine >= 0.99 (rounding of ~35 chained bf16 tensors);
+  * optimizer update against the restated Keras RMSprop / Adam on the device's own gradients: 1e-5 relative.
+Nothing here reads /root/reference.
+"""
+import ctypes
+
+import numpy as np
+import pytest
+
+from oracle import unet_ref as R
+from oracle import unet_train_ref as T
+
+pytestmark = pytest.mark.gpu
+
+torch = pytest.importorskip('torch')
+
+
+def _lib():
+    from cnn_itmo_b200 import _lib as L
+    return L, L.load()
+
+
+@pytest.fixture(scope='module')
+def dev():
+    assert torch.cuda.is_available(), 'the gpu tests need a CUDA device'
+    cap = torch.cuda.get_device_capability(0)
+    assert cap[0] == 10, f'libitmo_b200 only contains sm_100a code; device is sm_{cap[0]}{cap[1]}'
+    return torch.device('cuda:0')
+
+
+def _rel(a, b):
+    a = np.asarray(a, np.float64).ravel()
+    b = np.asarray(b, np.float64).ravel()
+    return float(np.linalg.norm(a - b) / max(np.linalg.norm(b), 1e-30))
+
+
+def _cos(a, b):
+    a = np.asarray(a, np.float64).ravel()
+    b = np.asarray(b, np.float64).ravel()
+    return float(a @ b / max(np.linalg.norm(a) * np.linalg.norm(b), 1e-30))
+
+
+# ---- stateless gradient operators ---------------------------------------------------------------------------------
+WG_SHAPES = [  # (cin, cout, n, h, w)
+    (32, 32, 2, 32, 16), (32, 64, 1, 16, 24), (64, 64, 2, 16, 16), (64, 128, 1, 32, 8), (128, 128, 3, 16, 8),
+    (128, 256, 1, 16, 16), (256, 256, 2, 16, 8), (256, 512, 1, 16, 8), (512, 512, 1, 16, 16), (512, 32, 1, 16, 8),
+]
+
+
+@pytest.mark.parametrize('cin,cout,n,h,w', WG_SHAPES)
+def test_wgrad3x3_matches_autograd(dev, cin, cout, n, h, w):
+    L, lib = _lib()
+    g = torch.Generator().manual_seed(cin * 1000 + cout)
+    x = torch.randn(n, h, w, cin, generator=g).to(torch.bfloat16)
+    gy = torch.randn(n, h, w, cout, generator=g).to(torch.bfloat16)
+    xd, gd = x.to(dev), gy.to(dev)
+    dw = torch.zeros(3, 3, cin, cout, dtype=torch.float32, device=dev)
+    for _ in range(2):   # the operator ACCUMULATES: two launches = 2x
+        L.check(lib.itmo_wgrad3x3(xd.data_ptr(), cin, gd.data_ptr(), cout, n, h, w, dw.data_ptr(), None))
+    torch.cuda.synchronize()
+    k = torch.zeros(cout, cin, 3, 3, dtype=torch.float64, requires_grad=True)
+    y = torch.nn.functional.conv2d(x.double().permute(0, 3, 1, 2), k, padding=1)
+    y.backward(gy.double().permute(0, 3, 1, 2))
+    ref = 2.0 * k.grad.permute(2, 3, 1, 0).numpy()   # OIHW -> HWIO
+    got = dw.cpu().numpy()
+    assert _rel(got, ref) <= 2e-3, f'wgrad rel err {_rel(got, ref):.3e}'
+
+
+@pytest.mark.parametrize('cin,cout,n,h,w', WG_SHAPES[:8])
+def test_dgrad3x3_matches_autograd(dev, cin, cout, n, h, w):
+    L, lib = _lib()
+    g = torch.Generator().manual_seed(cin * 77 + cout)
+    gy = torch.randn(n, h, w, cout, generator=g).to(torch.bfloat16)
+    k = (torch.randn(3, 3, cin, cout, generator=g) / np.sqrt(9 * cout)).to(torch.bfloat16).float()
+    gd, kd = gy.to(dev), k.to(dev)
+    dx = torch.zeros(n, h, w, cin, dtype=torch.bfloat16, device=dev)
+    L.check(lib.itmo_dgrad3x3(gd.data_ptr(), cout, n, h, w, kd.data_ptr(), cin, dx.data_ptr(), None))
+    torch.cuda.synchronize()
+    xin = torch.zeros(n, cin, h, w, dtype=torch.float64, requires_grad=True)
+    y = torch.nn.functional.conv2d(xin, k.double().permute(3, 2, 0, 1), padding=1)
+    y.backward(gy.double().permute(0, 3, 1, 2))
+    ref = xin.grad.permute(0, 2, 3, 1).numpy()
+    got = dx.float().cpu().numpy()
+    assert _rel(got, ref) <= 6e-3, f'dgrad rel err {_rel(got, ref):.3e}'
+
+
+# ---- whole training step ------------------------------------------------------------------------------------------
+H, W, NB = 256, 128, 2   # smallest image the tile shapes allow (deepest level 16x8)
+
+
+def _weights(seed=3):
+    """he_normal-like weights with non-trivial BN affine parameters (so dgamma / dbeta paths are exercised)."""
+    ws = R.synthetic_weights(seed)
+    rng = np.random.default_rng(seed)
+    for w in ws:
+        if 'gamma' in w:
+            w['gamma'] = (1.0 + 0.1 * rng.standard_normal(w['gamma'].shape)).astype(np.float32)
+            w['beta'] = (0.2 + 0.1 * rng.standard_normal(w['beta'].shape)).astype(np.float32)
+    return ws
+
+
+@pytest.fixture(scope='module')
+def step_case(dev):
+    from cnn_itmo_b200 import train
+    ws = _weights()
+    x, y = T.synthetic_pair(NB, H, W, seed=11)
+    tr = train.Trainer(ws, micro_batch=NB, image_hw=(H, W), device=0)
+    return ws, x, y, tr
+
+
+def _run_backward(tr, x, y, dev, seed, dropout):
+    tr.zero_grad()
+    tr.metrics(reset=True)
+    xd = torch.from_numpy(x).to(dev)
+    yd = torch.from_numpy(y).to(dev)
+    pred = torch.empty(y.shape, dtype=torch.float32, device=dev)
+    tr.backward(xd, yd, float(y.size), seed=seed, dropout=dropout, freeze_moving=True, pred_dev=pred)
+    sq, hits = tr.metrics(reset=True)
+    return sq, hits, pred.cpu().numpy(), tr.get_grads()
+
+
+def _check_grads(got, ref, tol_rel, tol_cos):
+    bad = []
+    for li, (g, r) in enumerate(zip(got, ref)):
+        for name in ('kernel', 'bias', 'gamma', 'beta'):
+            if name not in r:
+                continue
+            rel, cos = _rel(g[name], r[name]), _cos(g[name], r[name])
+            if not (rel <= tol_rel and cos >= tol_cos):
+                bad.append(f'layer {li} {name}: rel {rel:.3e} cos {cos:.5f}')
+    assert not bad, '\n'.join(bad)
+
+
+def test_param_layout_matches_layers_txt():
+    L, lib = _lib()
+    assert lib.itmo_train_param_count() == R.param_count()['trainable'] == 11159011
+    assert 2 * lib.itmo_train_bn_count() == R.param_count()['non_trainable'] == 7808
+
+
+def test_train_forward_activations(step_case, dev):
+    ws, x, y, tr = step_case
+    _run_backward(tr, x, y, dev, seed=0, dropout=False)
+    ref = T.train_forward_backward(ws, x.astype(np.float32) / 255.0, y, None, return_acts=True)
+    for li in (0, 1, 2, 7, 9, 10, 11, 16, 17):
+        for which in ('z', 'a'):
+            got = tr.read_activation(li, which, NB)
+            r = ref[which][li]
+            assert _rel(got, r) <= 0.03, f'layer {li} {which}: rel {_rel(got, r):.3e}'
+
+
+def test_train_step_gradients_no_dropout(step_case, dev):
+    ws, x, y, tr = step_case
+    sq, hits, pred, grads = _run_backward(tr, x, y, dev, seed=0, dropout=False)
+    ref = T.train_forward_backward(ws, x.astype(np.float32) / 255.0, y, None)
+    assert abs(sq - ref['sq_err_sum']) <= 0.02 * ref['sq_err_sum']
+    assert abs(hits / (NB * H * W) - ref['acc']) <= 0.02
+    assert R.psnr(pred, ref['pred']) >= 35.0
+    _check_grads(grads, ref['grads'], 0.12, 0.99)
+
+
+def test_train_step_gradients_with_dropout(step_case, dev):
+    ws, x, y, tr = step_case
+    sq, hits, pred, grads = _run_backward(tr, x, y, dev, seed=1234, dropout=True)
+    ref = T.train_forward_backward(ws, x.astype(np.float32) / 255.0, y, 1234)
+    assert abs(sq - ref['sq_err_sum']) <= 0.02 * ref['sq_err_sum']
+    _check_grads(grads, ref['grads'], 0.12, 0.99)
+    # and the mask really was applied: the same step without dropout differs
+    sq2, _, _, _ = _run_backward(tr, x, y, dev, seed=1234, dropout=False)
+    assert abs(sq2 - sq) > 1e-6 * sq
+
+
+def test_gradient_accumulates_over_micro_batches(step_case, dev):
+    """Two micro-batches with the whole batch's loss_count accumulate; BN statistics are per micro-batch."""
+    ws, x, y, tr = step_case
+    tr.zero_grad()
+    for i in range(NB):
+        tr.backward(torch.from_numpy(x[i:i + 1]).to(dev), torch.from_numpy(y[i:i + 1]).to(dev), float(y.size), seed=0,
+                    dropout=False, freeze_moving=True)
+    got = tr.get_grads()
+    ref = [None] * NB
+    for i in range(NB):
+        ref[i] = T.train_forward_backward(ws, x[i:i + 1].astype(np.float32) / 255.0, y[i:i + 1], None,
+                                          loss_count=float(y.size))['grads']
+    summed = [{k: ref[0][li][k] + ref[1][li][k] for k in ref[0][li]} for li in range(len(ref[0]))]
+    _check_grads(got, summed, 0.12, 0.99)
+
+
+@pytest.mark.parametrize('opt', ['rmsprop', 'adam'])
+def test_optimizer_update_and_moving_stats(dev, opt):
+    from cnn_itmo_b200 import train
+    ws = _weights(5)
+    x, y = T.synthetic_pair(NB, H, W, seed=12)
+    tr = train.Trainer(ws, micro_batch=NB, image_hw=(H, W), device=0, optimizer=opt)
+    p0 = tr.params.cpu().numpy().astype(np.float64)
+    mov0 = tr.bn_moving.cpu().numpy().astype(np.float64)
+    tr.zero_grad()
+    tr.backward(torch.from_numpy(x).to(dev), torch.from_numpy(y).to(dev), float(y.size), seed=0, dropout=False)
+    g = tr.grads.cpu().numpy().astype(np.float64)
+    tr.update()
+    p1 = tr.params.cpu().numpy().astype(np.float64)
+    if opt == 'rmsprop':
+        want, _ = T.rmsprop_step(p0, g, np.zeros_like(p0), **T.RMSPROP_DEFAULTS)
+    else:
+        want, _, _ = T.adam_step(p0, g, np.zeros_like(p0), np.zeros_like(p0), 1, **T.ADAM_COMMENT_DEFAULTS)
+    # fp32 arithmetic on the device; updates are O(lr) so compare the deltas
+    assert np.abs((p1 - p0) - (want - p0)).max() <= 2e-5 * np.abs(want - p0).max() + 1e-9
+    # moving statistics of the first and a deep layer against the oracle's batch statistics
+    ref = T.train_forward_backward(ws, x.astype(np.float32) / 255.0, y, None)
+    mov1 = tr.bn_moving.cpu().numpy().astype(np.float64)
+    nbn = tr.n_bn
+    for li in (0, 9, 17):
+        off, cnt = tr.layout[li]['bn']
+        l = R.LAYERS[li]
+        scale = 2 if l.kind == 'convT' else 1
+        count = NB * (scale * l.hin * H // 512) * (scale * l.hin * W // 512)
+        mm, mv = T.moving_update(mov0[off:off + cnt], mov0[nbn + off:nbn + off + cnt], ref['batch_mean'][li],
+                                 ref['batch_var'][li], count)
+        assert np.abs(mov1[off:off + cnt] - mm).max() <= 2e-3 * max(1.0, np.abs(mm).max())
+        assert np.abs(mov1[nbn + off:nbn + off + cnt] - mv).max() <= 2e-3 * max(1.0, np.abs(mv).max())
+    tr.close()
+
+
+def test_loss_decreases_and_model_api(dev):
+    """Model.train_on_batch (the Keras surface, main.py:126-132) drives the same engine; a few steps on one batch must
+    reduce the mse, and the trained weights flow back into predict()."""
+    import cnn_itmo_b200 as M
+    m = M.Model(M.initial_weights(7), precision='bf16', max_batch=2)
+    m.compile(optimizer='rmsprop', loss='mse', metrics=['accuracy'])
+    m.train_micro_batch = 2
+    x, y = T.synthetic_pair(2, 512, 512, seed=21)
+    losses = [m.train_on_batch(x, y)[0] for _ in range(6)]
+    assert all(np.isfinite(losses)), losses
+    assert losses[-1] < losses[0], losses
+    m._pull_trained_weights()
+    out = m.predict(x.astype(np.float32) / 255.0)
+    assert out.shape == (2, 512, 512, 3) and np.isfinite(out).all()
+    m.close()
