@@ -115,7 +115,10 @@ int run_wgrad(const WgradArgs& a, cudaStream_t stream) {
   p.b_boxes = (bn + 63) / 64;
   p.a_box_bytes = 16 * (8 + 2 * p.pad) * itmo::kWgRowBytes;
   p.stage_bytes = p.a_boxes * p.a_box_bytes + p.b_boxes * itmo::kWgBoxPixB * itmo::kWgRowBytes;
-  p.n_stages = std::min(itmo::kWgMaxStages, (itmo::kSmemLimit - 2048) / p.stage_bytes);
+  // With one A box the MMA (always M = 128) still reads a second 64-channel group one box further on: its rows are
+  // never stored, but the read must stay inside the allocation -> one box of slack after the last stage.
+  const int slack = p.a_boxes == 1 ? p.a_box_bytes : 0;
+  p.n_stages = std::min(itmo::kWgMaxStages, (itmo::kSmemLimit - 2048 - slack) / p.stage_bytes);
   if (p.n_stages < 2) return fail(ITMO_ERR_INVALID, "wgrad: stage does not fit");
   const int tiles = p.n_groups * p.m_blocks * p.n_blocks;
   const long long pb_total = (long long)a.n * (a.h / 16) * (a.w / 8);
@@ -126,7 +129,7 @@ int run_wgrad(const WgradArgs& a, cudaStream_t stream) {
   p.ld_n = a.ld_n;
   p.m_off = a.m_off;
   p.n_off = a.n_off;
-  const int smem = 1024 + p.n_stages * p.stage_bytes + 256;
+  const int smem = 1024 + p.n_stages * p.stage_bytes + slack + 256;
   const int grid = tiles * p.ksplit;
   switch (bn) {
     case 32: return launch_wgrad_t<32>(p, grid, smem, stream);
@@ -156,6 +159,8 @@ struct itmo_trainer {
   __nv_bfloat16* a[ITMO_NUM_LAYERS] = {};     // BN (+dropout) output
   __nv_bfloat16* pooled[ITMO_NUM_LAYERS] = {};
   __nv_bfloat16* dskip[ITMO_NUM_LAYERS] = {};
+  __nv_bfloat16* dbg_dA[ITMO_NUM_LAYERS] = {};   // ITMO_TRAIN_KEEP_GRADS: copy of each layer's dL/da (parity tests)
+  __nv_bfloat16* dbg_dpre[ITMO_NUM_LAYERS] = {};
   __nv_bfloat16* x32 = nullptr;
   __nv_bfloat16* g[2] = {};     // ping-pong activation gradients
   __nv_bfloat16* gp = nullptr;  // dpre
@@ -180,7 +185,8 @@ struct PhaseStamp {
   itmo_trainer* t;
   cudaStream_t s;
   cudaEvent_t end = nullptr;
-  PhaseStamp(itmo_trainer* t_, int phase, cudaStream_t s_) : t(t_), s(s_) {
+  int phase, line;
+  PhaseStamp(itmo_trainer* t_, int phase_, cudaStream_t s_, int line_ = 0) : t(t_), s(s_), phase(phase_), line(line_) {
     t->launches++;
     if (!t->profiling) return;
     cudaEvent_t beg;
@@ -191,6 +197,12 @@ struct PhaseStamp {
   }
   ~PhaseStamp() {
     if (end) cudaEventRecord(end, s);
+    static const int dbg_sync = env_int("ITMO_TRAIN_SYNC", 0);   // debug: find the launch that faults
+    if (dbg_sync) {
+      cudaError_t e = cudaStreamSynchronize(s);
+      fprintf(stderr, "itmo train: launch group %lld (phase %d, line %d): %s\n", t->launches, phase, line,
+              cudaGetErrorString(e));
+    }
   }
 };
 
@@ -222,7 +234,7 @@ int train_forward(itmo_trainer* t, const void* x, int x_dtype, int nb, int flags
     const LayerDef& L = kLayers[li];
     const int hi = lay_hin(t, L), wi = lay_win(t, L), ho = lay_hout(t, L), wo = lay_wout(t, L);
     if (L.kind == kRgbConv) {
-      PhaseStamp ps(t, kPhFwdConv, s);
+      PhaseStamp ps(t, kPhFwdConv, s, __LINE__);
       int rc = run_rgb_conv(ITMO_PREC_BF16, x, x_dtype, nb, hi, wi, t->params + lay.kernel[li], t->params + lay.bias[li],
                             ones, zeros, t->z[li], nullptr, s);
       if (rc) return rc;
@@ -245,14 +257,14 @@ int train_forward(itmo_trainer* t, const void* x, int x_dtype, int nb, int flags
       a.cout = L.cout;
       a.out = t->z[li];
       a.head_dtype = itmo::kHeadNone;
-      PhaseStamp ps(t, kPhFwdConv, s);
+      PhaseStamp ps(t, kPhFwdConv, s, __LINE__);
       int rc = run_conv(a, s);
       if (rc) return rc;
     }
     const size_t npix = size_t(nb) * ho * wo;
     const bool dropout = (li == 7 || li == 9) && !(flags & ITMO_TRAIN_NO_DROPOUT);
     {
-      PhaseStamp ps(t, kPhOther, s);
+      PhaseStamp ps(t, kPhOther, s, __LINE__);
       itmo::bn_stats_kernel<<<int(std::min<size_t>(num_sms() * 4, (npix + 63) / 64)), 256, 0, s>>>(t->z[li], npix, L.cout,
                                                                                                  fstats(t, li));
       itmo::bn_finalize_kernel<<<(L.cout + 127) / 128, 128, 0, s>>>(
@@ -278,7 +290,7 @@ int train_backward(itmo_trainer* t, const void* x, int x_dtype, const float* y, 
   // head (layer 18): loss, accuracy, d a[17], head parameter gradients
   {
     const size_t npix = size_t(nb) * t->H * t->W;
-    PhaseStamp ps(t, kPhOther, s);
+    PhaseStamp ps(t, kPhOther, s, __LINE__);
     itmo::head_train_kernel<<<int(std::min<size_t>(num_sms() * 4, (npix + 127) / 128)), 128, 0, s>>>(
         t->a[17], y, (const float*)t->wfwd[18], t->params + lay.bias[18], npix, float(1.0 / loss_count), t->g[0], pred, t->metrics,
         t->grads + lay.kernel[18], t->grads + lay.bias[18]);
@@ -291,8 +303,16 @@ int train_backward(itmo_trainer* t, const void* x, int x_dtype, const float* y, 
     __nv_bfloat16* dA = t->g[(17 - li) & 1];
     __nv_bfloat16* dNext = t->g[(17 - li + 1) & 1];
     const bool dropout = (li == 7 || li == 9) && !(flags & ITMO_TRAIN_NO_DROPOUT);
+    if (flags & ITMO_TRAIN_KEEP_GRADS) {
+      if (!t->dbg_dA[li]) {
+        int rc = tr_alloc(t, &t->dbg_dA[li], size_t(t->cap) * ho * wo * L.cout);
+        if (rc == ITMO_OK) rc = tr_alloc(t, &t->dbg_dpre[li], size_t(t->cap) * ho * wo * L.cout);
+        if (rc) return rc;
+      }
+      ITMO_CUDA(cudaMemcpyAsync(t->dbg_dA[li], dA, npix * L.cout * 2, cudaMemcpyDeviceToDevice, s));
+    }
     {
-      PhaseStamp ps(t, kPhOther, s);
+      PhaseStamp ps(t, kPhOther, s, __LINE__);
       const int grid = int(std::min<size_t>(num_sms() * 4, (npix + 63) / 64));
       itmo::bn_bwd_reduce_kernel<<<grid, 256, 0, s>>>(dA, t->z[li], npix, L.cout, bnv(t, li, 0), bnv(t, li, 1),
                                                       t->drop_seed[li], dropout ? 1 : 0, bstats(t, li));
@@ -304,10 +324,12 @@ int train_backward(itmo_trainer* t, const void* x, int x_dtype, const float* y, 
       t->launches += 2;
       ITMO_CUDA(cudaGetLastError());
     }
+    if (flags & ITMO_TRAIN_KEEP_GRADS)
+      ITMO_CUDA(cudaMemcpyAsync(t->dbg_dpre[li], t->gp, npix * L.cout * 2, cudaMemcpyDeviceToDevice, s));
     // ---- weight gradient
     if (L.kind == kRgbConv) {
       {
-        PhaseStamp ps(t, kPhOther, s);
+        PhaseStamp ps(t, kPhOther, s, __LINE__);
         const size_t np = size_t(nb) * hi * wi;
         if (x_dtype == ITMO_DT_U8)
           itmo::rgb_to_c32_kernel<uint8_t><<<ew_grid(np * 4), 256, 0, s>>>((const uint8_t*)x, t->x32, np, 1.f);
@@ -329,7 +351,7 @@ int train_backward(itmo_trainer* t, const void* x, int x_dtype, const float* y, 
       w.dw = t->grads + lay.kernel[li];
       w.ld_m = 3;
       w.ld_n = L.cout;
-      PhaseStamp ps(t, kPhWgrad, s);
+      PhaseStamp ps(t, kPhWgrad, s, __LINE__);
       int rc = run_wgrad(w, s);
       if (rc) return rc;
     } else if (L.kind == kConv) {
@@ -348,7 +370,7 @@ int train_backward(itmo_trainer* t, const void* x, int x_dtype, const float* y, 
         w.ld_m = L.cin0 + L.cin1;
         w.ld_n = L.cout;
         w.m_off = src == 0 ? 0 : L.cin0;
-        PhaseStamp ps(t, kPhWgrad, s);
+        PhaseStamp ps(t, kPhWgrad, s, __LINE__);
         int rc = run_wgrad(w, s);
         if (rc) return rc;
       }
@@ -369,7 +391,7 @@ int train_backward(itmo_trainer* t, const void* x, int x_dtype, const float* y, 
         w.dw = t->grads + lay.kernel[li] + size_t(ph) * 2 * L.cout * L.cin0;
         w.ld_m = 2 * L.cout;
         w.ld_n = L.cin0;
-        PhaseStamp ps(t, kPhWgrad, s);
+        PhaseStamp ps(t, kPhWgrad, s, __LINE__);
         int rc = run_wgrad(w, s);
         if (rc) return rc;
       }
@@ -402,14 +424,14 @@ int train_backward(itmo_trainer* t, const void* x, int x_dtype, const float* y, 
         a.no_relu = 1;
         a.head_dtype = itmo::kHeadNone;
         {
-          PhaseStamp ps(t, kPhDgrad, s);
+          PhaseStamp ps(t, kPhDgrad, s, __LINE__);
           int rc = run_conv(a, s);
           if (rc) return rc;
         }
         if (src == 0 && L.src0_pooled) {
           const LayerDef& S = kLayers[sl];
           const int hs = lay_hout(t, S), ws = lay_wout(t, S);
-          PhaseStamp ps(t, kPhOther, s);
+          PhaseStamp ps(t, kPhOther, s, __LINE__);
           itmo::pool_bwd_add_kernel<<<ew_grid(size_t(nb) * (hs / 2) * (ws / 2) * (S.cout / 8)), 256, 0, s>>>(
               t->dskip[sl], t->gq, t->a[sl], dNext, nb, hs, ws, S.cout);
           ITMO_CUDA(cudaGetLastError());
@@ -438,7 +460,7 @@ int train_backward(itmo_trainer* t, const void* x, int x_dtype, const float* y, 
       a.out = dNext;
       a.no_relu = 1;
       a.head_dtype = itmo::kHeadNone;
-      PhaseStamp ps(t, kPhDgrad, s);
+      PhaseStamp ps(t, kPhDgrad, s, __LINE__);
       int rc = run_conv(a, s);
       if (rc) return rc;
     }
@@ -652,7 +674,11 @@ int itmo_train_read_activation(itmo_trainer* t, int layer, int which, int n, flo
   if (!t || !dst_host) return fail(ITMO_ERR_INVALID, "null argument");
   if (layer < 0 || layer >= 18) return fail(ITMO_ERR_INVALID, "layer out of range");
   const LayerDef& L = kLayers[layer];
-  const __nv_bfloat16* src = which == 0 ? t->z[layer] : which == 1 ? t->a[layer] : t->pooled[layer];
+  const __nv_bfloat16* src = which == 0   ? t->z[layer]
+                             : which == 1 ? t->a[layer]
+                             : which == 2 ? t->pooled[layer]
+                             : which == 3 ? t->dbg_dA[layer]
+                                          : t->dbg_dpre[layer];
   if (!src) return fail(ITMO_ERR_STATE, "tensor not materialised");
   size_t cnt = size_t(n) * lay_hout(t, L) * lay_wout(t, L) * L.cout;
   if (which == 2) cnt /= 4;

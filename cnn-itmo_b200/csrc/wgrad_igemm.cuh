@@ -64,7 +64,7 @@ __global__ void __launch_bounds__(kWgThreads, 1) wgrad_igemm_kernel(const __grid
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_addr = sm100::smem_u32(smem_raw);
   uint8_t* smem = smem_raw + (((raw_addr + 1023u) & ~1023u) - raw_addr);
-  uint8_t* aux = smem + p.n_stages * p.stage_bytes;
+  uint8_t* aux = smem + p.n_stages * p.stage_bytes + (p.a_boxes == 1 ? p.a_box_bytes : 0);   // slack: see run_wgrad
   uint64_t* full = reinterpret_cast<uint64_t*>(aux);
   uint64_t* empty = full + kWgMaxStages;
   uint64_t* tmem_full = empty + kWgMaxStages;

@@ -142,7 +142,7 @@ class Trainer:
         _lib.check(_lib.load().itmo_train_zero_grad(self._h, self._stream()))
 
     def backward(self, x_dev, y_dev, loss_count: float, seed: int = 0, dropout: bool = True,
-                 freeze_moving: bool = False, pred_dev=None):
+                 freeze_moving: bool = False, pred_dev=None, keep_grads: bool = False):
         """Forward (training mode) + backward of one micro-batch of DEVICE tensors: x uint8 or float32 [n,h,w,3],
         y float32 [n,h,w,3]; gradients are added into self.grads."""
         torch = self._torch
@@ -152,7 +152,8 @@ class Trainer:
                              f'{tuple(y_dev.shape)}')
         if x_dev.dtype not in (torch.uint8, torch.float32) or y_dev.dtype != torch.float32:
             raise ValueError('x must be uint8 or float32 and y float32')
-        flags = (0 if dropout else _lib.TRAIN_NO_DROPOUT) | (_lib.TRAIN_FREEZE_MOVING if freeze_moving else 0)
+        flags = (0 if dropout else _lib.TRAIN_NO_DROPOUT) | (_lib.TRAIN_FREEZE_MOVING if freeze_moving else 0) | \
+            (_lib.TRAIN_KEEP_GRADS if keep_grads else 0)
         _lib.check(_lib.load().itmo_train_backward(
             self._h, x_dev.data_ptr(), _lib.DT_U8 if x_dev.dtype == torch.uint8 else _lib.DT_F32, y_dev.data_ptr(),
             pred_dev.data_ptr() if pred_dev is not None else None, n, float(loss_count), int(seed) & 0xFFFFFFFF, flags,
@@ -209,7 +210,7 @@ class Trainer:
         l = graph.LAYERS[layer]
         scale = 2 if l.kind == 'convT' else 1
         ho, wo = scale * l.hin * self.h // 512, scale * l.hin * self.w // 512
-        idx = {'z': 0, 'a': 1, 'pooled': 2}[which]
+        idx = {'z': 0, 'a': 1, 'pooled': 2, 'dA': 3, 'dpre': 4}[which]
         if idx == 2:
             ho, wo = ho // 2, wo // 2
         buf = np.empty((n, ho, wo, l.cout), np.float32)

@@ -175,7 +175,8 @@ int itmo_inverse_reinhard(const void* frames_u8_dev, void* hdr_f32_dev, int n_fr
 typedef struct itmo_trainer itmo_trainer;
 enum itmo_train_flags {
   ITMO_TRAIN_NO_DROPOUT = 1,   /* Dropout layers act as identity (parity tests against a deterministic oracle) */
-  ITMO_TRAIN_FREEZE_MOVING = 2 /* do not update moving_mean / moving_variance */
+  ITMO_TRAIN_FREEZE_MOVING = 2, /* do not update moving_mean / moving_variance */
+  ITMO_TRAIN_KEEP_GRADS = 4     /* keep a copy of every layer's activation gradients (itmo_train_read_activation 3 / 4) */
 };
 enum itmo_optimizer {
   ITMO_OPT_RMSPROP = 0, /* model.py:281; Keras defaults lr 1e-3, rho 0.9, eps 1e-7 */
@@ -207,7 +208,8 @@ int itmo_train_metrics(itmo_trainer* t, double* sq_err_sum, double* hits, int re
  * RMSprop: beta1_or_rho = rho, beta2 unused. Adam: bias-corrected with the trainer's step counter. */
 int itmo_train_update(itmo_trainer* t, int optimizer, float lr, float beta1_or_rho, float beta2, float eps,
                       float grad_scale, void* stream);
-/* Debug / parity: activation of the last micro-batch as float32; which 0 = ReLU(conv+b), 1 = BN(+dropout) output, 2 = pooled */
+/* Debug / parity: activation of the last micro-batch as float32; which 0 = ReLU(conv+b), 1 = BN(+dropout) output, 2 = pooled,
+ * 3 = dL/d(BN output), 4 = dL/d(conv output before ReLU) (both only after a backward with ITMO_TRAIN_KEEP_GRADS) */
 int itmo_train_read_activation(itmo_trainer* t, int layer, int which, int n, float* dst_host, size_t cap_elems,
                                size_t* n_elems);
 /* Device timing per phase: 0 forward convs, 1 data-gradient convs, 2 weight-gradient GEMMs, 3 everything else */

@@ -52,9 +52,26 @@ def layer_dropout_seed(seed: int, layer: int) -> int:
     return (seed * 0x9E3779B9 + layer * 0x85EBCA6B + 1) & 0xFFFFFFFF
 
 
+def _bf16_round_fn():
+    """Autograd function that rounds the value to bf16 on the way forward and the gradient to bf16 on the way back:
+    what storing a tensor (and, later, its gradient) as bf16 in HBM does."""
+    import torch
+
+    class RoundBf16(torch.autograd.Function):
+        @staticmethod
+        def forward(ctx, t):
+            return t.to(torch.bfloat16).to(t.dtype)
+
+        @staticmethod
+        def backward(ctx, g):
+            return g.to(torch.bfloat16).to(g.dtype)
+
+    return RoundBf16.apply
+
+
 def train_forward_backward(weights: Sequence[Dict[str, np.ndarray]], x_nhwc: np.ndarray, y_nhwc: np.ndarray,
                            drop_seed: Optional[int] = None, dtype=None, loss_count: Optional[float] = None,
-                           return_acts: bool = False):
+                           return_acts: bool = False, emulate_bf16: bool = False):
     """One forward (training mode) + backward. Returns dict(loss=sum of squared errors / loss_count, sq_err_sum, acc,
     pred [N,H,W,3], grads = list of {kernel, bias, gamma, beta} in Keras layouts, batch_mean / batch_var per layer).
     drop_seed None = dropout disabled (identity), else the micro-batch seed."""
@@ -73,23 +90,29 @@ def train_forward_backward(weights: Sequence[Dict[str, np.ndarray]], x_nhwc: np.
             d['beta'] = torch.from_numpy(np.ascontiguousarray(w['beta'])).to(dtype).requires_grad_(True)
         params.append(d)
     outs, pooled, zs, means, vars_ = {}, {}, {}, {}, {}
+    # emulate_bf16: mimic where the device path stores bf16 (every conv input and its gradient, z, a, the tensor-core
+    # layers' weights); everything else (accumulation, statistics, parameter gradients) stays in `dtype`.
+    rnd = _bf16_round_fn() if emulate_bf16 else (lambda t: t)
     for s in R.LAYERS:
         p = params[s.index]
         if s.kind == 'head':
             k = p['kernel'].permute(3, 2, 0, 1)  # HWIO -> OIHW
-            pred = torch.sigmoid(F.conv2d(outs[17], k, p['bias']))
+            pred = torch.sigmoid(F.conv2d(rnd(outs[17]), k, p['bias']))
             continue
         if len(s.src) == 2:
-            inp = torch.cat([outs[s.src[0]], outs[s.src[1]]], dim=1)   # (skip, up): model.py:246
+            inp = torch.cat([rnd(outs[s.src[0]]), rnd(outs[s.src[1]])], dim=1)   # (skip, up): model.py:246
         elif s.src[0] < 0:
             inp = x
         else:
-            inp = pooled[s.src[0]] if s.src_pooled else outs[s.src[0]]
+            inp = rnd(pooled[s.src[0]] if s.src_pooled else outs[s.src[0]])
+        kern = p['kernel']
+        if emulate_bf16 and s.index != 0:
+            kern = kern + (kern.detach().to(torch.bfloat16).to(dtype) - kern.detach())   # bf16 value, identity gradient
         if s.kind == 'conv':
-            z = F.conv2d(inp, p['kernel'].permute(3, 2, 0, 1), p['bias'], padding=1)
+            z = F.conv2d(inp, kern.permute(3, 2, 0, 1), p['bias'], padding=1)
         else:
-            z = F.conv_transpose2d(inp, p['kernel'].permute(3, 2, 0, 1), p['bias'], stride=2)  # [a,b,Co,Ci] -> [Ci,Co,a,b]
-        z = torch.relu(z)
+            z = F.conv_transpose2d(inp, kern.permute(3, 2, 0, 1), p['bias'], stride=2)  # [a,b,Co,Ci] -> [Ci,Co,a,b]
+        z = rnd(torch.relu(z))
         m = z.mean(dim=(0, 2, 3))
         v = z.var(dim=(0, 2, 3), unbiased=False)
         a = p['gamma'][None, :, None, None] * (z - m[None, :, None, None]) / torch.sqrt(v[None, :, None, None] + R.BN_EPS) \
@@ -99,6 +122,7 @@ def train_forward_backward(weights: Sequence[Dict[str, np.ndarray]], x_nhwc: np.
             keep = dropout_keep_mask((n, h, w_, c), layer_dropout_seed(drop_seed, s.index))
             keep_t = torch.from_numpy(np.ascontiguousarray(keep.transpose(0, 3, 1, 2))).to(dtype)
             a = a * keep_t * (1.0 / (1.0 - R.DROPOUT_RATE))
+        a = rnd(a)
         outs[s.index] = a
         zs[s.index] = z
         means[s.index] = m.detach().numpy().astype(np.float64)
