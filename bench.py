@@ -478,6 +478,154 @@ def run_frames_arm(a):
     return 0
 
 
+def run_train_arm(a):
+    """--workload train (BASELINE configs[4]): data-parallel training step on synthetic SDR/HDR pairs, GLOBAL batch
+    a.train_batch (512) split over the ranks (strong scaling), micro-batched through the activation arena; forward in
+    training mode + dgrad/wgrad + ONE NCCL all-reduce of the flat fp32 gradient buffer (44.6 MB) + fused RMSprop.
+    `value` = images/s of whole optimizer steps with the batch resident in HBM; `e2e` = Trainer.train_on_batch on pinned
+    host arrays (H2D of the batch and the loss read-back inside the timed region)."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    rank = int(os.environ.get('RANK', '0'))
+    local_rank = int(os.environ.get('LOCAL_RANK', '0'))
+    if not torch.cuda.is_available():
+        raise SystemExit('bench.py: no CUDA device')
+    a.gpus = world
+    torch.cuda.set_device(local_rank)
+    dev = torch.device('cuda', local_rank)
+    if world > 1:
+        os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
+        dist.init_process_group('nccl', device_id=dev)
+    import __graft_entry__ as G
+    if not os.path.exists(G.LIB):
+        G.build()
+    import cnn_itmo_b200 as M
+    from cnn_itmo_b200 import graph, train
+    from cnn_itmo_b200.model import pinned_empty
+    if a.train_batch % world:
+        raise SystemExit(f'bench.py: global batch {a.train_batch} is not divisible by {world} ranks')
+    per_rank = a.train_batch // world
+    mb = min(a.micro_batch, per_rank)
+    tr = train.Trainer(M.initial_weights(seed=218), micro_batch=mb, image_hw=(IMG, IMG), device=local_rank,
+                       optimizer='rmsprop')
+    g = torch.Generator(device=dev).manual_seed(7 + rank)
+    x = torch.randint(0, 256, (per_rank, IMG, IMG, 3), dtype=torch.uint8, device=dev, generator=g)
+    y = torch.rand((per_rank, IMG, IMG, 3), dtype=torch.float32, device=dev, generator=g)
+    loss_count = float(a.train_batch) * IMG * IMG * 3
+    stream = torch.cuda.current_stream()
+    state = {'step': 0}
+
+    def step():
+        tr.zero_grad()
+        for i0 in range(0, per_rank, mb):
+            tr.backward(x[i0:i0 + mb], y[i0:i0 + mb], loss_count, seed=state['step'] * 7919 + i0)
+        tr.allreduce_grads()
+        tr.update()
+        state['step'] += 1
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+
+    for _ in range(max(a.warmup, 3)):
+        step()
+    barrier()
+    tr.metrics(reset=True)
+    tr.set_profiling(True)
+    tr.phase_times(reset=True)
+    launches0 = tr.launch_count()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    ev0.record(stream)
+    for _ in range(a.steps):
+        step()
+    ev1.record(stream)
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    ms_total = ev0.elapsed_time(ev1)
+    phases = tr.phase_times(reset=True)
+    tr.set_profiling(False)
+    launches = tr.launch_count() - launches0
+    sq, hits = tr.metrics(reset=True)
+    if world > 1:
+        t = torch.tensor([ms_total], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_total = float(t.item())
+    ips = a.train_batch * a.steps / (ms_total / 1e3)
+    # end to end through the public call: pinned host batch -> H2D -> step -> loss back on the host
+    hx = pinned_empty((per_rank, IMG, IMG, 3), np.uint8)
+    hy = pinned_empty((per_rank, IMG, IMG, 3), np.float32)
+    hx[...] = x.cpu().numpy()
+    hy[...] = y.cpu().numpy()
+    e2e_steps = max(1, min(a.steps, 3))
+    barrier()
+    t0 = time.perf_counter()
+    last = None
+    for _ in range(e2e_steps):
+        last = tr.train_on_batch(hx, hy)
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    if world > 1:
+        t = torch.tensor([dt], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dt = float(t.item())
+    e2e = a.train_batch * e2e_steps / dt
+    if rank == 0:
+        peaks = measured_peaks()
+        fwd = graph.forward_flops_per_image()
+        convs = [l for l in graph.LAYERS if l.kind != 'head']
+        flop = lambda l: 2.0 * (l.hin ** 2) * (9 if l.kind == 'conv' else 4) * sum(l.cin) * l.cout
+        f_fwd = sum(flop(l) for l in convs)
+        f_dgrad = sum(flop(l) for l in convs[1:])          # the first layer needs no data gradient
+        f_wgrad = f_fwd
+        gemm_ms = phases['fwd_conv'][0] + phases['dgrad'][0] + phases['wgrad'][0]
+        gemm_calls = phases['fwd_conv'][1] + phases['dgrad'][1] + phases['wgrad'][1]
+        images_rank = per_rank * a.steps
+        ach = (f_fwd + f_dgrad + f_wgrad) * images_rank / (gemm_ms / 1e3) / 1e12 if gemm_ms > 0 else None
+        per_phase = {k: {'ms_per_step': round(v[0] / a.steps, 3), 'launches_per_step': v[1] // a.steps}
+                     for k, v in phases.items()}
+        per_phase['fwd_conv']['tflops'] = round(f_fwd * images_rank / (phases['fwd_conv'][0] / 1e3) / 1e12, 1)
+        per_phase['dgrad']['tflops'] = round(f_dgrad * images_rank / (phases['dgrad'][0] / 1e3) / 1e12, 1)
+        per_phase['wgrad']['tflops'] = round(f_wgrad * images_rank / (phases['wgrad'][0] / 1e3) / 1e12, 1)
+        line = {'metric': 'U-Net SDR->HDR training throughput (512x512 images, forward + backward + RMSprop)',
+                'value': round(ips, 2), 'unit': 'images/s', 'n_gpus': world, 'steps': a.steps,
+                'warmup': max(a.warmup, 3), 'ms_per_step': round(ms_total / a.steps, 3), 'higher_is_better': True,
+                'scaling': 'strong', 'vs_baseline': None, 'dtype': 'bf16', 'data': 'synthetic',
+                'mpix_per_s': round(ips * MPIX_PER_IMAGE, 2),
+                'tflops_per_gpu': round((f_fwd + f_dgrad + f_wgrad) * ips / world / 1e12, 1),
+                'config': {'workload': f'data-parallel training step, global batch {a.train_batch} ({per_rank} per GPU in '
+                                       f'micro-batches of {mb}), 512x512x3 uint8 SDR in, float32 target, random-init '
+                                       'weights, Dropout on, RMSprop (BASELINE configs[4])',
+                           'global_batch': a.train_batch, 'micro_batch': mb,
+                           'parallelism': f'dp{world} (one NCCL all-reduce of the 44.6 MB flat fp32 gradient per step)',
+                           'l2': 'every micro-batch streams > 10 GB of activations; no explicit flush'},
+                'clocks': clocks,
+                'e2e': {'value': round(e2e, 2), 'unit': 'images/s', 'h2d_bytes_per_step': int(hx.nbytes + hy.nbytes),
+                        'd2h_bytes_per_step': 16, 'steps': e2e_steps, 'api': 'Trainer.train_on_batch (pinned host arrays)',
+                        'last_loss': round(float(last[0]), 6)},
+                'gpu_launches': int(launches),
+                'roofline': {'bound': 'tensor', 'kernel': 'conv_igemm_kernel (forward + dgrad) + wgrad_igemm_kernel',
+                             'achieved': round(ach, 1) if ach else None, 'peak': peaks['tflops_sustained'],
+                             'unit': 'TFLOP/s', 'frac': round(ach / peaks['tflops_sustained'], 4) if ach else None,
+                             'traffic': None, 'peak_source': peaks['source'] + ' (bf16 sustained)',
+                             'flops_per_launch': (f_fwd + f_dgrad + f_wgrad) * images_rank / max(gemm_calls, 1),
+                             'avg_launch_ms': round(gemm_ms / max(gemm_calls, 1), 4),
+                             'share_of_step': round(gemm_ms / ms_total, 4), 'phases': per_phase},
+                'train_loss': round(sq / (a.steps * per_rank * IMG * IMG * 3.0), 6), 'cpu_baseline': None}
+        print(json.dumps(line), flush=True)
+    tr.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
 def main(argv=None) -> int:
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
@@ -491,7 +639,9 @@ def main(argv=None) -> int:
     ap.add_argument('--cpu-sample', type=int, default=4, help='images per step of the CPU restatement')
     ap.add_argument('--cpu-budget', type=float, default=15.0, help='seconds of CPU work for cpu_baseline')
     ap.add_argument('--no-cpu', action='store_true', help='skip the cpu_baseline leg')
-    ap.add_argument('--workload', default='batch', choices=['batch', '4k'],
+    ap.add_argument('--train-batch', type=int, default=512, help='GLOBAL batch of --workload train (configs[4]: 512)')
+    ap.add_argument('--micro-batch', type=int, default=32, help='images per forward/backward pass of --workload train')
+    ap.add_argument('--workload', default='batch', choices=['batch', '4k', 'train'],
                     help="'batch' = BASELINE configs[2] (default, the headline); '4k' = configs[3] tiled frames")
     ap.add_argument('--frames', type=int, default=2, help='4K frames per GPU per step (--workload 4k)')
     a = ap.parse_args(argv)
@@ -499,6 +649,8 @@ def main(argv=None) -> int:
         return run_reference_arm(a)
     if a.workload == '4k':
         return run_frames_arm(a)
+    if a.workload == 'train':
+        return run_train_arm(a)
     return run_b200_arm(a)
 
 
