@@ -64,6 +64,15 @@ int ew_grid(size_t work_items) {
   return int(std::min<size_t>((work_items + 255) / 256, size_t(num_sms()) * 8));
 }
 
+// Grid of a grid-stride kernel: every SM filled with as many 256-thread blocks as its registers / shared memory allow
+// (one full wave: a partial second wave would idle most of the machine for half the kernel).
+template <typename K>
+int full_wave_grid(K kern, size_t max_blocks) {
+  int per_sm = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 256, 0) != cudaSuccess || per_sm < 1) per_sm = 2;
+  return int(std::max<size_t>(1, std::min<size_t>(size_t(num_sms()) * per_sm, max_blocks)));
+}
+
 struct WgradArgs {
   const void* a;   // shifted operand (M side)
   int ca_tensor;   // channels of the tensor behind `a`
@@ -265,8 +274,9 @@ int train_forward(itmo_trainer* t, const void* x, int x_dtype, int nb, int flags
     const bool dropout = (li == 7 || li == 9) && !(flags & ITMO_TRAIN_NO_DROPOUT);
     {
       PhaseStamp ps(t, kPhOther, s, __LINE__);
-      itmo::bn_stats_kernel<<<int(std::min<size_t>(num_sms() * 4, (npix + 63) / 64)), 256, 0, s>>>(t->z[li], npix, L.cout,
-                                                                                                 fstats(t, li));
+      static const int g_stats = full_wave_grid(itmo::bn_stats_kernel, size_t(1) << 30);
+      itmo::bn_stats_kernel<<<int(std::min<size_t>(g_stats, (npix + 63) / 64)), 256, 0, s>>>(t->z[li], npix, L.cout,
+                                                                                           fstats(t, li));
       itmo::bn_finalize_kernel<<<(L.cout + 127) / 128, 128, 0, s>>>(
           fstats(t, li), L.cout, double(npix), 1e-3f, 0.99f, t->params + lay.gamma[li], t->params + lay.beta[li],
           bnv(t, li, 0), bnv(t, li, 1), bnv(t, li, 2), bnv(t, li, 3),
@@ -313,8 +323,11 @@ int train_backward(itmo_trainer* t, const void* x, int x_dtype, const float* y, 
     }
     {
       PhaseStamp ps(t, kPhOther, s, __LINE__);
-      const int grid = int(std::min<size_t>(num_sms() * 4, (npix + 63) / 64));
-      itmo::bn_bwd_reduce_kernel<<<grid, 256, 0, s>>>(dA, t->z[li], npix, L.cout, bnv(t, li, 0), bnv(t, li, 1),
+      static const int g_red = full_wave_grid(itmo::bn_bwd_reduce_kernel, size_t(1) << 30);
+      static const int g_app = full_wave_grid(itmo::bn_bwd_apply_kernel, size_t(1) << 30);
+      const int grid_r = int(std::min<size_t>(g_red, (npix + 63) / 64));
+      const int grid = int(std::min<size_t>(g_app, (npix + 63) / 64));
+      itmo::bn_bwd_reduce_kernel<<<grid_r, 256, 0, s>>>(dA, t->z[li], npix, L.cout, bnv(t, li, 0), bnv(t, li, 1),
                                                       t->drop_seed[li], dropout ? 1 : 0, bstats(t, li));
       itmo::bn_bwd_apply_kernel<<<grid, 256, 0, s>>>(dA, t->z[li], t->gp, npix, L.cout, t->params + lay.gamma[li],
                                                      bnv(t, li, 0), bnv(t, li, 1), bstats(t, li), double(npix),

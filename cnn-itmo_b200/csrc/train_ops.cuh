@@ -48,7 +48,7 @@ __device__ __forceinline__ bool drop_keep(uint32_t e, uint32_t seed) {
 
 // ---- BN training statistics: sum / sum of squares per channel of z = ReLU(conv + b) ------------------------------
 // grid-stride over pixels; blockDim = 256; thread -> (pixel lane, 8-channel group). stats[0..C) = sum, [C..2C) = sumsq.
-__global__ void __launch_bounds__(256) bn_stats_kernel(const __nv_bfloat16* __restrict__ z, size_t npix, int C,
+__global__ void __launch_bounds__(256, 4) bn_stats_kernel(const __nv_bfloat16* __restrict__ z, size_t npix, int C,
                                                        double* __restrict__ stats) {
   __shared__ float s_sum[512], s_sq[512];
   for (int i = threadIdx.x; i < C; i += blockDim.x) s_sum[i] = s_sq[i] = 0.f;
@@ -59,13 +59,22 @@ __global__ void __launch_bounds__(256) bn_stats_kernel(const __nv_bfloat16* __re
   const int pl = threadIdx.x / groups;
   float a[8] = {}, q[8] = {};
   if (pl < lanes) {
-    for (size_t pix = size_t(blockIdx.x) * lanes + pl; pix < npix; pix += size_t(gridDim.x) * lanes) {
-      float f[8];
-      ld8(z + pix * C + cg * 8).get(f);
+    const size_t stride = size_t(gridDim.x) * lanes;
+    for (size_t pix = size_t(blockIdx.x) * lanes + pl; pix < npix; pix += 4 * stride) {
+      Bf8 v[4];   // four independent 16-byte loads in flight per thread
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        a[i] += f[i];
-        q[i] = fmaf(f[i], f[i], q[i]);
+      for (int u = 0; u < 4; ++u)
+        if (pix + u * stride < npix) v[u] = ld8(z + (pix + u * stride) * C + cg * 8);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        if (pix + u * stride >= npix) break;
+        float f[8];
+        v[u].get(f);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          a[i] += f[i];
+          q[i] = fmaf(f[i], f[i], q[i]);
+        }
       }
     }
 #pragma unroll
@@ -275,7 +284,7 @@ __global__ void __launch_bounds__(128) head_train_kernel(const __nv_bfloat16* __
 
 // ---- BN backward, pass 1: per-channel sums of dA' and dA' * zhat (dA' = dA through the dropout mask) ---------------
 // sums[0..C) = sum dA', sums[C..2C) = sum dA' * (z - mean) * invstd
-__global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dA,
+__global__ void __launch_bounds__(256, 3) bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dA,
                                                             const __nv_bfloat16* __restrict__ z, size_t npix, int C,
                                                             const float* __restrict__ mean, const float* __restrict__ invstd,
                                                             uint32_t drop_seed, int dropout, double* __restrict__ sums) {
@@ -293,17 +302,30 @@ __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const __nv_bfloat16*
       mu[i] = mean[cg * 8 + i];
       is[i] = invstd[cg * 8 + i];
     }
-    for (size_t pix = size_t(blockIdx.x) * lanes + pl; pix < npix; pix += size_t(gridDim.x) * lanes) {
-      const size_t e0 = pix * C + cg * 8;
-      float d[8], f[8];
-      ld8(dA + e0).get(d);
-      ld8(z + e0).get(f);
+    const size_t stride = size_t(gridDim.x) * lanes;
+    for (size_t pix = size_t(blockIdx.x) * lanes + pl; pix < npix; pix += 2 * stride) {
+      Bf8 vd[2], vz[2];
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        float dv = d[i];
-        if (dropout) dv = drop_keep(uint32_t(e0 + i), drop_seed) ? 2.f * dv : 0.f;
-        sa[i] += dv;
-        sb[i] = fmaf(dv, (f[i] - mu[i]) * is[i], sb[i]);
+      for (int u = 0; u < 2; ++u)
+        if (pix + u * stride < npix) {
+          const size_t e0 = (pix + u * stride) * C + cg * 8;
+          vd[u] = ld8(dA + e0);
+          vz[u] = ld8(z + e0);
+        }
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        if (pix + u * stride >= npix) break;
+        const size_t e0 = (pix + u * stride) * C + cg * 8;
+        float d[8], f[8];
+        vd[u].get(d);
+        vz[u].get(f);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          float dv = d[i];
+          if (dropout) dv = drop_keep(uint32_t(e0 + i), drop_seed) ? 2.f * dv : 0.f;
+          sa[i] += dv;
+          sb[i] = fmaf(dv, (f[i] - mu[i]) * is[i], sb[i]);
+        }
       }
     }
 #pragma unroll
@@ -321,7 +343,7 @@ __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const __nv_bfloat16*
 
 // ---- BN backward, pass 2 (+ ReLU backward): dpre = [z > 0] * gamma*invstd * (dA' - mean(dA') - zhat * mean(dA' zhat)) --
 // also accumulates the bias gradient sum(dpre) per channel (of the bf16-rounded dpre the GEMMs consume).
-__global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dA,
+__global__ void __launch_bounds__(256, 3) bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dA,
                                                            const __nv_bfloat16* __restrict__ z,
                                                            __nv_bfloat16* __restrict__ dpre, size_t npix, int C,
                                                            const float* __restrict__ gamma, const float* __restrict__ mean,
@@ -336,35 +358,48 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const __nv_bfloat16* 
   const int lanes = blockDim.x / groups;
   const int pl = threadIdx.x / groups;
   if (pl < lanes) {
-    float mu[8], is[8], gs[8], m1[8], m2[8], db[8] = {};
+    // dz = gs * (dA' - m1 - (z - mu) * is * m2) = gs * dA' + kz * z + k0   with kz = -gs*is*m2, k0 = gs * (mu*is*m2 - m1)
+    float gs[8], kz[8], k0[8], db[8] = {};
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
       const int c = cg * 8 + i;
-      mu[i] = mean[c];
-      is[i] = invstd[c];
-      gs[i] = gamma[c] * is[i];
-      m1[i] = float(sums[c] / M);
-      m2[i] = float(sums[C + c] / M);
+      const float mu = mean[c], is = invstd[c];
+      const float m1 = float(sums[c] / M), m2 = float(sums[C + c] / M);
+      gs[i] = gamma[c] * is;
+      kz[i] = -gs[i] * is * m2;
+      k0[i] = gs[i] * (mu * is * m2 - m1);
     }
-    for (size_t pix = size_t(blockIdx.x) * lanes + pl; pix < npix; pix += size_t(gridDim.x) * lanes) {
-      const size_t e0 = pix * C + cg * 8;
-      float d[8], f[8], o[8];
-      ld8(dA + e0).get(d);
-      ld8(z + e0).get(f);
+    const size_t stride = size_t(gridDim.x) * lanes;
+    for (size_t pix = size_t(blockIdx.x) * lanes + pl; pix < npix; pix += 2 * stride) {
+      Bf8 vd[2], vz[2];
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        float dv = d[i];
-        if (dropout) dv = drop_keep(uint32_t(e0 + i), drop_seed) ? 2.f * dv : 0.f;
-        const float zh = (f[i] - mu[i]) * is[i];
-        const float dz = gs[i] * (dv - m1[i] - zh * m2[i]);
-        o[i] = f[i] > 0.f ? dz : 0.f;
+      for (int u = 0; u < 2; ++u)
+        if (pix + u * stride < npix) {
+          const size_t e0 = (pix + u * stride) * C + cg * 8;
+          vd[u] = ld8(dA + e0);
+          vz[u] = ld8(z + e0);
+        }
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        if (pix + u * stride >= npix) break;
+        const size_t e0 = (pix + u * stride) * C + cg * 8;
+        float d[8], f[8], o[8];
+        vd[u].get(d);
+        vz[u].get(f);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          float dv = d[i];
+          if (dropout) dv = drop_keep(uint32_t(e0 + i), drop_seed) ? 2.f * dv : 0.f;
+          const float dz = fmaf(gs[i], dv, fmaf(kz[i], f[i], k0[i]));
+          o[i] = f[i] > 0.f ? dz : 0.f;
+        }
+        Bf8 ov;
+        ov.set(o);
+        st8(dpre + e0, ov);
+        ov.get(o);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) db[i] += o[i];
       }
-      Bf8 ov;
-      ov.set(o);
-      st8(dpre + e0, ov);
-      ov.get(o);
-#pragma unroll
-      for (int i = 0; i < 8; ++i) db[i] += o[i];
     }
 #pragma unroll
     for (int i = 0; i < 8; ++i) atomicAdd(&s_db[cg * 8 + i], db[i]);
