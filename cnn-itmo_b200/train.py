@@ -42,6 +42,53 @@ def param_layout() -> List[Dict[str, Tuple[int, int]]]:
     return out
 
 
+def world_info() -> Tuple[int, int]:
+    """(world_size, rank) of the default process group, (1, 0) when torch.distributed is not initialised."""
+    import torch.distributed as dist
+    if dist.is_available() and dist.is_initialized():
+        return dist.get_world_size(), dist.get_rank()
+    return 1, 0
+
+
+def shard_range(n_global: int, world: int, rank: int) -> Tuple[int, int]:
+    """Contiguous [begin, end) slice of a global batch that `rank` trains on (BASELINE configs[4]: 512 images split
+    512 / 256 / 128 / 64 per GPU). The batch must divide evenly: every rank runs the same number of micro-batches, so
+    the all-reduce is reached in lock step."""
+    if n_global % world:
+        raise ValueError(f'global batch {n_global} is not divisible by {world} ranks')
+    per = n_global // world
+    return rank * per, (rank + 1) * per
+
+
+def global_loss_count(n_local: int, h: int, w: int, world: int) -> float:
+    """Number of output elements the mse averages over for the WHOLE batch (Keras 'mse' = mean over N*H*W*3): every
+    rank divides its squared-error gradient by this, so the SUM over ranks is the gradient of the global mean."""
+    return float(n_local * world) * h * w * 3
+
+
+def allreduce_flat(flat_tensor):
+    """The one exchange step of data-parallel training: in-place SUM of a flat gradient tensor over all ranks
+    (NCCL over NVLink for CUDA tensors, gloo for the CPU tests). No-op for a single process."""
+    import torch.distributed as dist
+    world, _ = world_info()
+    if world > 1:
+        dist.all_reduce(flat_tensor, op=dist.ReduceOp.SUM)
+    return flat_tensor
+
+
+def flatten_layers(layers: Sequence[Dict[str, np.ndarray]], layout=None) -> np.ndarray:
+    """Per-layer {kernel, bias, gamma, beta} dicts -> the flat fp32 buffer in the library's layout (itmo_train_layout)."""
+    layout = layout or param_layout()
+    n = int(_lib.load().itmo_train_param_count())
+    flat = np.zeros(n, np.float32)
+    for li, lay in enumerate(layout):
+        for name in ('kernel', 'bias', 'gamma', 'beta'):
+            if name in lay:
+                off, cnt = lay[name]
+                flat[off:off + cnt] = np.asarray(layers[li][name], np.float32).reshape(-1)
+    return flat
+
+
 class Trainer:
     def __init__(self, weights: Sequence[Dict[str, np.ndarray]], micro_batch: int = 8, image_hw=(512, 512),
                  device: int = 0, optimizer: str = 'rmsprop', lr: Optional[float] = None, **opt_kwargs):
@@ -162,9 +209,7 @@ class Trainer:
     def allreduce_grads(self):
         """The one exchange step of data-parallel training: sum of the flat gradient buffer over all ranks
         (NCCL over NVLink when the process group's backend is nccl)."""
-        import torch.distributed as dist
-        if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
-            dist.all_reduce(self.grads, op=dist.ReduceOp.SUM)
+        allreduce_flat(self.grads)
 
     def update(self, grad_scale: float = 1.0):
         o = self.opt
@@ -187,9 +232,9 @@ class Trainer:
         x = np.ascontiguousarray(x if np.asarray(x).dtype == np.uint8 else np.asarray(x, np.float32))
         y = np.ascontiguousarray(np.asarray(y, np.float32))
         n = x.shape[0]
-        world = dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
+        world, _ = world_info()
         n_global = n * world
-        loss_count = float(n_global) * self.h * self.w * 3
+        loss_count = global_loss_count(n, self.h, self.w, world)
         seed = self.step_index if seed is None else seed
         self.zero_grad()
         for i0 in range(0, n, self.micro_batch):

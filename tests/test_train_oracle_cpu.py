@@ -138,3 +138,66 @@ def test_model_training_surface_errors_without_gpu():
         m.compile()
         with pytest.raises(Exception):   # no GPU -> loud failure, never a CPU fallback
             m.train_on_batch(np.zeros((1, 512, 512, 3), np.float32), np.zeros((1, 512, 512, 3), np.float32))
+
+
+# ---- data-parallel host logic over two gloo ranks (the N > 1 path without GPUs) ---------------------------------------
+def _dp_worker(rank, world, port, q):
+    import os
+    import torch.distributed as dist
+    os.environ['MASTER_ADDR'] = '127.0.0.1'
+    os.environ['MASTER_PORT'] = str(port)
+    dist.init_process_group('gloo', rank=rank, world_size=world)
+    try:
+        from cnn_itmo_b200 import train
+        ws = _small_weights(6)
+        rng = np.random.default_rng(5)
+        x = rng.uniform(0, 1, (4, 16, 16, 3))
+        y = rng.uniform(0, 1, (4, 16, 16, 3))
+        b, e = train.shard_range(4, world, rank)
+        count = train.global_loss_count(e - b, 16, 16, world)
+        res = T.train_forward_backward(ws, x[b:e], y[b:e], None, dtype=torch.float64, loss_count=count)
+        flat = torch.from_numpy(train.flatten_layers(res['grads']).astype(np.float64))
+        train.allreduce_flat(flat)
+        sq = torch.tensor([res['sq_err_sum']], dtype=torch.float64)
+        train.allreduce_flat(sq)
+        q.put((rank, flat.numpy(), float(sq[0]) / count, count))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_data_parallel_exchange_over_two_gloo_ranks():
+    """Each rank runs its shard with the GLOBAL loss_count; the all-reduced flat gradient equals the sum of the
+    per-shard gradients (BN statistics are per replica) and the all-reduced loss the global mse."""
+    import multiprocessing as mp
+    import socket
+    from cnn_itmo_b200 import train
+    with socket.socket() as s:
+        s.bind(('127.0.0.1', 0))
+        port = s.getsockname()[1]
+    ctx = mp.get_context('spawn')
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_dp_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    outs = sorted([q.get(timeout=300) for _ in procs], key=lambda t: t[0])
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert np.array_equal(outs[0][1], outs[1][1])            # every rank ends with the same gradient
+    assert outs[0][3] == 4 * 16 * 16 * 3
+    ws = _small_weights(6)
+    rng = np.random.default_rng(5)
+    x = rng.uniform(0, 1, (4, 16, 16, 3))
+    y = rng.uniform(0, 1, (4, 16, 16, 3))
+    want = np.zeros_like(outs[0][1])
+    loss = 0.0
+    for r in range(2):
+        b, e = train.shard_range(4, 2, r)
+        res = T.train_forward_backward(ws, x[b:e], y[b:e], None, dtype=torch.float64, loss_count=float(y.size))
+        want += train.flatten_layers(res['grads']).astype(np.float64)
+        loss += res['sq_err_sum'] / y.size
+    assert np.allclose(outs[0][1], want, rtol=1e-6, atol=1e-12)
+    assert np.isclose(outs[0][2], loss)
+    with pytest.raises(ValueError):
+        train.shard_range(5, 2, 0)
+    assert train.shard_range(512, 8, 3) == (192, 256)
