@@ -162,6 +162,7 @@ def run_reference_arm(a):
     torch.set_num_threads(cores)
     ws = M.initial_weights(seed=218)
     tw = R.TorchWeights(ws)
+    a.cpu_sample = max(1, min(a.cpu_sample, 12))   # 20 default steps x 12 images ~ 1 minute of CPU work
     imgs = np.random.default_rng(0).integers(0, 256, (a.cpu_sample, IMG, IMG, 3), dtype=np.uint8)
     for _ in range(max(1, a.warmup)):
         R.predict_like_reference(tw, imgs[:1])
@@ -636,7 +637,9 @@ def main(argv=None) -> int:
     ap.add_argument('--chunk', type=int, default=int(os.environ.get('ITMO_BENCH_CHUNK', '64')),
                     help='images the activation arena holds (itmo_create max_batch)')
     ap.add_argument('--precision', default='bf16', choices=['bf16', 'fp16', 'tf32', 'fp32'])
-    ap.add_argument('--cpu-sample', type=int, default=4, help='images per step of the CPU restatement')
+    ap.add_argument('--cpu-sample', type=int, default=48,
+                    help='upper bound on the images of the cpu_baseline sample (the --cpu-budget seconds decide); the '
+                         'reference arm runs min(this, 12) images per step')
     ap.add_argument('--cpu-budget', type=float, default=15.0, help='seconds of CPU work for cpu_baseline')
     ap.add_argument('--no-cpu', action='store_true', help='skip the cpu_baseline leg')
     ap.add_argument('--train-batch', type=int, default=512, help='GLOBAL batch of --workload train (configs[4]: 512)')
