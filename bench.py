@@ -326,8 +326,20 @@ def run_b200_arm(a):
     n_igemm = sum(int(p['launches_per_step']) for p in per_layer[1:])
     achieved = igemm_flops / (igemm_ms * 1e-3) / 1e12 if igemm_ms > 0 else 0.0
     peak = peaks['tflops_sustained']
+    # DRAM bytes per launch from the committed ncu --set full capture of the same launches (profiles/, made by
+    # tools/gpu_ncu_traffic.sh); only quoted when the capture's precision and arena chunk are this run's
+    traffic = traffic_src = None
+    tpath = os.path.join(ROOT, 'profiles', f'r01_igemm_traffic_chunk{a.chunk}.json')
+    if os.path.exists(tpath):
+        with open(tpath) as f:
+            tj = json.load(f)
+        if tj.get('precision') == a.precision and tj.get('chunk_images') == min(a.chunk, B):
+            traffic = tj['dram_bytes_per_launch_avg']
+            traffic_src = os.path.relpath(tpath, ROOT)
     roofline = {'bound': 'tensor', 'kernel': 'itmo::conv_igemm_kernel', 'achieved': round(achieved, 2),
-                'peak': peak, 'unit': 'TFLOP/s', 'frac': round(achieved / peak, 4), 'traffic': None,
+                'peak': peak, 'unit': 'TFLOP/s', 'frac': round(achieved / peak, 4), 'traffic': traffic,
+                'traffic_unit': 'DRAM bytes per launch (ncu dram__bytes_read.sum + dram__bytes_write.sum)',
+                'traffic_source': traffic_src,
                 'peak_source': f"{peaks['source']} (bf16 sustained; kernel timed inside a long step)",
                 'flops_per_launch': igemm_flops / max(1, n_igemm),
                 'avg_launch_ms': round(igemm_ms / max(1, n_igemm), 4),

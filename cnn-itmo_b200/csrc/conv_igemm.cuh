@@ -75,6 +75,9 @@ struct ConvParams {
   int dbg;             // timing experiments only (results wrong): 16 no activation TMA, 32 no epilogue, 64 no MMAs
   int kb_hi;           // channel blocks of the leading (x*w_hi) part; the rest go to accumulator S-1
   int no_relu;         // 1: y = (acc + bias) * scale + shift without the ReLU (data-gradient convolutions of the training step)
+  double* stats;       // training forward (16-bit modes): per-channel sum [cout] and sum of squares [cout] of the stored
+                       // output z = ReLU(acc + bias) are accumulated here (BatchNormalization batch statistics,
+                       // model.py:196); the BN affine is then the identity and bn_scale / bn_shift are not read
   const float* bias;      // [cout]
   const float* bn_scale;  // [cout]  gamma / sqrt(var + eps)
   const float* bn_shift;  // [cout]  beta - mean * scale
@@ -154,6 +157,22 @@ __device__ __forceinline__ void store4_f32(float* dst, float* dst_lo, int mode, 
       *reinterpret_cast<float4*>(dst_lo) =
           make_float4(a - tf32_trunc(a), b - tf32_trunc(b), c - tf32_trunc(c), d - tf32_trunc(d));
   }
+}
+
+// Sum over the 32 lanes of a warp of 32 per-lane values at once: after five exchange rounds lane j holds
+// sum over lanes of v[j] (31 shuffles instead of 32 x 5). v is clobbered.
+__device__ __forceinline__ float warp_transpose_sum32(float (&v)[32], int lane) {
+#pragma unroll
+  for (int off = 16; off >= 1; off >>= 1) {
+    const bool upper = (lane & off) != 0;
+#pragma unroll
+    for (int i = 0; i < off; ++i) {
+      const float send = upper ? v[i] : v[i + off];
+      const float keep = upper ? v[i + off] : v[i];
+      v[i] = keep + __shfl_xor_sync(0xFFFFFFFFu, send, off);
+    }
+  }
+  return v[0];
 }
 
 template <typename Elem, int BLOCK_N, int SWZ>
@@ -293,10 +312,11 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
   if (warp_idx == 2) {
     sm100::tmem_alloc(tmem_ptr_smem, tmem_cols);
   }
+  const bool with_stats = p.stats != nullptr;   // then s_scale / s_shift hold this CTA's sum / sum of squares
   for (int i = threadIdx.x; i < p.cout; i += blockDim.x) {
     s_bias[i] = p.bias[i];
-    s_scale[i] = p.bn_scale[i];
-    s_shift[i] = p.bn_shift[i];
+    s_scale[i] = with_stats ? 0.f : p.bn_scale[i];
+    s_shift[i] = with_stats ? 0.f : p.bn_shift[i];
   }
   if (p.head_dtype != kHeadNone) {
     for (int i = threadIdx.x; i < 3 * 64 + 3; i += blockDim.x)
@@ -520,7 +540,7 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
 #pragma unroll
           for (int i = 0; i < kChunk; ++i) {
             const float a = __uint_as_float(v[i]) + s_bias[co0 + i];
-            f[i] = fmaf(p.no_relu ? a : fmaxf(a, 0.f), s_scale[co0 + i], s_shift[co0 + i]);
+            f[i] = with_stats ? fmaxf(a, 0.f) : fmaf(p.no_relu ? a : fmaxf(a, 0.f), s_scale[co0 + i], s_shift[co0 + i]);
           }
           if (p.head_dtype != kHeadNone) {
 #pragma unroll
@@ -537,6 +557,23 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
             uint32_t pk[kChunk / 2];
 #pragma unroll
             for (int i = 0; i < kChunk / 2; ++i) pk[i] = pack2<Elem>(f[2 * i], f[2 * i + 1]);
+            if constexpr (sizeof(Elem) == 2 && ElemTraits<Elem>::kFmt == sm100::kFmtBF16) {
+              if (with_stats) {
+                // statistics of the ROUNDED values (what bn_apply and the backward read back from HBM)
+                float sv[kChunk], sq[kChunk];
+#pragma unroll
+                for (int i = 0; i < kChunk / 2; ++i) {
+                  sv[2 * i] = __uint_as_float(pk[i] << 16);
+                  sv[2 * i + 1] = __uint_as_float(pk[i] & 0xFFFF0000u);
+                  sq[2 * i] = sv[2 * i] * sv[2 * i];
+                  sq[2 * i + 1] = sv[2 * i + 1] * sv[2 * i + 1];
+                }
+                const float tsum = warp_transpose_sum32(sv, lane);
+                const float tsq = warp_transpose_sum32(sq, lane);
+                atomicAdd(&s_scale[co0 + lane], tsum);
+                atomicAdd(&s_shift[co0 + lane], tsq);
+              }
+            }
             if (p.out != nullptr) {
               uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<Elem*>(p.out) + pix * p.cout + co0);
 #pragma unroll
@@ -612,6 +649,12 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
   // ---------------------------------------------------------------- teardown
   sm100::tc_fence_before_sync();
   __syncthreads();
+  if (with_stats) {
+    for (int i = threadIdx.x; i < p.cout; i += blockDim.x) {
+      atomicAdd(&p.stats[i], double(s_scale[i]));
+      atomicAdd(&p.stats[p.cout + i], double(s_shift[i]));
+    }
+  }
   if (warp_idx == 2) {
     sm100::tc_fence_after_sync();
     sm100::tmem_dealloc(tmem_base, tmem_cols);

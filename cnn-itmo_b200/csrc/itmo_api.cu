@@ -369,6 +369,7 @@ struct ConvArgs {
   long long row_stride[2];   // source 0 / 1 viewed with these row / image strides (elements, 0 = dense)
   long long img_stride[2];
   int w_tap_stride_rows;     // rows between two taps of the packed weights (0 = the rows this launch uses)
+  double* stats;             // per-channel sum / sum of squares of the output (training forward), see ConvParams
 };
 
 // Debug / tuning overrides (environment, read once): ITMO_FORCE_NM = 1|2|4, ITMO_NO_RESIDENT = 1
@@ -481,6 +482,7 @@ int run_conv(const ConvArgs& a, cudaStream_t stream) {
   p.dbg = dbg;
   p.acc_split = acc_split;
   p.no_relu = a.no_relu;
+  p.stats = a.stats;
   p.kb_hi = cin / bk;
   p.store_mode = a.precision == ITMO_PREC_TF32   ? itmo::kStoreTf32Rna
                  : a.precision == ITMO_PREC_FP32 ? itmo::kStoreSplit

@@ -239,6 +239,7 @@ int train_forward(itmo_trainer* t, const void* x, int x_dtype, int nb, int flags
   const float* ones = t->consts;
   const float* zeros = t->consts + 512;
   ITMO_CUDA(cudaMemsetAsync(t->stats, 0, sizeof(double) * 2048 * ITMO_NUM_LAYERS, s));
+  static const bool fuse_stats = env_int("ITMO_TRAIN_FUSE_STATS", 1) != 0;
   for (int li = 0; li < 18; ++li) {
     const LayerDef& L = kLayers[li];
     const int hi = lay_hin(t, L), wi = lay_win(t, L), ho = lay_hout(t, L), wo = lay_wout(t, L);
@@ -266,6 +267,7 @@ int train_forward(itmo_trainer* t, const void* x, int x_dtype, int nb, int flags
       a.cout = L.cout;
       a.out = t->z[li];
       a.head_dtype = itmo::kHeadNone;
+      a.stats = fuse_stats ? fstats(t, li) : nullptr;   // BN batch statistics accumulated by the conv epilogue
       PhaseStamp ps(t, kPhFwdConv, s, __LINE__);
       int rc = run_conv(a, s);
       if (rc) return rc;
@@ -275,7 +277,8 @@ int train_forward(itmo_trainer* t, const void* x, int x_dtype, int nb, int flags
     {
       PhaseStamp ps(t, kPhOther, s, __LINE__);
       static const int g_stats = full_wave_grid(itmo::bn_stats_kernel, size_t(1) << 30);
-      itmo::bn_stats_kernel<<<int(std::min<size_t>(g_stats, (npix + 63) / 64)), 256, 0, s>>>(t->z[li], npix, L.cout,
+      if (!(fuse_stats && L.kind != kRgbConv))
+        itmo::bn_stats_kernel<<<int(std::min<size_t>(g_stats, (npix + 63) / 64)), 256, 0, s>>>(t->z[li], npix, L.cout,
                                                                                            fstats(t, li));
       itmo::bn_finalize_kernel<<<(L.cout + 127) / 128, 128, 0, s>>>(
           fstats(t, li), L.cout, double(npix), 1e-3f, 0.99f, t->params + lay.gamma[li], t->params + lay.beta[li],
