@@ -74,6 +74,7 @@ struct ConvParams {
                        // accumulators and keeps the two small cross terms in the last one.
   int dbg;             // timing experiments only (results wrong): 16 no activation TMA, 32 no epilogue, 64 no MMAs
   int kb_hi;           // channel blocks of the leading (x*w_hi) part; the rest go to accumulator S-1
+  int cout_log2;       // log2(cout) when cout is a power of two, else -1
   int no_relu;         // 1: y = (acc + bias) * scale + shift without the ReLU (data-gradient convolutions of the training step)
   double* stats;       // training forward (16-bit modes): per-channel sum [cout] and sum of squares [cout] of the stored
                        // output z = ReLU(acc + bias) are accumulated here (BatchNormalization batch statistics,
@@ -173,6 +174,62 @@ __device__ __forceinline__ float warp_transpose_sum32(float (&v)[32], int lane) 
     }
   }
   return v[0];
+}
+
+// 4x4 transposition of 16-byte pieces inside each quad of lanes: on entry lane j (= lane & 3) holds pieces
+// t[4k..4k+3], k = 0..3, of ITS row; on exit t[4k..4k+3] is piece j of the row lane (quad base + k) came with.
+__device__ __forceinline__ void quad_transpose_16B(uint32_t (&t)[16], int lane) {
+#pragma unroll
+  for (int bit = 1; bit <= 2; bit <<= 1) {
+    const bool upper = (lane & bit) != 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      if (k & bit) continue;               // pairs (k, k + bit)
+#pragma unroll
+      for (int w = 0; w < 4; ++w) {
+        const uint32_t send = upper ? t[4 * k + w] : t[4 * (k + bit) + w];
+        const uint32_t got = __shfl_xor_sync(0xFFFFFFFFu, send, bit);
+        if (upper) t[4 * k + w] = got; else t[4 * (k + bit) + w] = got;
+      }
+    }
+  }
+}
+
+// y = ReLU(acc + bias) * scale + shift on one 32-column accumulator chunk (kStats: training forward, identity
+// affine; kLinear: no ReLU, the data-gradient convolutions). The vectors are read as 128-bit broadcasts.
+template <bool kStats, bool kLinear>
+__device__ __forceinline__ void epi_affine(const uint32_t (&v)[32], float (&f)[32], const float4 (&b4)[8],
+                                           const float* __restrict__ ss, const float* __restrict__ st) {
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    float a0 = __uint_as_float(v[4 * i]) + b4[i].x, a1 = __uint_as_float(v[4 * i + 1]) + b4[i].y;
+    float a2 = __uint_as_float(v[4 * i + 2]) + b4[i].z, a3 = __uint_as_float(v[4 * i + 3]) + b4[i].w;
+    if constexpr (!kLinear) {
+      a0 = fmaxf(a0, 0.f);
+      a1 = fmaxf(a1, 0.f);
+      a2 = fmaxf(a2, 0.f);
+      a3 = fmaxf(a3, 0.f);
+    }
+    f[4 * i] = a0;
+    f[4 * i + 1] = a1;
+    f[4 * i + 2] = a2;
+    f[4 * i + 3] = a3;
+  }
+  if constexpr (!kStats) {
+    float4 sc[8], sh[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      sc[i] = reinterpret_cast<const float4*>(ss)[i];
+      sh[i] = reinterpret_cast<const float4*>(st)[i];
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      f[4 * i] = fmaf(f[4 * i], sc[i].x, sh[i].x);
+      f[4 * i + 1] = fmaf(f[4 * i + 1], sc[i].y, sh[i].y);
+      f[4 * i + 2] = fmaf(f[4 * i + 2], sc[i].z, sh[i].z);
+      f[4 * i + 3] = fmaf(f[4 * i + 3], sc[i].w, sh[i].w);
+    }
+  }
 }
 
 template <typename Elem, int BLOCK_N, int SWZ>
@@ -512,18 +569,12 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
           if (split_by_chunk && (chunk & 1) != ws) continue;
           uint32_t v[kChunk];
           sm100::tmem_ld_32x32b_x32(taddr + uint32_t(j * BLOCK_N + chunk * kChunk), v);
-          sm100::tmem_ld_wait();
-          for (int sa = 1; sa < S; ++sa) {  // split accumulators: sum the partial results in fp32 (rn)
-            uint32_t u[kChunk];
-            sm100::tmem_ld_32x32b_x32(taddr + uint32_t((sa * nm + j) * BLOCK_N + chunk * kChunk), u);
-            sm100::tmem_ld_wait();
-#pragma unroll
-            for (int i = 0; i < kChunk; ++i) v[i] = __float_as_uint(__uint_as_float(v[i]) + __uint_as_float(u[i]));
-          }
+          // output coordinates and the bias vector while the TMEM load is in flight
           const int n_glob = n_tile * BLOCK_N + chunk * kChunk;  // row of the packed weight matrix
           int co0, oy, ox, Ho, Wo;
           if (p.mode == kModeConvT2x2) {
-            const int ph = n_glob / p.cout;  // phase a*2+b of the 2x2 transposed kernel
+            // phase a*2+b of the 2x2 transposed kernel (shift when cout is a power of two: no division chain)
+            const int ph = p.cout_log2 >= 0 ? (n_glob >> p.cout_log2) : n_glob / p.cout;
             co0 = n_glob - ph * p.cout;
             oy = 2 * y + (ph >> 1);
             ox = 2 * x + (ph & 1);
@@ -536,18 +587,33 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
             Ho = p.H;
             Wo = p.W;
           }
-          float f[kChunk];
+          float4 b4[8];
 #pragma unroll
-          for (int i = 0; i < kChunk; ++i) {
-            const float a = __uint_as_float(v[i]) + s_bias[co0 + i];
-            f[i] = with_stats ? fmaxf(a, 0.f) : fmaf(p.no_relu ? a : fmaxf(a, 0.f), s_scale[co0 + i], s_shift[co0 + i]);
+          for (int i = 0; i < 8; ++i) b4[i] = reinterpret_cast<const float4*>(s_bias + co0)[i];
+          sm100::tmem_ld_wait();
+          for (int sa = 1; sa < S; ++sa) {  // split accumulators: sum the partial results in fp32 (rn)
+            uint32_t u[kChunk];
+            sm100::tmem_ld_32x32b_x32(taddr + uint32_t((sa * nm + j) * BLOCK_N + chunk * kChunk), u);
+            sm100::tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < kChunk; ++i) v[i] = __float_as_uint(__uint_as_float(v[i]) + __uint_as_float(u[i]));
           }
+          // bias / ReLU / BN affine of the chunk; one straight-line variant per mode so that the broadcast
+          // shared-memory reads are hoisted ahead of the arithmetic (run-time flags inside the unrolled loop
+          // serialise load -> use -> load and leave the LSU latency exposed)
+          float f[kChunk];
+          if (with_stats) epi_affine<true, false>(v, f, b4, s_scale + co0, s_shift + co0);
+          else if (p.no_relu) epi_affine<false, true>(v, f, b4, s_scale + co0, s_shift + co0);
+          else epi_affine<false, false>(v, f, b4, s_scale + co0, s_shift + co0);
           if (p.head_dtype != kHeadNone) {
 #pragma unroll
-            for (int i = 0; i < kChunk; ++i) {
-              h0 = fmaf(f[i], s_head[0 * 64 + co0 + i], h0);
-              h1 = fmaf(f[i], s_head[1 * 64 + co0 + i], h1);
-              h2 = fmaf(f[i], s_head[2 * 64 + co0 + i], h2);
+            for (int i = 0; i < kChunk; i += 4) {
+              const float4 w0 = *reinterpret_cast<const float4*>(s_head + 0 * 64 + co0 + i);
+              const float4 w1 = *reinterpret_cast<const float4*>(s_head + 1 * 64 + co0 + i);
+              const float4 w2 = *reinterpret_cast<const float4*>(s_head + 2 * 64 + co0 + i);
+              h0 = fmaf(f[i + 3], w0.w, fmaf(f[i + 2], w0.z, fmaf(f[i + 1], w0.y, fmaf(f[i], w0.x, h0))));
+              h1 = fmaf(f[i + 3], w1.w, fmaf(f[i + 2], w1.z, fmaf(f[i + 1], w1.y, fmaf(f[i], w1.x, h1))));
+              h2 = fmaf(f[i + 3], w2.w, fmaf(f[i + 2], w2.z, fmaf(f[i + 1], w2.y, fmaf(f[i], w2.x, h2))));
             }
           }
           const size_t pix = (size_t(img) * Ho + oy) * Wo + ox;
@@ -575,9 +641,21 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
               }
             }
             if (p.out != nullptr) {
-              uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<Elem*>(p.out) + pix * p.cout + co0);
+              // The four lanes of a quad hold four horizontally adjacent pixels (64 B of channels each). A 4x4
+              // transposition of the 16-byte pieces inside the quad lets every store instruction write 64
+              // contiguous bytes per pixel (8 lines per request instead of 32 half-written sectors' worth of lines).
+              uint32_t t[kChunk / 2];
 #pragma unroll
-              for (int i = 0; i < kChunk / 8; ++i) dst[i] = make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
+              for (int i = 0; i < kChunk / 2; ++i) t[i] = pk[i];
+              quad_transpose_16B(t, lane);
+              const int jq = lane & 3;
+              const int xstep = p.mode == kModeConvT2x2 ? 2 : 1;   // output pixels between two lanes of the quad
+              Elem* base = reinterpret_cast<Elem*>(p.out) + co0 + 8 * jq;
+#pragma unroll
+              for (int k = 0; k < 4; ++k) {
+                const size_t pk_pix = size_t(ptrdiff_t(pix) + ptrdiff_t((k - jq) * xstep));
+                *reinterpret_cast<uint4*>(base + pk_pix * p.cout) = make_uint4(t[4 * k], t[4 * k + 1], t[4 * k + 2], t[4 * k + 3]);
+              }
             }
             if (p.pooled != nullptr) {
 #pragma unroll

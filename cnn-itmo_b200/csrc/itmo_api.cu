@@ -473,6 +473,9 @@ int run_conv(const ConvArgs& a, cudaStream_t stream) {
   p.nm = nm;
   p.n_tiles = n_tiles;
   p.cout = a.cout;
+  p.cout_log2 = -1;
+  for (int b = 0; b < 16; ++b)
+    if ((1 << b) == a.cout) p.cout_log2 = b;
   p.mode = a.mode;
   p.a_stage_bytes = a_stage;
   p.n_a_stages = n_a;
@@ -556,7 +559,10 @@ template <typename Elem>
 int run_rgb_tc_t(const void* in, int in_dtype, int n, int h, int w, const float* w_hwio, const float* bias,
                  const float* scale, const float* shift, void* out, cudaStream_t stream) {
   const int tiles = n * (h / itmo::kRgbTileH) * (w / itmo::kRgbTileW);
-  const int grid = std::min(tiles, num_sms() * 8);
+  // persistent grid = exactly the CTAs resident at once: __launch_bounds__(128, 5) caps the registers for five
+  // CTAs per SM, which 23 KB of shared memory and 32 TMEM columns each also allow
+  constexpr int per_sm = 5;
+  const int grid = std::min(tiles, num_sms() * per_sm);
   if (in_dtype == ITMO_DT_U8)
     itmo::rgb_conv_tc_kernel<Elem, uint8_t><<<grid, 128, 0, stream>>>((const uint8_t*)in, (Elem*)out, w_hwio, bias,
                                                                        scale, shift, n, h, w, 1.0f / 255.0f);

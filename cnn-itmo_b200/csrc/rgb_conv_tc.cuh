@@ -23,7 +23,7 @@ constexpr int kRgbHaloH = kRgbTileH + 2, kRgbHaloW = kRgbTileW + 2;
 // in:  [NB,H,W,3] uint8 (raw pixels) or float (already /255); out: [NB,H,W,32] Elem
 // w_hwio: [27][32] fp32 (Keras HWIO flattened), in_scale: 1/255 for uint8 input, 1 for float input
 template <typename Elem, typename InT>
-__global__ void __launch_bounds__(128) rgb_conv_tc_kernel(const InT* __restrict__ in, Elem* __restrict__ out,
+__global__ void __launch_bounds__(128, 5) rgb_conv_tc_kernel(const InT* __restrict__ in, Elem* __restrict__ out,
                                                           const float* __restrict__ w_hwio,
                                                           const float* __restrict__ bias,
                                                           const float* __restrict__ scale,
@@ -80,6 +80,29 @@ __global__ void __launch_bounds__(128) rgb_conv_tc_kernel(const InT* __restrict_
   uint32_t phase = 0;
   constexpr uint32_t idesc = sm100::make_idesc(ElemTraits<Elem>::kFmt, 128, 32);
 
+  // uint8 input: the halo rows are fetched as aligned 32-bit words (26 words cover the 102 bytes of a halo row),
+  // two independent loads per thread, issued one tile ahead so that their latency hides behind the MMA and the
+  // epilogue of the current tile. Needs a 4-byte aligned input pointer (W is a multiple of 32, so every row is).
+  constexpr int kWordsPerRow = 26, kWords = kRgbHaloH * kWordsPerRow;   // 156
+  const bool fast_u8 = sizeof(InT) == 1 && (reinterpret_cast<uintptr_t>(in) & 3) == 0;
+  auto fetch_word = [&](int tile, int idx) -> uint32_t {
+    if (idx >= kWords || tile >= total) return 0u;
+    const int tx = tile % tiles_x;
+    const int ty = (tile / tiles_x) % tiles_y;
+    const int img = tile / (tiles_x * tiles_y);
+    const int hy = idx / kWordsPerRow, k = idx - hy * kWordsPerRow;
+    const int yy = ty * kRgbTileH + hy - 1;
+    const int off = tx * kRgbTileW * 3 - 4 + 4 * k;             // byte offset inside the image row
+    if (yy < 0 || yy >= H || off < 0 || off >= 3 * W) return 0u;  // 'same' padding (whole words: 3*W % 4 == 0)
+    return __ldg(reinterpret_cast<const uint32_t*>(reinterpret_cast<const uint8_t*>(in) +
+                                                   (size_t(img) * H + yy) * W * 3 + off));
+  };
+  uint32_t nw0 = 0, nw1 = 0;
+  if (fast_u8) {
+    nw0 = fetch_word(blockIdx.x, tid);
+    nw1 = fetch_word(blockIdx.x, tid + 128);
+  }
+
   for (int tile = blockIdx.x; tile < total; tile += gridDim.x) {
     const int tx = tile % tiles_x;
     const int ty = (tile / tiles_x) % tiles_y;
@@ -87,16 +110,36 @@ __global__ void __launch_bounds__(128) rgb_conv_tc_kernel(const InT* __restrict_
     const int x0 = tx * kRgbTileW, y0 = ty * kRgbTileH;
 
     // ---- halo tile -> shared memory as floats (zero outside the image = 'same' padding)
-    for (int i = tid; i < kRgbHaloH * kRgbHaloW * 3; i += 128) {
-      const int hy = i / (kRgbHaloW * 3), rem = i - hy * (kRgbHaloW * 3);
-      const int hx = rem / 3;
-      const int yy = y0 + hy - 1, xx = x0 + hx - 1;
-      float v = 0.f;
-      if (yy >= 0 && yy < H && xx >= 0 && xx < W)
-        v = float(in[((size_t(img) * H + yy) * W + x0 - 1) * 3 + rem]);
-      s_halo[hy][rem] = v;
+    if (fast_u8) {
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int idx = tid + 128 * h;
+        const uint32_t wv = h ? nw1 : nw0;
+        if (idx < kWords) {
+          const int hy = idx / kWordsPerRow, k = idx - hy * kWordsPerRow;
+#pragma unroll
+          for (int b = 0; b < 4; ++b) {
+            const int rem = 4 * k - 1 + b;                      // halo-row byte this word byte lands on
+            if (rem >= 0 && rem < kRgbHaloW * 3) s_halo[hy][rem] = float((wv >> (8 * b)) & 0xFFu);
+          }
+        }
+      }
+    } else {
+      for (int i = tid; i < kRgbHaloH * kRgbHaloW * 3; i += 128) {
+        const int hy = i / (kRgbHaloW * 3), rem = i - hy * (kRgbHaloW * 3);
+        const int hx = rem / 3;
+        const int yy = y0 + hy - 1, xx = x0 + hx - 1;
+        float v = 0.f;
+        if (yy >= 0 && yy < H && xx >= 0 && xx < W)
+          v = float(in[((size_t(img) * H + yy) * W + x0 - 1) * 3 + rem]);
+        s_halo[hy][rem] = v;
+      }
     }
     __syncthreads();
+    if (fast_u8) {   // next tile's words: in flight during the im2col, the MMA and the epilogue
+      nw0 = fetch_word(tile + gridDim.x, tid);
+      nw1 = fetch_word(tile + gridDim.x, tid + 128);
+    }
 
     // ---- im2col: k = dy*9 + dx*3 + ch = dy*9 + (9 consecutive halo values starting at pixel c)
     {
@@ -146,9 +189,21 @@ __global__ void __launch_bounds__(128) rgb_conv_tc_kernel(const InT* __restrict_
                             s_scale[2 * i + 1], s_shift[2 * i + 1]);
       pk[i] = pack2<Elem>(f0, f1);
     }
-    uint4* dst = reinterpret_cast<uint4*>(out + ((size_t(img) * H + y0 + r) * W + x0 + c) * 32);
+    // The 32 pixels of a warp are 2 KB of contiguous output. Stage them in the (now idle) im2col tile with a
+    // 16-byte-piece swizzle, then store 512 contiguous bytes per instruction instead of 32 pieces 64 B apart.
+    uint8_t* stage = s_a + warp * 2048;
+    const int lane = tid & 31;
 #pragma unroll
-    for (int i = 0; i < 4; ++i) dst[i] = make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
+    for (int i = 0; i < 4; ++i)
+      *reinterpret_cast<uint4*>(stage + lane * 64 + ((i ^ ((lane >> 1) & 3)) * 16)) =
+          make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
+    __syncwarp();
+    uint4* dst = reinterpret_cast<uint4*>(out + ((size_t(img) * H + y0 + r) * W + x0) * 32);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int u = k * 32 + lane, px = u >> 2;
+      dst[u] = *reinterpret_cast<const uint4*>(stage + px * 64 + (((u & 3) ^ ((px >> 1) & 3)) * 16));
+    }
   }
 
   sm100::tc_fence_before_sync();
