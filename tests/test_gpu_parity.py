@@ -193,6 +193,39 @@ def test_first_layer_from_raw_pixels(dev, prec, in_dtype):
     assert (np.abs(got - ref) <= tol).all(), float(np.abs(got - ref).max())
 
 
+@pytest.mark.parametrize('offset', [0, 1, 2, 3])
+def test_first_layer_uint8_pointer_alignment(dev, offset):
+    """conv2d_1 from uint8 pixels at every byte alignment of the input pointer: 4-byte aligned pointers take the
+    word-wise prefetched halo path of rgb_conv_tc_kernel, the others its byte-wise path; both must give the same
+    result (bit-exact: same operands, same MMA)."""
+    L, lib = _lib()
+    n, h = 3, 512
+    g = torch.Generator().manual_seed(23 + offset)
+    xin = torch.randint(0, 256, (n, h, h, 3), generator=g, dtype=torch.uint8)
+    k = torch.randn(3, 3, 3, 32, generator=g) * (2.0 / 27) ** 0.5
+    bias = torch.rand(32, generator=g) * 0.2 - 0.1
+    bn, scale, shift = _bn_params(32, g)
+    ref = _oracle_block('conv', torch.from_numpy(R.preprocess_u8(xin.numpy())), k, bias, bn).permute(0, 2, 3, 1).numpy()
+    d = lambda t: t.to(dev).contiguous()
+    kd, bd, sd, td = d(k), d(bias), d(scale), d(shift)
+    buf = torch.zeros(xin.numel() + 8, dtype=torch.uint8, device=dev)
+    assert buf.data_ptr() % 4 == 0
+    buf[offset:offset + xin.numel()] = xin.to(dev).reshape(-1)
+    out = torch.full((n, h, h, 32), float('nan'), dtype=torch.bfloat16, device=dev)
+    L.check(lib.itmo_conv3x3_bn_rgb(L.PREC_BF16, buf.data_ptr() + offset, L.DT_U8, n, h, h, kd.data_ptr(),
+                                    bd.data_ptr(), sd.data_ptr(), td.data_ptr(), 32, out.data_ptr(), None))
+    torch.cuda.synchronize()
+    got = out.float().cpu().double().numpy()
+    assert (np.abs(got - ref) <= _tol(ref, 'bf16')).all(), float(np.abs(got - ref).max())
+    if offset:
+        aligned = torch.full_like(out, float('nan'))
+        xd = xin.to(dev).contiguous()
+        L.check(lib.itmo_conv3x3_bn_rgb(L.PREC_BF16, xd.data_ptr(), L.DT_U8, n, h, h, kd.data_ptr(), bd.data_ptr(),
+                                        sd.data_ptr(), td.data_ptr(), 32, aligned.data_ptr(), None))
+        torch.cuda.synchronize()
+        assert torch.equal(aligned.view(torch.int16), out.view(torch.int16))
+
+
 @pytest.mark.parametrize('prec', PRECS)
 def test_last_conv_with_fused_head(dev, prec):
     """conv2d_14 + Conv2D(3,1,sigmoid) (model.py:262,276) + the uint8 truncation of predict.py:64."""
