@@ -640,15 +640,17 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
                 atomicAdd(&s_shift[co0 + lane], tsq);
               }
             }
-            if (p.out != nullptr) {
-              // The four lanes of a quad hold four horizontally adjacent pixels (64 B of channels each). A 4x4
-              // transposition of the 16-byte pieces inside the quad lets every store instruction write 64
-              // contiguous bytes per pixel (8 lines per request instead of 32 half-written sectors' worth of lines).
-              uint32_t t[kChunk / 2];
+            // The four lanes of a quad hold four horizontally adjacent pixels (64 B of channels each). A 4x4
+            // transposition of the 16-byte pieces inside the quad lets every store instruction write 64
+            // contiguous bytes per pixel (8 lines per request instead of 32 half-written sectors' worth of lines).
+            // After it lane j of a quad holds piece j of all four pixels, so the horizontal half of the 2x2
+            // max-pool is in-thread and only the vertical half needs a shuffle (8 instead of 32 per chunk).
+            uint32_t t[kChunk / 2];
 #pragma unroll
-              for (int i = 0; i < kChunk / 2; ++i) t[i] = pk[i];
-              quad_transpose_16B(t, lane);
-              const int jq = lane & 3;
+            for (int i = 0; i < kChunk / 2; ++i) t[i] = pk[i];
+            if (p.out != nullptr || p.pooled != nullptr) quad_transpose_16B(t, lane);
+            const int jq = lane & 3;
+            if (p.out != nullptr) {
               const int xstep = p.mode == kModeConvT2x2 ? 2 : 1;   // output pixels between two lanes of the quad
               Elem* base = reinterpret_cast<Elem*>(p.out) + co0 + 8 * jq;
 #pragma unroll
@@ -658,16 +660,19 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
               }
             }
             if (p.pooled != nullptr) {
+              uint32_t m[8];   // [0..3]: pixels 0,1 of the quad -> pooled column 0; [4..7]: pixels 2,3 -> column 1
 #pragma unroll
-              for (int i = 0; i < kChunk / 2; ++i) {
-                pk[i] = max2<Elem>(pk[i], __shfl_xor_sync(0xFFFFFFFFu, pk[i], 1));   // horizontal neighbour
-                pk[i] = max2<Elem>(pk[i], __shfl_xor_sync(0xFFFFFFFFu, pk[i], 8));   // vertical neighbour
+              for (int w = 0; w < 4; ++w) {
+                m[w] = max2<Elem>(t[w], t[4 + w]);
+                m[4 + w] = max2<Elem>(t[8 + w], t[12 + w]);
               }
-              if (pool_writer) {
-                uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<Elem*>(p.pooled) + ppix * p.cout + co0);
 #pragma unroll
-                for (int i = 0; i < kChunk / 8; ++i)
-                  dst[i] = make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
+              for (int w = 0; w < 8; ++w) m[w] = max2<Elem>(m[w], __shfl_xor_sync(0xFFFFFFFFu, m[w], 8));  // row below
+              if ((lane & 8) == 0) {                             // even row of the block writes
+                const size_t pp0 = (size_t(img) * (p.H / 2) + (y >> 1)) * (p.W / 2) + ((x - jq) >> 1);
+                Elem* pb = reinterpret_cast<Elem*>(p.pooled) + co0 + 8 * jq;
+                *reinterpret_cast<uint4*>(pb + pp0 * p.cout) = make_uint4(m[0], m[1], m[2], m[3]);
+                *reinterpret_cast<uint4*>(pb + (pp0 + 1) * p.cout) = make_uint4(m[4], m[5], m[6], m[7]);
               }
             }
           } else {
