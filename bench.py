@@ -318,7 +318,18 @@ def run_b200_arm(a):
             continue
         ms_per_step = ms / a.steps
         tf = fl * B / (ms_per_step * 1e-3) / 1e12 if ms_per_step > 0 else 0.0
+        # algorithmic HBM bytes per image: every source read once, the output written once (+ the
+        # pooled copy), the weights once per launch; uint8 pixels in front of conv2d_1, uint8 RGB behind conv2d_14
+        es = 2 if a.precision in ('bf16', 'fp16') else 4
+        hout = 2 * l.hin if l.kind == 'convT' else l.hin
+        by = l.hin ** 2 * (3 if l.index == 0 else sum(l.cin) * es)
+        by += IMG * IMG * 3 if l.index == 17 else hout ** 2 * l.cout * es * (1.25 if l.pool else 1.0)
+        gbs = by * B / (ms_per_step * 1e-3) / 1e9 if ms_per_step > 0 else 0.0
+        t_tensor = fl / (peaks['tflops_sustained'] * 1e12)
+        t_hbm = by / (peaks['hbm_gbs'] * 1e9)
         per_layer.append({'layer': l.name, 'ms_per_step': round(ms_per_step, 4), 'tflops': round(tf, 1),
+                          'gbs': round(gbs, 1), 'bound': 'tensor' if t_tensor >= t_hbm else 'hbm',
+                          'frac_of_bound': round(max(t_tensor, t_hbm) * B / (ms_per_step * 1e-3), 4) if ms_per_step > 0 else None,
                           'launches_per_step': calls / a.steps})
         if l.index != 0:
             igemm_flops += fl * B
@@ -343,12 +354,16 @@ def run_b200_arm(a):
                 'peak_source': f"{peaks['source']} (bf16 sustained; kernel timed inside a long step)",
                 'flops_per_launch': igemm_flops / max(1, n_igemm),
                 'avg_launch_ms': round(igemm_ms / max(1, n_igemm), 4),
-                'share_of_step': round(igemm_ms / ms_step, 4)}
+                'share_of_step': round(igemm_ms / ms_step, 4),
+                # every layer against ITS bound (tensor: bf16 sustained peak; hbm: measured copy bandwidth)
+                'layers': [{k: p[k] for k in ('layer', 'ms_per_step', 'tflops', 'gbs', 'bound', 'frac_of_bound')}
+                           for p in per_layer]}
 
     if rank == 0:
         log('per-layer (rank 0, CUDA events inside the timed region):')
         for p in per_layer:
-            log(f"  {p['layer']:<22} {p['ms_per_step']:9.3f} ms/step  {p['tflops']:8.1f} TFLOP/s")
+            log(f"  {p['layer']:<22} {p['ms_per_step']:9.3f} ms/step  {p['tflops']:8.1f} TFLOP/s  {p['gbs']:8.1f} GB/s  "
+                f"{p['bound']:<6} {p['frac_of_bound']}")
         log(f'  sum of layers {sum(p["ms_per_step"] for p in per_layer):.3f} ms, step {ms_step:.3f} ms')
         os.makedirs(os.path.join(ROOT, 'gpurun_out'), exist_ok=True)
         with open(os.path.join(ROOT, 'gpurun_out', f'bench_layers_{a.precision}_n{world}.json'), 'w') as f:

@@ -97,6 +97,11 @@ def read_checkpoint(path: str) -> Tuple[Weights, Dict[str, Any]]:
                     meta[key] = json.loads(_as_str(top[key]))
                 except Exception:  # noqa: BLE001
                     meta[key] = _as_str(top[key])
+        if 'optimizer_weights' in f:   # model.save(include_optimizer=True): the state ModelCheckpoint keeps (main.py:123-124)
+            og = f['optimizer_weights']
+            onames = _names(og.attrs['weight_names']) if 'weight_names' in og.attrs else []
+            meta['optimizer_weight_names'] = onames
+            meta['optimizer_weights'] = [np.asarray(og[n].read() if hasattr(og[n], 'read') else og[n]) for n in onames]
     finally:
         f.close()
     if len(kernels) != graph.NUM_LAYERS or len(bns) != graph.NUM_LAYERS - 1:
@@ -178,15 +183,19 @@ def model_config() -> Dict[str, Any]:
                        'output_layers': [['conv2d_15', 0, 0]]}}
 
 
-def training_config() -> Dict[str, Any]:
-    """model.compile(optimizer='rmsprop', loss='mse', metrics=['accuracy']) (model.py:281)."""
-    return {'optimizer_config': {'class_name': 'RMSprop',
-                                 'config': {'lr': 0.001, 'rho': 0.9, 'decay': 0.0, 'epsilon': 1e-07}},
+def training_config(optimizer: str = 'rmsprop') -> Dict[str, Any]:
+    """model.compile(optimizer='rmsprop', loss='mse', metrics=['accuracy']) (model.py:281); 'adam' = the variant in
+    the comments of model.py:280,282 (beta_1 = 0.5)."""
+    opt = {'class_name': 'RMSprop', 'config': {'lr': 0.001, 'rho': 0.9, 'decay': 0.0, 'epsilon': 1e-07}}
+    if optimizer == 'adam':
+        opt = {'class_name': 'Adam', 'config': {'lr': 0.001, 'beta_1': 0.5, 'beta_2': 0.999, 'decay': 0.0,
+                                                'epsilon': 1e-07, 'amsgrad': False}}
+    return {'optimizer_config': opt,
             'loss': 'mse', 'metrics': ['accuracy'], 'sample_weight_mode': None, 'loss_weights': None}
 
 
 def write_checkpoint(path: str, weights: Weights, weights_only: bool = False,
-                     optimizer_weights: Optional[List[np.ndarray]] = None):
+                     optimizer_weights: Optional[List[np.ndarray]] = None, optimizer: str = 'rmsprop'):
     """Write ``weights`` (execution order) in the Keras HDF5 layout. ``weights_only`` mimics
     ``model.save_weights`` (no model_config, groups at the root)."""
     if len(weights) != graph.NUM_LAYERS:
@@ -214,13 +223,16 @@ def write_checkpoint(path: str, weights: Weights, weights_only: bool = False,
         w.root.attrs['keras_version'] = h5min.VlenStr(b'2.2.4')
         w.root.attrs['backend'] = h5min.VlenStr(b'tensorflow')
         w.root.attrs['model_config'] = h5min.VlenStr(json.dumps(model_config()).encode('utf-8'))
-        w.root.attrs['training_config'] = h5min.VlenStr(json.dumps(training_config()).encode('utf-8'))
+        w.root.attrs['training_config'] = h5min.VlenStr(json.dumps(training_config(optimizer)).encode('utf-8'))
         if optimizer_weights is not None:
             og = w.group('optimizer_weights')
             names = []
+            cls = 'Adam' if optimizer == 'adam' else 'RMSprop'
             for i, a in enumerate(optimizer_weights):
-                n = f'training/RMSprop/Variable{"_" + str(i) if i else ""}:0'
-                w.dataset('optimizer_weights/' + n, np.asarray(a, dtype=np.float32))
+                # Keras 2.2.x names: K.zeros(...) variables of the optimizer's name scope, numbered in creation order
+                n = f'training/{cls}/Variable{"_" + str(i) if i else ""}:0'
+                a = np.asarray(a)
+                w.dataset('optimizer_weights/' + n, a if a.dtype == np.int64 else a.astype(np.float32))
                 names.append(n.encode('utf-8'))
             og.attrs['weight_names'] = np.array(names) if names else np.zeros((0,), dtype=np.float64)
     w.save(path)

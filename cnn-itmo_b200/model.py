@@ -283,9 +283,14 @@ class Model:
         """model.save (what ModelCheckpoint calls every epoch, main.py:123-124): full Keras HDF5 layout."""
         if not overwrite and os.path.exists(filepath):
             raise OSError(f'{filepath} exists')
+        opt_w, opt_name = getattr(self, '_optimizer_weights', None), getattr(self, '_optimizer_name', 'rmsprop')
         if getattr(self, '_trainer', None) is not None:
             self._pull_trained_weights()
-        checkpoint.write_checkpoint(filepath, self._weights, weights_only=False)
+            opt_w, opt_name = self._trainer.get_optimizer_weights(), self._trainer.optimizer
+        # /optimizer_weights (RMSprop accumulators in trainable_weights order) so that training can resume from the
+        # file, here or in Keras (SURVEY 8f-3)
+        checkpoint.write_checkpoint(filepath, self._weights, weights_only=False,
+                                    optimizer_weights=opt_w if include_optimizer else None, optimizer=opt_name)
 
     # ---- training (main.py:126-132) -----------------------------------------------------------------
     def _ensure_trainer(self, micro_batch: Optional[int] = None):
@@ -298,6 +303,10 @@ class Model:
             kw = {} if isinstance(self.optimizer, str) else {k: v for k, v in self.optimizer.items() if k != 'name'}
             self._trainer = train.Trainer(self._weights, micro_batch=micro_batch or self.train_micro_batch,
                                           device=self.device, optimizer=opt, **kw)
+            pending = getattr(self, '_optimizer_weights', None)
+            if pending is not None and getattr(self, '_optimizer_name', opt) == self._trainer.optimizer:
+                self._trainer.set_optimizer_weights(pending)   # resume from a checkpoint's /optimizer_weights
+            self._optimizer_weights = None
         return self._trainer
 
     train_micro_batch = 8
@@ -387,6 +396,15 @@ def load_model(filepath: str, custom_objects=None, compile: bool = True, precisi
     model = Model(weights, precision=precision, device=device, max_batch=max_batch,
                   bn_epsilon=meta.get('bn_epsilon', graph.BN_EPS))
     model.meta = meta
+    opt_name = 'rmsprop'
+    tc = meta.get('training_config')
+    if isinstance(tc, dict) and str(tc.get('optimizer_config', {}).get('class_name', '')).lower() == 'adam':
+        opt_name = 'adam'
     if compile:
-        model.compile(optimizer='rmsprop', loss='mse', metrics=['accuracy'])
+        model.compile(optimizer=opt_name, loss='mse', metrics=['accuracy'])
+        if meta.get('optimizer_weights'):
+            # like keras.models.load_model: the optimizer state travels with the model and is installed when the
+            # training engine is first needed (Model._ensure_trainer)
+            model._optimizer_weights = meta['optimizer_weights']
+            model._optimizer_name = opt_name
     return model

@@ -89,6 +89,57 @@ def flatten_layers(layers: Sequence[Dict[str, np.ndarray]], layout=None) -> np.n
     return flat
 
 
+def keras_trainable_order() -> List[Tuple[int, str]]:
+    """(layer index, field) of every trainable weight in the order of Keras' ``model.trainable_weights`` — layers as
+    ``model.layers`` lists them, Conv2D / Conv2DTranspose [kernel, bias], BatchNormalization [gamma, beta]. This is
+    the order of the RMSprop accumulators in a checkpoint's /optimizer_weights group (main.py:123-124)."""
+    out: List[Tuple[int, str]] = []
+    for k in graph.keras_layers():
+        if k.weight_layer is None:
+            continue
+        out += [(k.weight_layer, f) for f in (('gamma', 'beta') if k.cls == 'BatchNormalization' else ('kernel', 'bias'))]
+    return out
+
+
+def optimizer_weights_from_flat(state: np.ndarray, layout, optimizer: str, iterations: int = 0) -> List[np.ndarray]:
+    """Flat optimizer state [2 * n_params] (RMSprop: accumulators in the first half; Adam: m | v) -> the list Keras
+    2.2.x keeps in ``optimizer.weights``: RMSprop = one accumulator per trainable weight; Adam = [iterations] + ms + vs."""
+    n = state.size // 2
+    order = keras_trainable_order()
+
+    def half(h):
+        arrs = []
+        for li, f in order:
+            off, cnt = layout[li][f]
+            a = state[h * n + off:h * n + off + cnt].copy()
+            arrs.append(a.reshape(graph.kernel_shape(graph.LAYERS[li])) if f == 'kernel' else a)
+        return arrs
+    if optimizer == 'rmsprop':
+        return half(0)
+    return [np.asarray(iterations, np.int64)] + half(0) + half(1)
+
+
+def optimizer_weights_to_flat(weights: Sequence[np.ndarray], layout, optimizer: str, n_params: int):
+    """Inverse of optimizer_weights_from_flat -> (flat state [2 * n_params], iterations)."""
+    order = keras_trainable_order()
+    want = len(order) if optimizer == 'rmsprop' else 1 + 2 * len(order)
+    if len(weights) != want:
+        raise ValueError(f'{optimizer} state of this model has {want} arrays, got {len(weights)}')
+    state = np.zeros(2 * n_params, np.float32)
+    it = 0
+    ws = list(weights)
+    if optimizer != 'rmsprop':
+        it = int(np.asarray(ws.pop(0)).reshape(-1)[0])
+    for h in range(1 if optimizer == 'rmsprop' else 2):
+        for i, (li, f) in enumerate(order):
+            off, cnt = layout[li][f]
+            a = np.asarray(ws[h * len(order) + i], np.float32).reshape(-1)
+            if a.size != cnt:
+                raise ValueError(f'optimizer weight {i} ({graph.LAYERS[li].name}/{f}) has {a.size} elements, expected {cnt}')
+            state[h * n_params + off:h * n_params + off + cnt] = a
+    return state, it
+
+
 class Trainer:
     def __init__(self, weights: Sequence[Dict[str, np.ndarray]], micro_batch: int = 8, image_hw=(512, 512),
                  device: int = 0, optimizer: str = 'rmsprop', lr: Optional[float] = None, **opt_kwargs):
@@ -179,6 +230,19 @@ class Trainer:
         """Per-layer dicts in the Keras layouts (what checkpoint.write_checkpoint / Model take)."""
         self._torch.cuda.synchronize(self._dev)
         return self._unflatten(self.params.cpu().numpy(), True)
+
+    def get_optimizer_weights(self) -> List[np.ndarray]:
+        """The optimizer state as Keras lists it in ``model.optimizer.weights`` (what model.save writes under
+        /optimizer_weights, main.py:123-124)."""
+        self._torch.cuda.synchronize(self._dev)
+        return optimizer_weights_from_flat(self.opt_state.cpu().numpy(), self.layout, self.optimizer, self.step_index)
+
+    def set_optimizer_weights(self, weights: Sequence[np.ndarray]):
+        """Resume: load the state a checkpoint's /optimizer_weights group holds."""
+        state, it = optimizer_weights_to_flat(weights, self.layout, self.optimizer, self.n_params)
+        self.opt_state.copy_(self._torch.from_numpy(state))
+        if self.optimizer != 'rmsprop':
+            self.step_index = it
 
     def get_grads(self) -> List[Dict[str, np.ndarray]]:
         self._torch.cuda.synchronize(self._dev)

@@ -253,3 +253,30 @@ def test_loss_decreases_and_model_api(dev):
     out = m.predict(x.astype(np.float32) / 255.0)
     assert out.shape == (2, 512, 512, 3) and np.isfinite(out).all()
     m.close()
+
+
+def test_checkpoint_resumes_optimizer_state(dev, tmp_path):
+    """Model.save after training writes /optimizer_weights; load_model + the next train_on_batch starts
+    from the same RMSprop accumulators and parameters (what ModelCheckpoint + keras.models.load_model give)."""
+    import cnn_itmo_b200 as M
+    m = M.Model(M.initial_weights(7), precision='bf16', max_batch=2)
+    m.compile(optimizer='rmsprop', loss='mse', metrics=['accuracy'])
+    m.train_micro_batch = 2
+    x, y = T.synthetic_pair(2, 512, 512, seed=33)
+    for _ in range(2):
+        m.train_on_batch(x, y)
+    p = str(tmp_path / 'saved7-model-02-0.50.hdf5')
+    m.save(p)
+    state = m._trainer.opt_state.cpu().numpy().copy()
+    params = m._trainer.params.cpu().numpy().copy()
+    assert np.abs(state[:m._trainer.n_params]).max() > 0
+    m.close()
+    r = M.load_model(p, precision='bf16', max_batch=2)
+    r.train_micro_batch = 2
+    assert len(r.meta['optimizer_weights']) == 74
+    tr = r._ensure_trainer()
+    np.testing.assert_array_equal(tr.opt_state.cpu().numpy(), state)
+    np.testing.assert_array_equal(tr.params.cpu().numpy(), params)
+    loss = r.train_on_batch(x, y)[0]
+    assert np.isfinite(loss)
+    r.close()

@@ -64,6 +64,56 @@ def test_checkpoint_roundtrip_keras_layout(tmp_path):
     np.testing.assert_array_equal(got2[11]['kernel'], ws[11]['kernel'])
 
 
+def _fake_layout():
+    """A flat parameter layout with the library's field order (kernel, bias, gamma, beta per layer) built from the graph
+    table — enough to exercise the optimizer-state ordering without the CUDA library."""
+    layout, off = [], 0
+    for l in graph.LAYERS:
+        ks = graph.kernel_shape(l)
+        d = {}
+        for name, cnt in (('kernel', int(np.prod(ks))), ('bias', l.cout)) + ((('gamma', l.cout), ('beta', l.cout)) if l.bn else ()):
+            d[name] = (off, cnt)
+            off += cnt
+        layout.append(d)
+    return layout, off
+
+
+@pytest.mark.parametrize('opt', ['rmsprop', 'adam'])
+def test_optimizer_state_roundtrip_in_keras_order(tmp_path, opt):
+    """model.save writes the optimizer state under /optimizer_weights in the order of Keras'
+    trainable_weights (main.py:123-124 ModelCheckpoint); reading it back restores the flat state exactly."""
+    from cnn_itmo_b200 import train, h5min
+    layout, n = _fake_layout()
+    assert n == graph.count_params()['trainable'] == 11159011
+    order = train.keras_trainable_order()
+    assert len(order) == 2 * graph.NUM_LAYERS + 2 * (graph.NUM_LAYERS - 1)
+    assert order[:4] == [(0, 'kernel'), (0, 'bias'), (0, 'gamma'), (0, 'beta')]
+    assert order[-2:] == [(18, 'kernel'), (18, 'bias')]
+    rng = np.random.default_rng(3)
+    state = rng.random(2 * n, dtype=np.float32)
+    if opt == 'rmsprop':
+        state[n:] = 0
+    ows = train.optimizer_weights_from_flat(state, layout, opt, iterations=41)
+    assert len(ows) == (len(order) if opt == 'rmsprop' else 1 + 2 * len(order))
+    first = ows[0] if opt == 'rmsprop' else ows[1]
+    assert first.shape == (3, 3, 3, 32)                       # accumulator of conv2d_1/kernel, Keras HWIO
+    p = str(tmp_path / f'ck-{opt}.hdf5')
+    ws = R.synthetic_weights(5)
+    checkpoint.write_checkpoint(p, ws, optimizer_weights=ows, optimizer=opt)
+    got, meta = checkpoint.read_checkpoint(p)
+    np.testing.assert_array_equal(got[3]['kernel'], ws[3]['kernel'])
+    cls = 'RMSprop' if opt == 'rmsprop' else 'Adam'
+    assert meta['training_config']['optimizer_config']['class_name'] == cls
+    assert meta['optimizer_weight_names'][0] == f'training/{cls}/Variable:0'
+    assert meta['optimizer_weight_names'][5] == f'training/{cls}/Variable_5:0'
+    back, it = train.optimizer_weights_to_flat(meta['optimizer_weights'], layout, opt, n)
+    np.testing.assert_array_equal(back, state)
+    assert it == (0 if opt == 'rmsprop' else 41)
+    assert h5min.File(p)[f'optimizer_weights/training/{cls}/Variable_1:0'].shape == ((32,) if opt == 'rmsprop' else (3, 3, 3, 32))
+    with pytest.raises(ValueError):
+        train.optimizer_weights_to_flat(meta['optimizer_weights'][:-1], layout, opt, n)
+
+
 def test_checkpoint_matching_is_by_type_order_not_suffix(tmp_path):
     """A model built second in a Keras session has conv2d_16..; matching must not depend on the numbers."""
     from cnn_itmo_b200 import h5min
