@@ -124,18 +124,44 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const __nv_bfloat16* __re
   const int groups = C >> 3;
   const int Hp = H >> 1, Wp = W >> 1;
   const size_t total = size_t(NB) * Hp * Wp * groups;
-  for (size_t gid = blockIdx.x * size_t(blockDim.x) + threadIdx.x; gid < total; gid += size_t(gridDim.x) * blockDim.x) {
-    const int cg = int(gid % groups);
-    size_t w = gid / groups;
-    const int xp = int(w % Wp);
-    w /= Wp;
-    const int yp = int(w % Hp);
-    const int img = int(w / Hp);
-    float sc[8], sh[8];
+  const size_t stride = size_t(gridDim.x) * blockDim.x;
+  // the channel group of a thread never changes when the grid stride is a multiple of the group count (always, for the
+  // power-of-two widths of this network): scale / shift are then loaded once, not once per window
+  const bool fixed_cg = stride % groups == 0;
+  const bool small = total < (size_t(1) << 31);          // 32-bit index arithmetic (64-bit divisions are ~10x dearer)
+  float sc[8], sh[8];
+  if (fixed_cg) {
+    const int cg0 = int((blockIdx.x * size_t(blockDim.x) + threadIdx.x) % groups);
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
-      sc[i] = scale[cg * 8 + i];
-      sh[i] = shift[cg * 8 + i];
+      sc[i] = scale[cg0 * 8 + i];
+      sh[i] = shift[cg0 * 8 + i];
+    }
+  }
+  for (size_t gid = blockIdx.x * size_t(blockDim.x) + threadIdx.x; gid < total; gid += stride) {
+    int cg, xp, yp, img;
+    if (small) {
+      uint32_t w = uint32_t(gid);
+      cg = int(w % uint32_t(groups));
+      w /= uint32_t(groups);
+      xp = int(w % uint32_t(Wp));
+      w /= uint32_t(Wp);
+      yp = int(w % uint32_t(Hp));
+      img = int(w / uint32_t(Hp));
+    } else {
+      cg = int(gid % groups);
+      size_t w = gid / groups;
+      xp = int(w % Wp);
+      w /= Wp;
+      yp = int(w % Hp);
+      img = int(w / Hp);
+    }
+    if (!fixed_cg) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        sc[i] = scale[cg * 8 + i];
+        sh[i] = shift[cg * 8 + i];
+      }
     }
     float mx[8];
 #pragma unroll
@@ -174,7 +200,7 @@ __global__ void __launch_bounds__(128) head_train_kernel(const __nv_bfloat16* __
                                                          __nv_bfloat16* __restrict__ d_a, float* __restrict__ pred,
                                                          double* __restrict__ acc, float* __restrict__ dwh,
                                                          float* __restrict__ dbh) {
-  __shared__ float s_w[3 * 64 + 3];
+  __shared__ __align__(16) float s_w[3 * 64 + 4];
   __shared__ float s_a[4][32][65];
   __shared__ float s_dl[4][32][3];
   __shared__ float s_dw[3 * 64 + 3];
@@ -206,10 +232,13 @@ __global__ void __launch_bounds__(128) head_train_kernel(const __nv_bfloat16* __
     }
     float z0 = s_w[192], z1 = s_w[193], z2 = s_w[194];
 #pragma unroll
-    for (int c = 0; c < 64; ++c) {
-      z0 = fmaf(av[c], s_w[c], z0);
-      z1 = fmaf(av[c], s_w[64 + c], z1);
-      z2 = fmaf(av[c], s_w[128 + c], z2);
+    for (int c = 0; c < 64; c += 4) {   // 128-bit broadcast reads of the head weights; same summation order as scalar
+      const float4 w0 = *reinterpret_cast<const float4*>(s_w + c);
+      const float4 w1 = *reinterpret_cast<const float4*>(s_w + 64 + c);
+      const float4 w2 = *reinterpret_cast<const float4*>(s_w + 128 + c);
+      z0 = fmaf(av[c + 3], w0.w, fmaf(av[c + 2], w0.z, fmaf(av[c + 1], w0.y, fmaf(av[c], w0.x, z0))));
+      z1 = fmaf(av[c + 3], w1.w, fmaf(av[c + 2], w1.z, fmaf(av[c + 1], w1.y, fmaf(av[c], w1.x, z1))));
+      z2 = fmaf(av[c + 3], w2.w, fmaf(av[c + 2], w2.z, fmaf(av[c + 1], w2.y, fmaf(av[c], w2.x, z2))));
     }
     const float p0 = 1.f / (1.f + expf(-z0)), p1 = 1.f / (1.f + expf(-z1)), p2 = 1.f / (1.f + expf(-z2));
     float dl0 = 0.f, dl1 = 0.f, dl2 = 0.f;
@@ -232,9 +261,15 @@ __global__ void __launch_bounds__(128) head_train_kernel(const __nv_bfloat16* __
       for (int j = 0; j < 8; ++j) {
         float f[8];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
+        for (int i = 0; i < 8; i += 4) {
           const int c = j * 8 + i;
-          f[i] = dl0 * s_w[c] + dl1 * s_w[64 + c] + dl2 * s_w[128 + c];
+          const float4 w0 = *reinterpret_cast<const float4*>(s_w + c);
+          const float4 w1 = *reinterpret_cast<const float4*>(s_w + 64 + c);
+          const float4 w2 = *reinterpret_cast<const float4*>(s_w + 128 + c);
+          f[i] = dl0 * w0.x + dl1 * w1.x + dl2 * w2.x;
+          f[i + 1] = dl0 * w0.y + dl1 * w1.y + dl2 * w2.y;
+          f[i + 2] = dl0 * w0.z + dl1 * w1.z + dl2 * w2.z;
+          f[i + 3] = dl0 * w0.w + dl1 * w1.w + dl2 * w2.w;
         }
         Bf8 o;
         o.set(f);
@@ -248,13 +283,22 @@ __global__ void __launch_bounds__(128) head_train_kernel(const __nv_bfloat16* __
     s_dl[wid][lane][1] = dl1;
     s_dl[wid][lane][2] = dl2;
     __syncwarp();
+    {
+      // g[j] belongs to index j*32 + lane -> k = j >> 1, c = (j & 1) * 32 + lane: per staged pixel two activation
+      // reads and three (broadcast) dl reads feed all six products, in the same q order as a per-output loop
+      float sg[6] = {};
+      for (int q = 0; q < 32; ++q) {
+        const float a_lo = s_a[wid][q][lane], a_hi = s_a[wid][q][32 + lane];
+        const float d0 = s_dl[wid][q][0], d1 = s_dl[wid][q][1], d2 = s_dl[wid][q][2];
+        sg[0] = fmaf(d0, a_lo, sg[0]);
+        sg[1] = fmaf(d0, a_hi, sg[1]);
+        sg[2] = fmaf(d1, a_lo, sg[2]);
+        sg[3] = fmaf(d1, a_hi, sg[3]);
+        sg[4] = fmaf(d2, a_lo, sg[4]);
+        sg[5] = fmaf(d2, a_hi, sg[5]);
+      }
 #pragma unroll
-    for (int j = 0; j < 6; ++j) {
-      const int idx = j * 32 + lane;
-      const int k = idx >> 6, c = idx & 63;
-      float s = 0.f;
-      for (int q = 0; q < 32; ++q) s = fmaf(s_dl[wid][q][k], s_a[wid][q][c], s);
-      g[j] += s;
+      for (int j = 0; j < 6; ++j) g[j] += sg[j];
     }
     if (lane < 3) {
       float s = 0.f;
