@@ -446,6 +446,8 @@ def run_frames_arm(a):
         step()
     barrier()
     launches0 = model.launch_count()
+    model.set_profiling(True)          # CUDA events around every layer launch, on the launch stream
+    model.layer_times(reset=True)
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
@@ -459,6 +461,21 @@ def run_frames_arm(a):
     clocks = sampler.stop() if rank == 0 else None
     ms_total = ev0.elapsed_time(ev1)
     launches = model.launch_count() - launches0
+    lt = model.layer_times(reset=True)
+    model.set_profiling(False)
+    # roofline of the implicit-GEMM kernel over the EXECUTED tiles (84 per frame), as in the batch workload
+    from cnn_itmo_b200 import graph as _g
+    ig_ms = sum(lt[l.index][0] for l in _g.LAYERS if l.kind != 'head' and l.index != 0)
+    ig_calls = sum(lt[l.index][1] for l in _g.LAYERS if l.kind != 'head' and l.index != 0)
+    ig_flops = (_g.forward_flops_per_image() - 2.0 * IMG * IMG * 27 * 32) * 84 * F * a.steps
+    peaks = measured_peaks()
+    ach = ig_flops / (ig_ms * 1e-3) / 1e12 if ig_ms > 0 else None
+    roofline = {'bound': 'tensor', 'kernel': 'itmo::conv_igemm_kernel (executed tiles)', 'achieved': round(ach, 2) if ach else None,
+                'peak': peaks['tflops_sustained'], 'unit': 'TFLOP/s',
+                'frac': round(ach / peaks['tflops_sustained'], 4) if ach else None, 'traffic': None,
+                'peak_source': peaks['source'] + ' (bf16 sustained)',
+                'flops_per_launch': ig_flops / max(1, ig_calls), 'avg_launch_ms': round(ig_ms / max(1, ig_calls), 4),
+                'share_of_step': round(ig_ms / ms_total, 4) if ms_total > 0 else None}
     if world > 1:
         t = torch.tensor([ms_total], device=dev, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -497,7 +514,7 @@ def run_frames_arm(a):
                 'clocks': clocks,
                 'e2e': {'value': round(e2e, 2), 'unit': 'Mpix/s', 'h2d_bytes_per_step': int(hx.nbytes),
                         'd2h_bytes_per_step': int(hy.nbytes), 'api': 'frames.predict_frames_device with pinned host copies'},
-                'gpu_launches': int(launches)}
+                'gpu_launches': int(launches), 'roofline': roofline, 'cpu_baseline': None}
         print(json.dumps(line), flush=True)
     model.close()
     if world > 1:

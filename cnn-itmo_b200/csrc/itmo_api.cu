@@ -561,7 +561,7 @@ int run_rgb_tc_t(const void* in, int in_dtype, int n, int h, int w, const float*
   const int tiles = n * (h / itmo::kRgbTileH) * (w / itmo::kRgbTileW);
   // persistent grid = exactly the CTAs resident at once: __launch_bounds__(128, 5) caps the registers for five
   // CTAs per SM, which 23 KB of shared memory and 32 TMEM columns each also allow
-  constexpr int per_sm = 5;
+  constexpr int per_sm = 8;
   const int grid = std::min(tiles, num_sms() * per_sm);
   if (in_dtype == ITMO_DT_U8)
     itmo::rgb_conv_tc_kernel<Elem, uint8_t><<<grid, 128, 0, stream>>>((const uint8_t*)in, (Elem*)out, w_hwio, bias,

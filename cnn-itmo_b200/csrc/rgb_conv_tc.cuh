@@ -23,7 +23,7 @@ constexpr int kRgbHaloH = kRgbTileH + 2, kRgbHaloW = kRgbTileW + 2;
 // in:  [NB,H,W,3] uint8 (raw pixels) or float (already /255); out: [NB,H,W,32] Elem
 // w_hwio: [27][32] fp32 (Keras HWIO flattened), in_scale: 1/255 for uint8 input, 1 for float input
 template <typename Elem, typename InT>
-__global__ void __launch_bounds__(128, 5) rgb_conv_tc_kernel(const InT* __restrict__ in, Elem* __restrict__ out,
+__global__ void __launch_bounds__(128, 8) rgb_conv_tc_kernel(const InT* __restrict__ in, Elem* __restrict__ out,
                                                           const float* __restrict__ w_hwio,
                                                           const float* __restrict__ bias,
                                                           const float* __restrict__ scale,
@@ -31,8 +31,10 @@ __global__ void __launch_bounds__(128, 5) rgb_conv_tc_kernel(const InT* __restri
                                                           float in_scale) {
   __shared__ __align__(1024) uint8_t s_a[128 * 128];  // im2col tile, 128 rows x 128 B, SWIZZLE_128B
   __shared__ __align__(1024) uint8_t s_b[32 * 128];   // weights, 32 rows (cout) x 128 B (K), SWIZZLE_128B
-  __shared__ float s_halo[kRgbHaloH][kRgbHaloW * 3 + 2];
-  __shared__ float s_bias[32], s_scale[32], s_shift[32];
+  __shared__ float s_halo[kRgbHaloH][kRgbHaloW * 3 + 2];   // float input: halo values
+  __shared__ uint32_t s_raw[kRgbHaloH][28];                 // uint8 input: halo rows as the raw words (26 used); byte b
+                                                            // of a row = image-row byte x0*3 - 4 + b = halo value b - 1
+  __shared__ __align__(16) float s_bias[32], s_scale[32], s_shift[32];
   __shared__ __align__(8) uint64_t s_bar;
   __shared__ uint32_t s_tmem;
 
@@ -111,28 +113,20 @@ __global__ void __launch_bounds__(128, 5) rgb_conv_tc_kernel(const InT* __restri
 
     // ---- halo tile -> shared memory as floats (zero outside the image = 'same' padding)
     if (fast_u8) {
-#pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        const int idx = tid + 128 * h;
-        const uint32_t wv = h ? nw1 : nw0;
-        if (idx < kWords) {
-          const int hy = idx / kWordsPerRow, k = idx - hy * kWordsPerRow;
-#pragma unroll
-          for (int b = 0; b < 4; ++b) {
-            const int rem = 4 * k - 1 + b;                      // halo-row byte this word byte lands on
-            if (rem >= 0 && rem < kRgbHaloW * 3) s_halo[hy][rem] = float((wv >> (8 * b)) & 0xFFu);
-          }
-        }
-      }
+      if (tid < kWords) s_raw[tid / kWordsPerRow][tid % kWordsPerRow] = nw0;
+      if (tid + 128 < kWords) s_raw[(tid + 128) / kWordsPerRow][(tid + 128) % kWordsPerRow] = nw1;
     } else {
       for (int i = tid; i < kRgbHaloH * kRgbHaloW * 3; i += 128) {
         const int hy = i / (kRgbHaloW * 3), rem = i - hy * (kRgbHaloW * 3);
         const int hx = rem / 3;
         const int yy = y0 + hy - 1, xx = x0 + hx - 1;
-        float v = 0.f;
-        if (yy >= 0 && yy < H && xx >= 0 && xx < W)
-          v = float(in[((size_t(img) * H + yy) * W + x0 - 1) * 3 + rem]);
-        s_halo[hy][rem] = v;
+        const bool inside = yy >= 0 && yy < H && xx >= 0 && xx < W;
+        if constexpr (sizeof(InT) == 1) {   // pointer not 4-byte aligned: byte loads into the same raw layout
+          reinterpret_cast<uint8_t*>(&s_raw[hy][0])[rem + 1] =
+              inside ? uint8_t(in[((size_t(img) * H + yy) * W + x0 - 1) * 3 + rem]) : uint8_t(0);
+        } else {
+          s_halo[hy][rem] = inside ? float(in[((size_t(img) * H + yy) * W + x0 - 1) * 3 + rem]) : 0.f;
+        }
       }
     }
     __syncthreads();
@@ -144,10 +138,27 @@ __global__ void __launch_bounds__(128, 5) rgb_conv_tc_kernel(const InT* __restri
     // ---- im2col: k = dy*9 + dx*3 + ch = dy*9 + (9 consecutive halo values starting at pixel c)
     {
       float a[32];
+      if constexpr (sizeof(InT) == 1) {
+        // 9 consecutive bytes from raw byte 3c + 1: three word reads + funnel shifts instead of 9 scalar reads
+        const int sb = 3 * c + 1, w0 = sb >> 2;
+        const uint32_t sh = uint32_t(sb & 3) * 8u;
 #pragma unroll
-      for (int dy = 0; dy < 3; ++dy)
+        for (int dy = 0; dy < 3; ++dy) {
+          const uint32_t W0 = s_raw[r + dy][w0], W1 = s_raw[r + dy][w0 + 1], W2 = s_raw[r + dy][w0 + 2];
+          const uint32_t q0 = __funnelshift_r(W0, W1, sh), q1 = __funnelshift_r(W1, W2, sh), q2 = W2 >> sh;
 #pragma unroll
-        for (int j = 0; j < 9; ++j) a[dy * 9 + j] = s_halo[r + dy][c * 3 + j];
+          for (int j = 0; j < 4; ++j) {
+            a[dy * 9 + j] = float((q0 >> (8 * j)) & 0xFFu);
+            a[dy * 9 + 4 + j] = float((q1 >> (8 * j)) & 0xFFu);
+          }
+          a[dy * 9 + 8] = float(q2 & 0xFFu);
+        }
+      } else {
+#pragma unroll
+        for (int dy = 0; dy < 3; ++dy)
+#pragma unroll
+          for (int j = 0; j < 9; ++j) a[dy * 9 + j] = s_halo[r + dy][c * 3 + j];
+      }
 #pragma unroll
       for (int j = 27; j < 32; ++j) a[j] = 0.f;
       const int sw = tid & 7;
@@ -182,12 +193,16 @@ __global__ void __launch_bounds__(128, 5) rgb_conv_tc_kernel(const InT* __restri
     sm100::tmem_ld_wait();
     uint32_t pk[16];
 #pragma unroll
-    for (int i = 0; i < 16; ++i) {
-      const float f0 = fmaf(fmaxf(fmaf(__uint_as_float(v[2 * i]), in_scale, s_bias[2 * i]), 0.f), s_scale[2 * i],
-                            s_shift[2 * i]);
-      const float f1 = fmaf(fmaxf(fmaf(__uint_as_float(v[2 * i + 1]), in_scale, s_bias[2 * i + 1]), 0.f),
-                            s_scale[2 * i + 1], s_shift[2 * i + 1]);
-      pk[i] = pack2<Elem>(f0, f1);
+    for (int i = 0; i < 8; ++i) {   // 128-bit broadcast reads: a quarter of the shared-memory wavefronts of scalar ones
+      const float4 b4 = reinterpret_cast<const float4*>(s_bias)[i];
+      const float4 sc4 = reinterpret_cast<const float4*>(s_scale)[i];
+      const float4 sh4 = reinterpret_cast<const float4*>(s_shift)[i];
+      const float f0 = fmaf(fmaxf(fmaf(__uint_as_float(v[4 * i]), in_scale, b4.x), 0.f), sc4.x, sh4.x);
+      const float f1 = fmaf(fmaxf(fmaf(__uint_as_float(v[4 * i + 1]), in_scale, b4.y), 0.f), sc4.y, sh4.y);
+      const float f2 = fmaf(fmaxf(fmaf(__uint_as_float(v[4 * i + 2]), in_scale, b4.z), 0.f), sc4.z, sh4.z);
+      const float f3 = fmaf(fmaxf(fmaf(__uint_as_float(v[4 * i + 3]), in_scale, b4.w), 0.f), sc4.w, sh4.w);
+      pk[2 * i] = pack2<Elem>(f0, f1);
+      pk[2 * i + 1] = pack2<Elem>(f2, f3);
     }
     // The 32 pixels of a warp are 2 KB of contiguous output. Stage them in the (now idle) im2col tile with a
     // 16-byte-piece swizzle, then store 512 contiguous bytes per instruction instead of 32 pieces 64 B apart.
