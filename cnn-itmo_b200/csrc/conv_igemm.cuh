@@ -38,7 +38,7 @@ constexpr int kBlkW = 8;
 constexpr int kTileM = 128;
 constexpr int kMaxCout = 512;
 constexpr int kMaxSeg = 6;
-constexpr int kMaxAStages = 4;
+constexpr int kMaxAStages = 8;
 constexpr int kMaxBStages = 8;
 constexpr int kNumThreads = 384;       // warp 0 TMA, 1 MMA, 2 TMEM alloc, 3 idle, 4..11 epilogue
 constexpr int kNumEpiWarps = 8;

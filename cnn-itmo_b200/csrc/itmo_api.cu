@@ -382,6 +382,7 @@ int env_int(const char* name, int dflt) {
 int run_conv(const ConvArgs& a, cudaStream_t stream) {
   static const int force_nm = env_int("ITMO_FORCE_NM", 0);
   static const int no_resident = env_int("ITMO_NO_RESIDENT", 0);
+  static const int max_a = std::max(2, env_int("ITMO_MAX_A_STAGES", 4));   // tuning: cap of the activation ring (A/B on B200: 8 is no faster, conv2d_2 6 % slower)
   const size_t es = elem_size(a.precision);
   if (a.h % itmo::kBlkH || a.w % itmo::kBlkW)
     return fail(ITMO_ERR_INVALID, "spatial size %dx%d must be a multiple of %dx%d", a.h, a.w, itmo::kBlkH,
@@ -432,7 +433,7 @@ int run_conv(const ConvArgs& a, cudaStream_t stream) {
   if (!no_resident && n_tiles == 1 && kb_total * taps * b_stage + 2 * a_stage <= budget) {
     resident = 1;
     n_b = kb_total * taps;
-    n_a = std::min(itmo::kMaxAStages, (budget - n_b * b_stage) / a_stage);
+    n_a = std::min(std::min(itmo::kMaxAStages, max_a), (budget - n_b * b_stage) / a_stage);
   } else {
     n_a = 2;
     n_b = std::min(itmo::kMaxBStages, (budget - n_a * a_stage) / b_stage);

@@ -121,6 +121,8 @@ int run_wgrad(const WgradArgs& a, cudaStream_t stream) {
   p.m_blocks = (a.ca + 127) / 128;
   p.n_blocks = a.cb / bn;
   p.a_boxes = a.ca > 64 ? 2 : 1;
+  static const int allow_m64 = env_int("ITMO_WGRAD_M64", 1);
+  p.m64 = (allow_m64 && a.ca <= 64) ? 1 : 0;
   p.b_boxes = (bn + 63) / 64;
   p.a_box_bytes = 16 * (8 + 2 * p.pad) * itmo::kWgRowBytes;
   p.stage_bytes = p.a_boxes * p.a_box_bytes + p.b_boxes * itmo::kWgBoxPixB * itmo::kWgRowBytes;

@@ -47,6 +47,7 @@ struct WgradParams {
   int n_stages;
   int ksplit;        // pixel-range slices
   int ca;            // valid A channels (rows written)
+  int m64;           // 1: UMMA M = 64 (ca <= 64): half the A operand bytes per MMA at the same MMA duration
   float* dw;         // [n_groups*tg][ld_m][ld_n] fp32, accumulated
   int ld_m, ld_n;    // rows / columns of one tap's matrix
   int m_off, n_off;  // where this launch's (A-channel, B-channel) block starts inside it
@@ -134,7 +135,9 @@ __global__ void __launch_bounds__(kWgThreads, 1) wgrad_igemm_kernel(const __grid
   } else if (warp_idx == 1) {
     if (sm100::elect_one()) {
       // both operands MN-major (bits 15, 16)
-      constexpr uint32_t idesc = sm100::make_idesc(sm100::kFmtBF16, 128, BN) | (1u << 15) | (1u << 16);
+      // M = 64 for the narrow layers: an MMA lasts max(M,128)*N/256 clocks either way, but its A tile is 2 KB
+      // instead of 4 KB of shared-memory reads (the 32/64-channel layers were bound by exactly those reads)
+      const uint32_t idesc = sm100::make_idesc(sm100::kFmtBF16, p.m64 ? 64 : 128, BN) | (1u << 15) | (1u << 16);
       const uint32_t a_hi = wg_desc_hi(uint32_t(halo_w) * kWgRowBytes);   // next 8 pixels of K: one tile row down
       const uint32_t b_hi = wg_desc_hi(8u * kWgRowBytes);
       const uint32_t a_lbo = uint32_t(p.a_box_bytes);                      // next 64 channels: the next box
@@ -170,7 +173,9 @@ __global__ void __launch_bounds__(kWgThreads, 1) wgrad_igemm_kernel(const __grid
     const int q = warp_idx & 3;
     sm100::mbar_wait_relaxed(tmem_full, 0, 500);
     sm100::tc_fence_after_sync();
-    const int row = mb * 128 + 32 * q + lane;
+    // M = 128: accumulator row r lives in TMEM lane r. M = 64: row r lives in lane (r % 16) + 32 * (r / 16), i.e.
+    // every warp's lane quarter holds 16 rows in its first 16 lanes
+    const int row = p.m64 ? (lane < 16 ? 16 * q + lane : p.ca) : mb * 128 + 32 * q + lane;
     const uint32_t taddr = tmem_base + (uint32_t(32 * q) << 16);
     for (int t = 0; t < p.tg; ++t) {
       const int tap = g * p.tg + t;
