@@ -7,6 +7,6 @@ timeout 300 $SMALL > $OUT/${TAG}_small_plain.log 2>&1 || { echo "plain run faile
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -s 640 -c 230 --csv --log-file $OUT/${TAG}_launches.csv $SMALL > $OUT/${TAG}_ncu_launches.log 2>&1
 echo "ncu launches rc=$?"
 timeout 300 $SMALL > $OUT/${TAG}_small_plain2.log 2>&1 && \
-timeout 1500 ncu --set full --clock-control none --import-source on -k regex:wgrad_igemm -s 78 -c 26 -f -o $OUT/${TAG}_wgrad $SMALL > $OUT/${TAG}_ncu_full.log 2>&1
+timeout 1500 ncu --set full --clock-control none -k regex:wgrad_igemm -s 78 -c 26 -f -o $OUT/${TAG}_wgrad $SMALL > $OUT/${TAG}_ncu_full.log 2>&1
 echo "ncu full rc=$?"
 ls -la $OUT | tail -8
