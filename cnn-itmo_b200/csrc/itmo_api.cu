@@ -558,31 +558,41 @@ int run_rgb_conv_t(const void* in, int in_dtype, int n, int h, int w, const floa
 
 template <typename Elem>
 int run_rgb_tc_t(const void* in, int in_dtype, int n, int h, int w, const float* w_hwio, const float* bias,
-                 const float* scale, const float* shift, void* out, cudaStream_t stream) {
+                 const float* scale, const float* shift, void* out, cudaStream_t stream,
+                 const itmo::RgbAffine* host_affine) {
   const int tiles = n * (h / itmo::kRgbTileH) * (w / itmo::kRgbTileW);
   // persistent grid = exactly the CTAs resident at once: __launch_bounds__(128, 5) caps the registers for five
   // CTAs per SM, which 23 KB of shared memory and 32 TMEM columns each also allow
   constexpr int per_sm = 8;
   const int grid = std::min(tiles, num_sms() * per_sm);
-  if (in_dtype == ITMO_DT_U8)
+  static const itmo::RgbAffine none = {};
+  if (host_affine) {   // the context's own first layer: affine vectors as kernel parameters (constant bank)
+    if (in_dtype == ITMO_DT_U8)
+      itmo::rgb_conv_tc_kernel<Elem, uint8_t, true><<<grid, 128, 0, stream>>>(
+          (const uint8_t*)in, (Elem*)out, w_hwio, bias, scale, shift, n, h, w, 1.0f / 255.0f, *host_affine);
+    else
+      itmo::rgb_conv_tc_kernel<Elem, float, true><<<grid, 128, 0, stream>>>((const float*)in, (Elem*)out, w_hwio, bias,
+                                                                             scale, shift, n, h, w, 1.0f, *host_affine);
+  } else if (in_dtype == ITMO_DT_U8) {
     itmo::rgb_conv_tc_kernel<Elem, uint8_t><<<grid, 128, 0, stream>>>((const uint8_t*)in, (Elem*)out, w_hwio, bias,
-                                                                       scale, shift, n, h, w, 1.0f / 255.0f);
-  else
+                                                                       scale, shift, n, h, w, 1.0f / 255.0f, none);
+  } else {
     itmo::rgb_conv_tc_kernel<Elem, float><<<grid, 128, 0, stream>>>((const float*)in, (Elem*)out, w_hwio, bias, scale,
-                                                                     shift, n, h, w, 1.0f);
+                                                                     shift, n, h, w, 1.0f, none);
+  }
   ITMO_CUDA(cudaGetLastError());
   return ITMO_OK;
 }
 
 int run_rgb_conv(int precision, const void* in, int in_dtype, int n, int h, int w, const float* w_hwio,
                  const float* bias, const float* scale, const float* shift, void* out, void* out_lo,
-                 cudaStream_t stream) {
+                 cudaStream_t stream, const itmo::RgbAffine* host_affine = nullptr) {
   static const int use_tc = env_int("ITMO_RGB_TC", 1);
   if (use_tc && prec_is16(precision) && h % itmo::kRgbTileH == 0 && w % itmo::kRgbTileW == 0) {
     // 16-bit modes: tensor-core im2col kernel (rgb_conv_tc.cuh)
     if (precision == ITMO_PREC_BF16)
-      return run_rgb_tc_t<__nv_bfloat16>(in, in_dtype, n, h, w, w_hwio, bias, scale, shift, out, stream);
-    return run_rgb_tc_t<__half>(in, in_dtype, n, h, w, w_hwio, bias, scale, shift, out, stream);
+      return run_rgb_tc_t<__nv_bfloat16>(in, in_dtype, n, h, w, w_hwio, bias, scale, shift, out, stream, host_affine);
+    return run_rgb_tc_t<__half>(in, in_dtype, n, h, w, w_hwio, bias, scale, shift, out, stream, host_affine);
   }
   const size_t total = size_t(n) * h * w * 4;
   const int grid = int(std::min<size_t>((total + 255) / 256, size_t(num_sms()) * 16));
@@ -617,6 +627,9 @@ struct itmo_ctx {
   int precision = ITMO_PREC_BF16;
   int cap = 0;  // images the arena holds
   bool weights_loaded = false;
+  // host copy of layer 0's bias / folded BN scale / shift: passed to rgb_conv_tc_kernel by value (constant bank)
+  itmo::RgbAffine l0_affine = {};
+  bool l0_affine_valid = false;
   long long launches = 0;
   int last_chunk = 0;  // images in the most recent forward chunk (for itmo_read_activation)
 
@@ -705,7 +718,8 @@ int forward_chunk(itmo_ctx* ctx, const void* in_dev, int in_dtype, void* out_dev
     LayerStamp stamp(ctx, li, stream);
     if (L.kind == kRgbConv) {
       int rc = run_rgb_conv(prec, in_dev, in_dtype, nb, L.hin, L.hin, (const float*)ctx->wpacked[li], ctx->bias[li],
-                            ctx->scale[li], ctx->shift[li], ctx->act[li], ctx->act_lo[li], stream);
+                            ctx->scale[li], ctx->shift[li], ctx->act[li], ctx->act_lo[li], stream,
+                            ctx->l0_affine_valid ? &ctx->l0_affine : nullptr);
       if (rc) return rc;
       ctx->launches++;
       continue;
@@ -951,6 +965,15 @@ int itmo_load_weights(itmo_ctx* ctx, const itmo_layer_weights* layers, int n_lay
   cudaStreamSynchronize(s);
   cudaFree(tmp);
   cudaFree(bn);
+  ctx->l0_affine_valid = false;
+  if (rc == ITMO_OK && kLayers[0].kind == kRgbConv && kLayers[0].cout == 32) {
+    // exactly the vectors the device holds (folded by bn_fold_kernel), so both kernel variants compute the same thing
+    cudaError_t e = cudaMemcpy(ctx->l0_affine.bias, ctx->bias[0], 32 * 4, cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess) e = cudaMemcpy(ctx->l0_affine.scale, ctx->scale[0], 32 * 4, cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess) e = cudaMemcpy(ctx->l0_affine.shift, ctx->shift[0], 32 * 4, cudaMemcpyDeviceToHost);
+    if (e != cudaSuccess) rc = fail(ITMO_ERR_CUDA, "layer 0 affine read-back failed: %s", cudaGetErrorString(e));
+    else ctx->l0_affine_valid = true;
+  }
   if (rc == ITMO_OK) ctx->weights_loaded = true;
   return rc;
 }

@@ -22,13 +22,20 @@ constexpr int kRgbHaloH = kRgbTileH + 2, kRgbHaloW = kRgbTileW + 2;
 
 // in:  [NB,H,W,3] uint8 (raw pixels) or float (already /255); out: [NB,H,W,32] Elem
 // w_hwio: [27][32] fp32 (Keras HWIO flattened), in_scale: 1/255 for uint8 input, 1 for float input
-template <typename Elem, typename InT>
+// bias / scale / shift of the 32 output channels handed over BY VALUE: kernel parameters live in the constant bank, so
+// the epilogue's FFMAs take them as immediate-indexed constant operands — no shared-memory reads at all (the 24
+// broadcast reads per pixel row were ~40 % of this kernel's L1 data-pipe wavefronts, its bottleneck).
+struct RgbAffine {
+  float bias[32], scale[32], shift[32];
+};
+
+template <typename Elem, typename InT, bool kConstAffine = false>
 __global__ void __launch_bounds__(128, 8) rgb_conv_tc_kernel(const InT* __restrict__ in, Elem* __restrict__ out,
                                                           const float* __restrict__ w_hwio,
                                                           const float* __restrict__ bias,
                                                           const float* __restrict__ scale,
                                                           const float* __restrict__ shift, int NB, int H, int W,
-                                                          float in_scale) {
+                                                          float in_scale, const __grid_constant__ RgbAffine aff) {
   __shared__ __align__(1024) uint8_t s_a[128 * 128];  // im2col tile, 128 rows x 128 B, SWIZZLE_128B
   __shared__ __align__(1024) uint8_t s_b[32 * 128];   // weights, 32 rows (cout) x 128 B (K), SWIZZLE_128B
   __shared__ float s_halo[kRgbHaloH][kRgbHaloW * 3 + 2];   // float input: halo values
@@ -61,9 +68,11 @@ __global__ void __launch_bounds__(128, 8) rgb_conv_tc_kernel(const InT* __restri
       const int pos = c8 ^ (tid & 7);
       *reinterpret_cast<uint4*>(s_b + tid * 128 + pos * 16) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
     }
-    s_bias[tid] = bias[tid];
-    s_scale[tid] = scale[tid];
-    s_shift[tid] = shift[tid];
+    if constexpr (!kConstAffine) {
+      s_bias[tid] = bias[tid];
+      s_scale[tid] = scale[tid];
+      s_shift[tid] = shift[tid];
+    }
   }
   if (tid == 0) {
     sm100::mbar_init(&s_bar, 1);
@@ -194,9 +203,16 @@ __global__ void __launch_bounds__(128, 8) rgb_conv_tc_kernel(const InT* __restri
     uint32_t pk[16];
 #pragma unroll
     for (int i = 0; i < 8; ++i) {   // 128-bit broadcast reads: a quarter of the shared-memory wavefronts of scalar ones
-      const float4 b4 = reinterpret_cast<const float4*>(s_bias)[i];
-      const float4 sc4 = reinterpret_cast<const float4*>(s_scale)[i];
-      const float4 sh4 = reinterpret_cast<const float4*>(s_shift)[i];
+      float4 b4, sc4, sh4;
+      if constexpr (kConstAffine) {
+        b4 = make_float4(aff.bias[4 * i], aff.bias[4 * i + 1], aff.bias[4 * i + 2], aff.bias[4 * i + 3]);
+        sc4 = make_float4(aff.scale[4 * i], aff.scale[4 * i + 1], aff.scale[4 * i + 2], aff.scale[4 * i + 3]);
+        sh4 = make_float4(aff.shift[4 * i], aff.shift[4 * i + 1], aff.shift[4 * i + 2], aff.shift[4 * i + 3]);
+      } else {
+        b4 = reinterpret_cast<const float4*>(s_bias)[i];
+        sc4 = reinterpret_cast<const float4*>(s_scale)[i];
+        sh4 = reinterpret_cast<const float4*>(s_shift)[i];
+      }
       const float f0 = fmaf(fmaxf(fmaf(__uint_as_float(v[4 * i]), in_scale, b4.x), 0.f), sc4.x, sh4.x);
       const float f1 = fmaf(fmaxf(fmaf(__uint_as_float(v[4 * i + 1]), in_scale, b4.y), 0.f), sc4.y, sh4.y);
       const float f2 = fmaf(fmaxf(fmaf(__uint_as_float(v[4 * i + 2]), in_scale, b4.z), 0.f), sc4.z, sh4.z);
