@@ -79,6 +79,12 @@ struct ConvParams {
   double* stats;       // training forward (16-bit modes): per-channel sum [cout] and sum of squares [cout] of the stored
                        // output z = ReLU(acc + bias) are accumulated here (BatchNormalization batch statistics,
                        // model.py:196); the BN affine is then the identity and bn_scale / bn_shift are not read
+  // Narrow 3x3 layers of a loaded context (cout == BLOCK_N <= 64, plain ConvBN epilogue): the affine vectors BY VALUE
+  // (the fused head's weights stay in shared memory: as constant operands they measured 4 % slower on conv2d_14). Kernel parameters sit in the constant bank, so the epilogue's FADD / FFMA take them
+  // as immediate-indexed constant operands: no shared-memory broadcast reads on the L1 data pipe these layers are
+  // bound by (it is shared with the tensor core's operand reads).
+  int const_affine;
+  float c_bias[64], c_scale[64], c_shift[64];
   const float* bias;      // [cout]
   const float* bn_scale;  // [cout]  gamma / sqrt(var + eps)
   const float* bn_shift;  // [cout]  beta - mean * scale
@@ -232,6 +238,13 @@ __device__ __forceinline__ void epi_affine(const uint32_t (&v)[32], float (&f)[3
   }
 }
 
+// The same with the vectors read from the kernel parameters at compile-time offsets (constant-bank operands).
+template <int CO0>
+__device__ __forceinline__ void epi_affine_const(const uint32_t (&v)[32], float (&f)[32], const ConvParams& p) {
+#pragma unroll
+  for (int i = 0; i < 32; ++i)
+    f[i] = fmaf(fmaxf(__uint_as_float(v[i]) + p.c_bias[CO0 + i], 0.f), p.c_scale[CO0 + i], p.c_shift[CO0 + i]);
+}
 template <typename Elem, int BLOCK_N, int SWZ>
 struct ConvCfg {
   static constexpr int kBK = SWZ / int(sizeof(Elem));     // channels per K block
@@ -587,9 +600,16 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
             Ho = p.H;
             Wo = p.W;
           }
+          // const_affine (host-checked: cout == BLOCK_N <= 64, 3x3 conv, one N tile): co0 = chunk * 32 is one of two
+          // compile-time values. (Selecting by co0 for the narrow transposed convs as well was tried: the extra code
+          // in the BLOCK_N = 256 instantiation and a different register allocation made conv2d_2 / conv2d_4 slower
+          // than without the constant path, an A/B wash overall.)
+          const bool use_const = BLOCK_N <= 64 && p.const_affine != 0;
           float4 b4[8];
+          if (!use_const) {
 #pragma unroll
-          for (int i = 0; i < 8; ++i) b4[i] = reinterpret_cast<const float4*>(s_bias + co0)[i];
+            for (int i = 0; i < 8; ++i) b4[i] = reinterpret_cast<const float4*>(s_bias + co0)[i];
+          }
           sm100::tmem_ld_wait();
           for (int sa = 1; sa < S; ++sa) {  // split accumulators: sum the partial results in fp32 (rn)
             uint32_t u[kChunk];
@@ -602,18 +622,28 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
           // shared-memory reads are hoisted ahead of the arithmetic (run-time flags inside the unrolled loop
           // serialise load -> use -> load and leave the LSU latency exposed)
           float f[kChunk];
-          if (with_stats) epi_affine<true, false>(v, f, b4, s_scale + co0, s_shift + co0);
-          else if (p.no_relu) epi_affine<false, true>(v, f, b4, s_scale + co0, s_shift + co0);
-          else epi_affine<false, false>(v, f, b4, s_scale + co0, s_shift + co0);
-          if (p.head_dtype != kHeadNone) {
+          if constexpr (BLOCK_N <= 64) {
+            if (use_const) {
+              if (chunk == 0) epi_affine_const<0>(v, f, p);
+              else epi_affine_const<(BLOCK_N > 32 ? 32 : 0)>(v, f, p);
+            }
+          }
+          if (!use_const) {
+            if (with_stats) epi_affine<true, false>(v, f, b4, s_scale + co0, s_shift + co0);
+            else if (p.no_relu) epi_affine<false, true>(v, f, b4, s_scale + co0, s_shift + co0);
+            else epi_affine<false, false>(v, f, b4, s_scale + co0, s_shift + co0);
+          }
+          {
+            if (p.head_dtype != kHeadNone) {
 #pragma unroll
-            for (int i = 0; i < kChunk; i += 4) {
-              const float4 w0 = *reinterpret_cast<const float4*>(s_head + 0 * 64 + co0 + i);
-              const float4 w1 = *reinterpret_cast<const float4*>(s_head + 1 * 64 + co0 + i);
-              const float4 w2 = *reinterpret_cast<const float4*>(s_head + 2 * 64 + co0 + i);
-              h0 = fmaf(f[i + 3], w0.w, fmaf(f[i + 2], w0.z, fmaf(f[i + 1], w0.y, fmaf(f[i], w0.x, h0))));
-              h1 = fmaf(f[i + 3], w1.w, fmaf(f[i + 2], w1.z, fmaf(f[i + 1], w1.y, fmaf(f[i], w1.x, h1))));
-              h2 = fmaf(f[i + 3], w2.w, fmaf(f[i + 2], w2.z, fmaf(f[i + 1], w2.y, fmaf(f[i], w2.x, h2))));
+              for (int i = 0; i < kChunk; i += 4) {
+                const float4 w0 = *reinterpret_cast<const float4*>(s_head + 0 * 64 + co0 + i);
+                const float4 w1 = *reinterpret_cast<const float4*>(s_head + 1 * 64 + co0 + i);
+                const float4 w2 = *reinterpret_cast<const float4*>(s_head + 2 * 64 + co0 + i);
+                h0 = fmaf(f[i + 3], w0.w, fmaf(f[i + 2], w0.z, fmaf(f[i + 1], w0.y, fmaf(f[i], w0.x, h0))));
+                h1 = fmaf(f[i + 3], w1.w, fmaf(f[i + 2], w1.z, fmaf(f[i + 1], w1.y, fmaf(f[i], w1.x, h1))));
+                h2 = fmaf(f[i + 3], w2.w, fmaf(f[i + 2], w2.z, fmaf(f[i + 1], w2.y, fmaf(f[i], w2.x, h2))));
+              }
             }
           }
           const size_t pix = (size_t(img) * Ho + oy) * Wo + ox;

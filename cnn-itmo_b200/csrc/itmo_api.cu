@@ -370,6 +370,11 @@ struct ConvArgs {
   long long img_stride[2];
   int w_tap_stride_rows;     // rows between two taps of the packed weights (0 = the rows this launch uses)
   double* stats;             // per-channel sum / sum of squares of the output (training forward), see ConvParams
+  // HOST copies of bias / scale / shift [cout]: when given and the layer is narrow enough they travel as kernel
+  // parameters (ConvParams::const_affine)
+  const float* h_bias;
+  const float* h_scale;
+  const float* h_shift;
 };
 
 // Debug / tuning overrides (environment, read once): ITMO_FORCE_NM = 1|2|4, ITMO_NO_RESIDENT = 1
@@ -491,6 +496,14 @@ int run_conv(const ConvArgs& a, cudaStream_t stream) {
   p.store_mode = a.precision == ITMO_PREC_TF32   ? itmo::kStoreTf32Rna
                  : a.precision == ITMO_PREC_FP32 ? itmo::kStoreSplit
                                                  : itmo::kStorePlain;
+  static const int allow_const = env_int("ITMO_CONST_AFFINE", 1);
+  if (allow_const && a.h_bias && a.h_scale && a.h_shift && conv && !a.one_tap && n_tiles == 1 && a.cout == block_n &&
+      block_n <= 64 && !a.no_relu && !a.stats) {
+    p.const_affine = 1;
+    memcpy(p.c_bias, a.h_bias, a.cout * sizeof(float));
+    memcpy(p.c_scale, a.h_scale, a.cout * sizeof(float));
+    memcpy(p.c_shift, a.h_shift, a.cout * sizeof(float));
+  }
   p.bias = a.bias;
   p.bn_scale = a.scale;
   p.bn_shift = a.shift;
@@ -630,6 +643,11 @@ struct itmo_ctx {
   // host copy of layer 0's bias / folded BN scale / shift: passed to rgb_conv_tc_kernel by value (constant bank)
   itmo::RgbAffine l0_affine = {};
   bool l0_affine_valid = false;
+  // host copies of every layer's bias / folded scale / shift (ConvArgs::h_*)
+  float h_bias[ITMO_NUM_LAYERS][itmo::kMaxCout] = {};
+  float h_scale[ITMO_NUM_LAYERS][itmo::kMaxCout] = {};
+  float h_shift[ITMO_NUM_LAYERS][itmo::kMaxCout] = {};
+  bool h_affine_valid = false;
   long long launches = 0;
   int last_chunk = 0;  // images in the most recent forward chunk (for itmo_read_activation)
 
@@ -747,6 +765,11 @@ int forward_chunk(itmo_ctx* ctx, const void* in_dev, int in_dtype, void* out_dev
     a.pooled = L.pool ? ctx->pooled[li] : nullptr;
     a.pooled_lo = L.pool ? ctx->pooled_lo[li] : nullptr;
     a.head_dtype = itmo::kHeadNone;
+    if (ctx->h_affine_valid) {
+      a.h_bias = ctx->h_bias[li];
+      a.h_scale = ctx->h_scale[li];
+      a.h_shift = ctx->h_shift[li];
+    }
     if (li == 17) {
       a.out = nullptr;  // conv2d_14's activation only feeds the head: never written to HBM
       a.out_lo = nullptr;
@@ -973,6 +996,20 @@ int itmo_load_weights(itmo_ctx* ctx, const itmo_layer_weights* layers, int n_lay
     if (e == cudaSuccess) e = cudaMemcpy(ctx->l0_affine.shift, ctx->shift[0], 32 * 4, cudaMemcpyDeviceToHost);
     if (e != cudaSuccess) rc = fail(ITMO_ERR_CUDA, "layer 0 affine read-back failed: %s", cudaGetErrorString(e));
     else ctx->l0_affine_valid = true;
+  }
+  ctx->h_affine_valid = false;
+  if (rc == ITMO_OK) {
+    cudaError_t e = cudaSuccess;
+    for (int li = 0; li < ITMO_NUM_LAYERS && e == cudaSuccess; ++li) {
+      const LayerDef& L = kLayers[li];
+      e = cudaMemcpy(ctx->h_bias[li], ctx->bias[li], L.cout * 4, cudaMemcpyDeviceToHost);
+      if (e == cudaSuccess && L.kind != kHead) {
+        e = cudaMemcpy(ctx->h_scale[li], ctx->scale[li], L.cout * 4, cudaMemcpyDeviceToHost);
+        if (e == cudaSuccess) e = cudaMemcpy(ctx->h_shift[li], ctx->shift[li], L.cout * 4, cudaMemcpyDeviceToHost);
+      }
+    }
+    if (e != cudaSuccess) rc = fail(ITMO_ERR_CUDA, "affine read-back failed: %s", cudaGetErrorString(e));
+    else ctx->h_affine_valid = true;
   }
   if (rc == ITMO_OK) ctx->weights_loaded = true;
   return rc;
