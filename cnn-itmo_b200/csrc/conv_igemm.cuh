@@ -75,6 +75,7 @@ struct ConvParams {
   int dbg;             // timing experiments only (results wrong): 16 no activation TMA, 32 no epilogue, 64 no MMAs
   int kb_hi;           // channel blocks of the leading (x*w_hi) part; the rest go to accumulator S-1
   int cout_log2;       // log2(cout) when cout is a power of two, else -1
+  int identity_epi;    // 1 (with no_relu): bias = 0, scale = 1, shift = 0 — the epilogue stores the accumulator as is
   int no_relu;         // 1: y = (acc + bias) * scale + shift without the ReLU (data-gradient convolutions of the training step)
   double* stats;       // training forward (16-bit modes): per-channel sum [cout] and sum of squares [cout] of the stored
                        // output z = ReLU(acc + bias) are accumulated here (BatchNormalization batch statistics,
@@ -606,7 +607,7 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
           // than without the constant path, an A/B wash overall.)
           const bool use_const = BLOCK_N <= 64 && p.const_affine != 0;
           float4 b4[8];
-          if (!use_const) {
+          if (!use_const && !p.identity_epi) {
 #pragma unroll
             for (int i = 0; i < 8; ++i) b4[i] = reinterpret_cast<const float4*>(s_bias + co0)[i];
           }
@@ -630,7 +631,10 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
           }
           if (!use_const) {
             if (with_stats) epi_affine<true, false>(v, f, b4, s_scale + co0, s_shift + co0);
-            else if (p.no_relu) epi_affine<false, true>(v, f, b4, s_scale + co0, s_shift + co0);
+            else if (p.no_relu && p.identity_epi) {   // data-gradient convolutions: nothing to add or scale
+#pragma unroll
+              for (int i = 0; i < kChunk; ++i) f[i] = __uint_as_float(v[i]);
+            } else if (p.no_relu) epi_affine<false, true>(v, f, b4, s_scale + co0, s_shift + co0);
             else epi_affine<false, false>(v, f, b4, s_scale + co0, s_shift + co0);
           }
           {

@@ -366,6 +366,7 @@ struct ConvArgs {
   // training step extensions (data-gradient convolutions)
   int one_tap;               // conv mode with a single tap and no padding (1x1 convolution)
   int no_relu;               // linear epilogue
+  int identity_epi;          // with no_relu: bias = 0, scale = 1, shift = 0 (the caller guarantees it)
   long long row_stride[2];   // source 0 / 1 viewed with these row / image strides (elements, 0 = dense)
   long long img_stride[2];
   int w_tap_stride_rows;     // rows between two taps of the packed weights (0 = the rows this launch uses)
@@ -491,6 +492,7 @@ int run_conv(const ConvArgs& a, cudaStream_t stream) {
   p.dbg = dbg;
   p.acc_split = acc_split;
   p.no_relu = a.no_relu;
+  p.identity_epi = (a.no_relu && a.identity_epi) ? 1 : 0;
   p.stats = a.stats;
   p.kb_hi = cin / bk;
   p.store_mode = a.precision == ITMO_PREC_TF32   ? itmo::kStoreTf32Rna

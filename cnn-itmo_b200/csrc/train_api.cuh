@@ -440,6 +440,7 @@ int train_backward(itmo_trainer* t, const void* x, int x_dtype, const float* y, 
         a.cout = src == 0 ? L.cin0 : L.cin1;
         a.out = dst;
         a.no_relu = 1;
+        a.identity_epi = 1;   // zeros / ones above: plain store of the accumulator
         a.head_dtype = itmo::kHeadNone;
         {
           PhaseStamp ps(t, kPhDgrad, s, __LINE__);
@@ -477,6 +478,7 @@ int train_backward(itmo_trainer* t, const void* x, int x_dtype, const float* y, 
       a.cout = L.cin0;
       a.out = dNext;
       a.no_relu = 1;
+      a.identity_epi = 1;   // zeros / ones above: plain store of the accumulator
       a.head_dtype = itmo::kHeadNone;
       PhaseStamp ps(t, kPhDgrad, s, __LINE__);
       int rc = run_conv(a, s);
@@ -795,6 +797,7 @@ int itmo_dgrad3x3(const void* g, int cout, int n, int h, int w, const float* ker
   a.cout = cin;
   a.out = dx;
   a.no_relu = 1;
+  a.identity_epi = 1;   // zeros / ones above: plain store of the accumulator
   a.head_dtype = itmo::kHeadNone;
   int rc = run_conv(a, s);
   cudaFreeAsync(wp, s);
