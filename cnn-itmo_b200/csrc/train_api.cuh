@@ -108,10 +108,16 @@ int run_wgrad(const WgradArgs& a, cudaStream_t stream) {
   itmo::WgradParams p;
   memset(&p, 0, sizeof(p));
   p.pad = a.conv3x3 ? 1 : 0;
-  p.tg = a.conv3x3 ? 3 : 1;
-  p.n_groups = a.conv3x3 ? 3 : 1;
-  int rc = make_act_map(&p.tmA, a.a, ITMO_PREC_BF16, a.ca_tensor, a.w, a.h, a.n, 128, 8 + 2 * p.pad, 16, a.a_row_stride,
-                        a.a_img_stride);
+  // Narrow 3x3 layers (<= 64 shifted channels, <= 32 gradient channels: conv2d_1, conv2d_2): one CTA holds all nine
+  // taps (9 x 32 accumulator columns), so a pixel block's halo tile and gradient tile are loaded once instead of once
+  // per kernel row — these layers were bound by the shared-memory traffic of those loads plus the MMA operand reads.
+  static const int allow_tg9 = env_int("ITMO_WGRAD_TG9", 1);
+  const bool tg9 = allow_tg9 && a.conv3x3 && bn <= 32 && a.ca <= 64;
+  p.tg = a.conv3x3 ? (tg9 ? 9 : 3) : 1;
+  p.n_groups = (a.conv3x3 && !tg9) ? 3 : 1;
+  p.a_rows = tg9 ? 18 : 16;
+  int rc = make_act_map(&p.tmA, a.a, ITMO_PREC_BF16, a.ca_tensor, a.w, a.h, a.n, 128, 8 + 2 * p.pad, p.a_rows,
+                        a.a_row_stride, a.a_img_stride);
   if (rc) return rc;
   rc = make_act_map(&p.tmB, a.b, ITMO_PREC_BF16, a.cb, a.w, a.h, a.n, 128, 8, 16);
   if (rc) return rc;
@@ -124,7 +130,7 @@ int run_wgrad(const WgradArgs& a, cudaStream_t stream) {
   static const int allow_m64 = env_int("ITMO_WGRAD_M64", 1);
   p.m64 = (allow_m64 && a.ca <= 64) ? 1 : 0;
   p.b_boxes = (bn + 63) / 64;
-  p.a_box_bytes = 16 * (8 + 2 * p.pad) * itmo::kWgRowBytes;
+  p.a_box_bytes = (p.a_rows * (8 + 2 * p.pad) * itmo::kWgRowBytes + 1023) / 1024 * 1024;   // 1 KB-aligned slot (swizzle atom)
   p.stage_bytes = p.a_boxes * p.a_box_bytes + p.b_boxes * itmo::kWgBoxPixB * itmo::kWgRowBytes;
   // With one A box the MMA (always M = 128) still reads a second 64-channel group one box further on: its rows are
   // never stored, but the read must stay inside the allocation -> one box of slack after the last stage.

@@ -36,8 +36,9 @@ struct WgradParams {
   CUtensorMap tmB;   // dims (Cb, W, H, N), box (64, 8, 16, 1), SWIZZLE_128B
   int H, W, NB;      // spatial size / batch of the (common) pixel grid
   int pad;           // 1: 3x3 conv (taps shift A by -1..1), 0: single tap
-  int tg;            // taps per tile = accumulators (3 or 1)
-  int n_groups;      // kernel rows (3 or 1)
+  int tg;            // taps per tile = accumulators: 3 (one kernel row), 9 (the whole 3x3 kernel, narrow layers) or 1
+  int n_groups;      // tiles along the kernel rows: 3 when tg == 3, else 1
+  int a_rows;        // pixel rows of an A box: 16, or 18 when the CTA covers all three kernel rows (tg == 9)
   int m_blocks;      // ceil(Ca / 128)
   int n_blocks;      // Cb / BN
   int a_boxes;       // 64-channel boxes of A per stage (1 or 2)
@@ -108,7 +109,8 @@ __global__ void __launch_bounds__(kWgThreads, 1) wgrad_igemm_kernel(const __grid
 
   if (warp_idx == 0) {
     if (sm100::elect_one()) {
-      const uint32_t bytes = uint32_t(p.a_boxes * p.a_box_bytes + p.b_boxes * kWgBoxPixB * kWgRowBytes);
+      // bytes the TMA delivers per stage (a_box_bytes is the 1 KB-aligned SLOT of a box, its data can be smaller)
+      const uint32_t bytes = uint32_t(p.a_boxes * p.a_rows * halo_w * kWgRowBytes + p.b_boxes * kWgBoxPixB * kWgRowBytes);
       int s = 0;
       uint32_t ph = 0;
       for (int pb = pb_beg; pb < pb_end; ++pb) {
@@ -121,7 +123,7 @@ __global__ void __launch_bounds__(kWgThreads, 1) wgrad_igemm_kernel(const __grid
         sm100::mbar_arrive_expect_tx(&full[s], bytes);
         for (int j = 0; j < p.a_boxes; ++j)
           sm100::tma_load_4d(st + j * p.a_box_bytes, &p.tmA, &full[s], mb * 128 + j * 64, tx * 8 - p.pad,
-                             ty * 16 + g - p.pad, img, sm100::kEvictNormal);
+                             ty * 16 + (p.tg == 9 ? 0 : g) - p.pad, img, sm100::kEvictNormal);
         uint8_t* sb = st + p.a_boxes * p.a_box_bytes;
         for (int j = 0; j < p.b_boxes; ++j)
           sm100::tma_load_4d(sb + j * kWgBoxPixB * kWgRowBytes, &p.tmB, &full[s], nb * BN + j * 64, tx * 8, ty * 16, img,
@@ -152,10 +154,12 @@ __global__ void __launch_bounds__(kWgThreads, 1) wgrad_igemm_kernel(const __grid
         const uint32_t a_lo = wg_desc_lo(a_addr, a_lbo);
         const uint32_t b_lo = wg_desc_lo(b_addr, b_lbo);
         for (int t = 0; t < p.tg; ++t) {
+          // tap -> whole-pixel shift inside the halo tile: (ky, kx) when the CTA holds all nine taps, else kx only
+          const int tshift = p.tg == 9 ? (t / 3) * halo_w + (t % 3) : t;
 #pragma unroll
           for (int ks = 0; ks < 8; ++ks) {
             const uint64_t da =
-                (uint64_t(a_hi) << 32) | uint64_t(a_lo + ((uint32_t((2 * ks * halo_w + t) * kWgRowBytes)) >> 4));
+                (uint64_t(a_hi) << 32) | uint64_t(a_lo + ((uint32_t((2 * ks * halo_w + tshift) * kWgRowBytes)) >> 4));
             const uint64_t db = (uint64_t(b_hi) << 32) | uint64_t(b_lo + ((uint32_t(2 * ks * 8 * kWgRowBytes)) >> 4));
             sm100::umma_ss<false>(tmem_base + uint32_t(t * BN), da, db, idesc, (pb != pb_beg || ks != 0) ? 1u : 0u);
           }
