@@ -328,7 +328,7 @@ __global__ void __launch_bounds__(128) head_train_kernel(const __nv_bfloat16* __
 
 // ---- BN backward, pass 1: per-channel sums of dA' and dA' * zhat (dA' = dA through the dropout mask) ---------------
 // sums[0..C) = sum dA', sums[C..2C) = sum dA' * (z - mean) * invstd
-__global__ void __launch_bounds__(256, 3) bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dA,
+__global__ void __launch_bounds__(256, 4) bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dA,
                                                             const __nv_bfloat16* __restrict__ z, size_t npix, int C,
                                                             const float* __restrict__ mean, const float* __restrict__ invstd,
                                                             uint32_t drop_seed, int dropout, double* __restrict__ sums) {
