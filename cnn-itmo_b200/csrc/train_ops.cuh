@@ -164,12 +164,18 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const __nv_bfloat16* __re
       }
     }
     float mx[8];
+    Bf8 zin[4];   // the four loads of the window first: all in flight before the first dependent store
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const size_t pix = (size_t(img) * H + 2 * yp + (k >> 1)) * W + 2 * xp + (k & 1);
+      zin[k] = ld8(z + pix * C + cg * 8);
+    }
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
       const size_t pix = (size_t(img) * H + 2 * yp + (k >> 1)) * W + 2 * xp + (k & 1);
       const size_t e0 = pix * C + cg * 8;
       float f[8];
-      ld8(z + e0).get(f);
+      zin[k].get(f);
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
         f[i] = fmaf(f[i], sc[i], sh[i]);
