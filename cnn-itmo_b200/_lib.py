@@ -41,6 +41,7 @@ SIGNATURES = {
     'itmo_forward': (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_int, c_uint, c_void_p]),
     'itmo_predict_host': (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_int, c_uint]),
     'itmo_launch_count': (c_longlong, [c_void_p]),
+    'itmo_saturation_count': (c_int, [c_void_p, POINTER(ctypes.c_ulonglong), c_int]),
     'itmo_host_alloc': (c_int, [POINTER(c_void_p), c_size_t]),
     'itmo_host_free': (None, [c_void_p]),
     'itmo_set_profiling': (c_int, [c_void_p, c_int]),
@@ -71,6 +72,8 @@ SIGNATURES = {
     'itmo_train_dropout_seed': (c_int, [c_uint, c_int, POINTER(c_uint)]),
     'itmo_train_metrics': (c_int, [c_void_p, POINTER(c_double), POINTER(c_double), c_int, c_void_p]),
     'itmo_train_update': (c_int, [c_void_p, c_int, c_float, c_float, c_float, c_float, c_float, c_void_p]),
+    'itmo_train_set_step': (c_int, [c_void_p, c_longlong]),
+    'itmo_train_get_step': (c_longlong, [c_void_p]),
     'itmo_train_read_activation': (c_int, [c_void_p, c_int, c_int, c_int, POINTER(c_float), c_size_t,
                                            POINTER(c_size_t)]),
     'itmo_train_set_profiling': (c_int, [c_void_p, c_int]),

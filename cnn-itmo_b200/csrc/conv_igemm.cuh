@@ -86,6 +86,9 @@ struct ConvParams {
   // bound by (it is shared with the tensor core's operand reads).
   int const_affine;
   float c_bias[64], c_scale[64], c_shift[64];
+  // fp16 storage only: incremented once per (thread, 32-channel chunk) in which a value was clamped to +-65504 by the
+  // saturating pack, so a checkpoint whose activations leave fp16's range cannot clip silently (itmo_saturation_count)
+  unsigned long long* sat_count;
   const float* bias;      // [cout]
   const float* bn_scale;  // [cout]  gamma / sqrt(var + eps)
   const float* bn_shift;  // [cout]  beta - mean * scale
@@ -654,6 +657,14 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
           const bool pool_writer = (lane & 9) == 0;          // even row, even column of the block
           const size_t ppix = (size_t(img) * (p.H / 2) + (y >> 1)) * (p.W / 2) + (x >> 1);
           if constexpr (sizeof(Elem) == 2) {
+            if constexpr (ElemTraits<Elem>::kFmt == sm100::kFmtF16) {
+              if (p.sat_count != nullptr && (p.out != nullptr || p.pooled != nullptr)) {
+                float amax = 0.f;
+#pragma unroll
+                for (int i = 0; i < kChunk; ++i) amax = fmaxf(amax, fabsf(f[i]));
+                if (amax > 65504.f) atomicAdd(p.sat_count, 1ull);
+              }
+            }
             uint32_t pk[kChunk / 2];
 #pragma unroll
             for (int i = 0; i < kChunk / 2; ++i) pk[i] = pack2<Elem>(f[2 * i], f[2 * i + 1]);

@@ -74,8 +74,20 @@ __device__ __forceinline__ double srgb_pow22(uint8_t v) { return pow(double(v) /
 __device__ __forceinline__ double rgb2lum(double r, double g, double b) {  // HDR-Toolbox RGB2Lum (Rec.709), :3
   return 0.2126 * r + 0.7152 * g + 0.0722 * b;
 }
-// inverse_Reinhard.m:4 as written divides by (I - 1); the inverse of Reinhard.m:22 L = X/(1+X) is X = L/(1-L)
-__device__ __forceinline__ double tone_inverse(double I, int as_written) { return as_written ? I / (I - 1.0) : I / (1.0 - I); }
+// inverse_Reinhard.m:4 as written divides by (I - 1); the inverse of Reinhard.m:22 L = X/(1+X) is X = L/(1-L).
+// The repaired form clamps I to 1 - 0.5/255 first: a saturated (255,255,255) pixel would otherwise give X = +inf, an
+// infinite geometric mean and an all-zero frame — and saturated highlights are the core inverse-tone-mapping case.
+constexpr double kLumMax = 1.0 - 0.5 / 255.0;
+__device__ __forceinline__ double tone_inverse(double I, int as_written) {
+  return as_written ? I / (I - 1.0) : fmin(I, kLumMax) / (1.0 - fmin(I, kLumMax));
+}
+// One pixel's term of the log-average (inverse_Reinhard.m:5-11). As written: log(max(X, realmin)) for every pixel.
+// Repaired: zero-luminance pixels are LEFT OUT of the geometric mean (each would add log(realmin) = -708 and 1 % of
+// black pixels would raise the scale ~1000x into the 2^32 clip); the mean is taken over the non-zero count.
+__device__ __forceinline__ double log_term(double I, int as_written) {
+  if (!as_written && I == 0.0) return 0.0;
+  return log(fmax(tone_inverse(I, as_written), DBL_MIN));   // max(NaN, realmin) = realmin in MATLAB and in fmax
+}
 
 // out frame <- valid rectangles of the tiles. T = uint8_t (optionally with the fused reductions) or float.
 template <typename T, bool STATS>
@@ -105,8 +117,7 @@ __global__ void __launch_bounds__(256) tile_scatter_kernel(const T* __restrict__
 #pragma unroll 4
       for (int p = 0; p < kPixPerThread; ++p) {
         const double I = rgb2lum(srgb_pow22(px[3 * p]), srgb_pow22(px[3 * p + 1]), srgb_pow22(px[3 * p + 2]));
-        const double X = tone_inverse(I, as_written);
-        lsum += log(fmax(X, DBL_MIN));   // max(NaN, realmin) = realmin in MATLAB and in fmax
+        lsum += log_term(I, as_written);
         zeros += (I == 0.0);
       }
     }
@@ -141,7 +152,7 @@ __global__ void __launch_bounds__(256) frame_stats_kernel(const uint8_t* __restr
   unsigned long long zeros = 0;
   for (size_t p = blockIdx.x * size_t(blockDim.x) + threadIdx.x; p < n_pix; p += size_t(gridDim.x) * blockDim.x) {
     const double I = rgb2lum(srgb_pow22(frame[3 * p]), srgb_pow22(frame[3 * p + 1]), srgb_pow22(frame[3 * p + 2]));
-    lsum += log(fmax(tone_inverse(I, as_written), DBL_MIN));
+    lsum += log_term(I, as_written);
     zeros += (I == 0.0);
   }
   for (int o = 16; o > 0; o >>= 1) {
@@ -156,13 +167,16 @@ __global__ void __launch_bounds__(256) frame_stats_kernel(const uint8_t* __restr
 
 // inverse_Reinhard.m:11-23 per pixel. as_written = 1 follows the script literally (IEEE semantics of its
 // degenerate cases included: G_E = exp(P log G_X / PB1 - PB2 log a / PB1), division by the zero-luminance count).
-// as_written = 0 is the repaired form: X = I/(1-I), E = key * X / G_X (geometric mean of the recovered luminance
-// normalised to `key`, mirroring Reinhard.m:19-21), zero-luminance pixels stay black.
+// as_written = 0 is the repaired form: X = I'/(1-I') with I' = min(I, 1 - 0.5/255), E = key * X / G_X (geometric mean
+// of the recovered luminance over the non-black pixels normalised to `key`, mirroring Reinhard.m:19-21), zero-luminance
+// pixels stay black.
 __global__ void __launch_bounds__(256) inverse_reinhard_kernel(const uint8_t* __restrict__ frame, float* __restrict__ hdr,
                                                                size_t n_pix, const FrameStats* __restrict__ stats,
                                                                int as_written, double key) {
   const double P = double(n_pix);
-  const double G_X = exp(stats->log_sum / P);  // :11
+  const double nz = P - double(stats->zero_lum);
+  // :11; the repaired form averages over the non-zero-luminance pixels (an all-black frame stays black)
+  const double G_X = as_written ? exp(stats->log_sum / P) : (nz > 0 ? exp(stats->log_sum / nz) : 1.0);
   double scale;
   if (as_written) {
     const double PB1 = double(stats->zero_lum), PB2 = P - PB1;  // :13-14

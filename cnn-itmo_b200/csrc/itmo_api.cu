@@ -376,6 +376,7 @@ struct ConvArgs {
   const float* h_bias;
   const float* h_scale;
   const float* h_shift;
+  unsigned long long* sat_count;   // fp16: device counter of clamped store groups (ConvParams::sat_count) or null
 };
 
 // Debug / tuning overrides (environment, read once): ITMO_FORCE_NM = 1|2|4, ITMO_NO_RESIDENT = 1
@@ -506,6 +507,7 @@ int run_conv(const ConvArgs& a, cudaStream_t stream) {
     memcpy(p.c_scale, a.h_scale, a.cout * sizeof(float));
     memcpy(p.c_shift, a.h_shift, a.cout * sizeof(float));
   }
+  p.sat_count = a.precision == ITMO_PREC_FP16 ? a.sat_count : nullptr;
   p.bias = a.bias;
   p.bn_scale = a.scale;
   p.bn_shift = a.shift;
@@ -652,6 +654,7 @@ struct itmo_ctx {
   bool h_affine_valid = false;
   long long launches = 0;
   int last_chunk = 0;  // images in the most recent forward chunk (for itmo_read_activation)
+  unsigned long long* sat_dev = nullptr;  // fp16 mode: clamped store groups since creation / the last reset
 
   // per layer device parameters
   void* wpacked[ITMO_NUM_LAYERS] = {};   // tensor-core layers: packed; layer 0: fp32 HWIO; head: fp32 [3][64]
@@ -767,6 +770,7 @@ int forward_chunk(itmo_ctx* ctx, const void* in_dev, int in_dtype, void* out_dev
     a.pooled = L.pool ? ctx->pooled[li] : nullptr;
     a.pooled_lo = L.pool ? ctx->pooled_lo[li] : nullptr;
     a.head_dtype = itmo::kHeadNone;
+    a.sat_count = ctx->sat_dev;
     if (ctx->h_affine_valid) {
       a.h_bias = ctx->h_bias[li];
       a.h_scale = ctx->h_scale[li];
@@ -793,7 +797,7 @@ int forward_chunk(itmo_ctx* ctx, const void* in_dev, int in_dtype, void* out_dev
 extern "C" {
 
 const char* itmo_last_error(void) { return g_last_error.c_str(); }
-int itmo_abi_version(void) { return 3; }
+int itmo_abi_version(void) { return 4; }
 
 int itmo_create(itmo_ctx** out, int device, int precision, int max_batch) {
   if (!out) return fail(ITMO_ERR_INVALID, "out is null");
@@ -870,6 +874,12 @@ int itmo_create(itmo_ctx** out, int device, int precision, int max_batch) {
     if (offs_act_lo[li] != size_t(-1)) ctx->act_lo[li] = (char*)ctx->arena + offs_act_lo[li];
     if (offs_pool_lo[li] != size_t(-1)) ctx->pooled_lo[li] = (char*)ctx->arena + offs_pool_lo[li];
   }
+  e = cudaMalloc((void**)&ctx->sat_dev, sizeof(unsigned long long));
+  if (e == cudaSuccess) e = cudaMemset(ctx->sat_dev, 0, sizeof(unsigned long long));
+  if (e != cudaSuccess) {
+    itmo_destroy(ctx);
+    return fail(ITMO_ERR_NOMEM, "cudaMalloc(counter) failed: %s", cudaGetErrorString(e));
+  }
   e = cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking);
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->h2d_stream, cudaStreamNonBlocking);
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->d2h_stream, cudaStreamNonBlocking);
@@ -897,6 +907,7 @@ void itmo_destroy(itmo_ctx* ctx) {
     cudaFree(ctx->shift[li]);
   }
   cudaFree(ctx->arena);
+  cudaFree(ctx->sat_dev);
   cudaFree(ctx->frm_tiles_in);
   cudaFree(ctx->frm_tiles_out);
   cudaFree(ctx->frm_u8);
@@ -1259,6 +1270,15 @@ int itmo_layer_times(itmo_ctx* ctx, double* ms_sum, long long* calls, int reset)
 }
 
 long long itmo_launch_count(const itmo_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+int itmo_saturation_count(itmo_ctx* ctx, unsigned long long* count, int reset) {
+  if (!ctx || !count) return fail(ITMO_ERR_INVALID, "null argument");
+  ITMO_CUDA(cudaSetDevice(ctx->device));
+  ITMO_CUDA(cudaDeviceSynchronize());
+  ITMO_CUDA(cudaMemcpy(count, ctx->sat_dev, sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+  if (reset) ITMO_CUDA(cudaMemset(ctx->sat_dev, 0, sizeof(unsigned long long)));
+  return ITMO_OK;
+}
 
 int itmo_read_activation(itmo_ctx* ctx, int layer, int which, float* dst_host, size_t cap_elems, size_t* n_elems) {
   if (!ctx || !dst_host || !n_elems) return fail(ITMO_ERR_INVALID, "null argument");

@@ -695,6 +695,15 @@ int itmo_train_update(itmo_trainer* t, int optimizer, float lr, float beta1_or_r
   return itmo_trainer_sync_weights(t, stream);
 }
 
+int itmo_train_set_step(itmo_trainer* t, long long steps) {
+  if (!t) return fail(ITMO_ERR_INVALID, "null trainer");
+  if (steps < 0) return fail(ITMO_ERR_INVALID, "negative step count");
+  t->opt_steps = steps;
+  return ITMO_OK;
+}
+
+long long itmo_train_get_step(const itmo_trainer* t) { return t ? t->opt_steps : 0; }
+
 int itmo_train_read_activation(itmo_trainer* t, int layer, int which, int n, float* dst_host, size_t cap_elems,
                                size_t* n_elems) {
   if (!t || !dst_host) return fail(ITMO_ERR_INVALID, "null argument");

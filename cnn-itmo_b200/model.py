@@ -14,6 +14,7 @@ from __future__ import annotations
 import ctypes
 import math
 import os
+import warnings
 from typing import Any, Callable, Dict, List, Optional, Sequence
 
 import numpy as np
@@ -27,7 +28,9 @@ _PRECISIONS = {'bf16': _lib.PREC_BF16, 'fp16': _lib.PREC_FP16, 'tf32': _lib.PREC
 
 
 def _default_precision() -> str:
-    return os.environ.get('ITMO_PRECISION', 'bf16').lower()
+    # fp16 is the default 16-bit mode: same tensor-core rate as bf16 with three more significand bits; it holds the
+    # north-star's PSNR >= 45 dB on the calibrated checkpoint where bf16 measures ~32 dB. bf16 is opt-in.
+    return os.environ.get('ITMO_PRECISION', 'fp16').lower()
 
 
 def _he_normal(rng: np.random.Generator, shape, fan_in: int) -> np.ndarray:
@@ -61,6 +64,44 @@ def initial_weights(seed: Optional[int] = None) -> checkpoint.Weights:
     return ws
 
 
+FP16_MAX = 65504.0
+FP16_MIN_NORMAL = 2.0 ** -14
+
+
+def fp16_range_report(weights: checkpoint.Weights, bn_eps: float = graph.BN_EPS, sigmas: float = 1000.0) -> List[str]:
+    """Load-time range check of the fp16 storage mode (the default). Every tensor the kernels keep in HBM is a
+    post-BatchNormalization activation y = gamma * zhat + beta with zhat the standardised ReLU output, so its range
+    follows from gamma / beta: flagged when |beta| + `sigmas` * |gamma| could leave fp16's +-65504. The first layer
+    is bounded exactly (inputs are in [0,1]): |y| <= |s| * (sum |w| + |b|) + |t|. Weights are flagged when they
+    overflow fp16 or when more than 1 % of a kernel's energy sits below fp16's smallest normal (2^-14), where
+    precision is lost. Returns human-readable findings (empty = fine); the device-side counter
+    (Model.saturation_count) catches what a static check cannot."""
+    out: List[str] = []
+    for l, w in zip(graph.LAYERS, weights):
+        k = np.asarray(w['kernel'], np.float64)
+        if np.abs(k).max(initial=0.0) > FP16_MAX:
+            out.append(f'{l.name}: kernel magnitude {np.abs(k).max():.3g} exceeds the fp16 range')
+        if l.kind in ('conv', 'convT') and l.index != 0:
+            e = float((k ** 2).sum())
+            small = float((k[np.abs(k) < FP16_MIN_NORMAL] ** 2).sum())
+            if e > 0 and small / e > 0.01:
+                out.append(f'{l.name}: {100 * small / e:.1f} % of the kernel energy is below fp16\'s smallest normal '
+                           '(2^-14): reduced precision')
+        if l.kind == 'head':
+            continue
+        g, b = np.asarray(w['gamma'], np.float64), np.asarray(w['beta'], np.float64)
+        bound = float((np.abs(b) + sigmas * np.abs(g)).max())
+        if l.index == 0:
+            s = g / np.sqrt(np.asarray(w['moving_variance'], np.float64) + bn_eps)
+            t = b - np.asarray(w['moving_mean'], np.float64) * s
+            zmax = np.abs(k).reshape(-1, k.shape[-1]).sum(0) + np.abs(np.asarray(w['bias'], np.float64))
+            bound = float((np.abs(s) * zmax + np.abs(t)).max())
+        if bound > FP16_MAX:
+            out.append(f'{l.name}: post-BatchNormalization activations may reach {bound:.3g} (> 65504): fp16 storage '
+                       "could saturate; precision='tf32' / 'fp32' has fp32 range")
+    return out
+
+
 def pinned_empty(shape, dtype) -> np.ndarray:
     """numpy array in page-locked host memory (itmo_host_alloc): H2D/D2H copies from/to it are asynchronous, so
     ``predict`` / ``predict_u8`` overlap them with the kernels. The memory is released with the array."""
@@ -85,7 +126,7 @@ class Model:
         if tuple(input_size) != (graph.IMG, graph.IMG, 3):
             raise ValueError(f'input_size {tuple(input_size)} is not supported: the kernels are built for the '
                              f'reference\'s native ({graph.IMG}, {graph.IMG}, 3) input (model.py:204); larger frames '
-                             'go through cnn_itmo_b200.tiling')
+                             'go through cnn_itmo_b200.frames')
         precision = (precision or _default_precision()).lower()
         if precision not in _PRECISIONS:
             raise ValueError(f"precision must be one of {sorted(_PRECISIONS)}, got {precision!r}")
@@ -103,10 +144,14 @@ class Model:
         self._weights = weights if weights is not None else initial_weights()
         self._ctx = ctypes.c_void_p()
         self._uploaded = False
+        self._trainer = None
+        self._trained_dirty = False     # the trainer's parameters are newer than self._weights
+        self._range_checked = False
 
     # ---- device context -----------------------------------------------------------------------------
     def _ensure_ctx(self):
         lib = _lib.load()
+        self._sync_trained()
         if not self._ctx:
             _lib.check(lib.itmo_create(ctypes.byref(self._ctx), self.device, _PRECISIONS[self.precision],
                                        self.max_batch))
@@ -121,7 +166,27 @@ class Model:
                         setattr(arr[i], field, a.ctypes.data_as(ctypes.POINTER(ctypes.c_float)))
             _lib.check(lib.itmo_load_weights(self._ctx, arr, graph.NUM_LAYERS, self.bn_epsilon))
             self._uploaded = True
+        if self.precision == 'fp16' and not self._range_checked:
+            self._range_checked = True
+            for msg in fp16_range_report(self._weights, self.bn_epsilon):
+                warnings.warn(msg, RuntimeWarning, stacklevel=3)
         return lib
+
+    def saturation_count(self, reset: bool = False) -> int:
+        """fp16 mode: epilogue store groups that clamped a value to +-65504 since the context was created / last reset
+        (itmo_saturation_count; synchronises the device). 0 in every other mode."""
+        if not self._ctx:
+            return 0
+        n = ctypes.c_ulonglong(0)
+        _lib.check(_lib.load().itmo_saturation_count(self._ctx, ctypes.byref(n), int(reset)))
+        return int(n.value)
+
+    def _warn_if_saturated(self):
+        if self.precision == 'fp16':
+            n = self.saturation_count(reset=True)
+            if n:
+                warnings.warn(f'fp16 activations saturated in {n} store groups during this predict call: the result is '
+                              "clipped; use precision='tf32' or 'fp32' for this checkpoint", RuntimeWarning, stacklevel=3)
 
     def close(self):
         if getattr(self, '_ctx', None):
@@ -179,6 +244,7 @@ class Model:
         out = pinned_empty((xf.shape[0], graph.IMG, graph.IMG, 3), np.float32)
         _lib.check(lib.itmo_predict_host(self._ctx, xf.ctypes.data, _lib.DT_F32, out.ctypes.data, _lib.DT_F32,
                                          xf.shape[0], 0))
+        self._warn_if_saturated()
         return out
 
     def predict_u8(self, images_u8, out: Optional[np.ndarray] = None) -> np.ndarray:
@@ -198,6 +264,7 @@ class Model:
             raise ValueError('out must be a C-contiguous uint8 array with the input\'s shape')
         _lib.check(lib.itmo_predict_host(self._ctx, x.ctypes.data, _lib.DT_U8, out.ctypes.data, _lib.DT_U8,
                                          x.shape[0], 0))
+        self._warn_if_saturated()
         return out
 
     def forward_device(self, in_ptr: int, in_dtype: str, out_ptr: int, out_dtype: str, n: int, stream: int = 0):
@@ -238,6 +305,7 @@ class Model:
     def get_weights(self) -> List[np.ndarray]:
         """Flat list in Keras' model.get_weights() order (model.layers order; kernel, bias / gamma, beta,
         moving_mean, moving_variance per layer)."""
+        self._sync_trained()
         out: List[np.ndarray] = []
         for k in graph.keras_layers():
             if k.weight_layer is None:
@@ -266,17 +334,26 @@ class Model:
                 i += 1
         if i != len(flat):
             raise ValueError(f'set_weights: expected {i} arrays, got {len(flat)}')
+        self._install_weights(new)
+
+    def _install_weights(self, new):
+        """New host weights: the inference context re-uploads on next use and a live training engine takes them too."""
         self._weights = new
         self._uploaded = False
+        self._range_checked = False
+        self._trained_dirty = False
+        if self._trainer is not None:
+            self._trainer.set_weights(new)
 
     def load_weights(self, filepath: str, by_name: bool = False):
-        self._weights, meta = checkpoint.read_checkpoint(filepath)
+        new, meta = checkpoint.read_checkpoint(filepath)
         self.meta.update(meta)
-        self._uploaded = False
+        self._install_weights(new)
 
     def save_weights(self, filepath: str, overwrite: bool = True):
         if not overwrite and os.path.exists(filepath):
             raise OSError(f'{filepath} exists')
+        self._sync_trained()
         checkpoint.write_checkpoint(filepath, self._weights, weights_only=True)
 
     def save(self, filepath: str, overwrite: bool = True, include_optimizer: bool = True):
@@ -284,8 +361,8 @@ class Model:
         if not overwrite and os.path.exists(filepath):
             raise OSError(f'{filepath} exists')
         opt_w, opt_name = getattr(self, '_optimizer_weights', None), getattr(self, '_optimizer_name', 'rmsprop')
-        if getattr(self, '_trainer', None) is not None:
-            self._pull_trained_weights()
+        self._sync_trained()
+        if self._trainer is not None:
             opt_w, opt_name = self._trainer.get_optimizer_weights(), self._trainer.optimizer
         # /optimizer_weights (RMSprop accumulators in trainable_weights order) so that training can resume from the
         # file, here or in Keras
@@ -296,13 +373,13 @@ class Model:
     def _ensure_trainer(self, micro_batch: Optional[int] = None):
         """The training engine (train.Trainer over itmo_train_*), created on first use with the model's weights."""
         from . import train
-        if getattr(self, '_trainer', None) is None:
+        if self._trainer is None:
             if self.optimizer is None:
                 raise RuntimeError('You must compile a model before training/testing. Use `model.compile(optimizer, loss)`.')
             opt = self.optimizer if isinstance(self.optimizer, str) else self.optimizer.get('name', 'rmsprop')
             kw = {} if isinstance(self.optimizer, str) else {k: v for k, v in self.optimizer.items() if k != 'name'}
             self._trainer = train.Trainer(self._weights, micro_batch=micro_batch or self.train_micro_batch,
-                                          device=self.device, optimizer=opt, **kw)
+                                          device=self.device, optimizer=opt, seed=self.train_seed, **kw)
             pending = getattr(self, '_optimizer_weights', None)
             if pending is not None and getattr(self, '_optimizer_name', opt) == self._trainer.optimizer:
                 self._trainer.set_optimizer_weights(pending)   # resume from a checkpoint's /optimizer_weights
@@ -310,12 +387,18 @@ class Model:
         return self._trainer
 
     train_micro_batch = 8
+    train_seed: Optional[int] = None     # Dropout mask stream of the training engine; None = fresh entropy per engine
 
-    def _pull_trained_weights(self):
-        """Bring the trainer's parameters back into the host copy predict()/save() use."""
-        if getattr(self, '_trainer', None) is not None:
+    def _sync_trained(self):
+        """If train_on_batch ran since the last pull, bring the trainer's parameters (and BN moving statistics) back
+        into the host copy that predict() / get_weights() / save*() use, and mark the inference context stale. One
+        D2H of 11.2 M floats, only when something was trained in between (the reference's per-epoch makePrediction
+        callback, main.py:36-63, and ModelCheckpoint both land here)."""
+        if self._trained_dirty and self._trainer is not None:
             self._weights = self._trainer.get_weights()
             self._uploaded = False
+            self._range_checked = False
+        self._trained_dirty = False
 
     def train_on_batch(self, x, y, sample_weight=None, class_weight=None):
         """One optimizer step on x [N,512,512,3] (floats in [0,1] like main.py:71's rescale=1./255, or raw uint8) and
@@ -363,12 +446,15 @@ class Model:
             for cb in callbacks or []:
                 if hasattr(cb, 'on_epoch_end'):
                     cb.on_epoch_end(epoch, logs)
-        self._pull_trained_weights()
+        for cb in callbacks or []:
+            if hasattr(cb, 'on_train_end'):
+                cb.on_train_end({})
+        self._sync_trained()
         return history
 
     def test_on_batch(self, x, y):
-        """[loss, accuracy] in inference mode (moving statistics), like Keras' test_on_batch."""
-        self._pull_trained_weights()
+        """[loss, accuracy] in inference mode (moving statistics), like Keras' test_on_batch. The trained parameters are
+        pulled once per training phase (the dirty flag), not once per validation step."""
         x = self._check_input(x)
         y = np.asarray(y, np.float32)
         pred = self.predict(np.asarray(x, np.float32) / (255.0 if np.asarray(x).dtype == np.uint8 else 1.0))

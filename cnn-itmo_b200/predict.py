@@ -39,7 +39,7 @@ def load_png(path: str) -> np.ndarray:
         a = a[:, :, :3]
     if a.shape[:2] != (graph.IMG, graph.IMG):
         raise ValueError(f'{path}: {a.shape[1]}x{a.shape[0]} image; the model takes {graph.IMG}x{graph.IMG} '
-                         '(use cnn_itmo_b200.tiling for larger frames)')
+                         '(use cnn_itmo_b200.frames for larger frames)')
     return np.ascontiguousarray(a, dtype=np.uint8)
 
 

@@ -13,6 +13,7 @@ every rank. There is no CPU fallback.
 from __future__ import annotations
 
 import ctypes
+import os
 from typing import Dict, List, Optional, Sequence, Tuple
 
 import numpy as np
@@ -141,8 +142,19 @@ def optimizer_weights_to_flat(weights: Sequence[np.ndarray], layout, optimizer: 
 
 
 class Trainer:
+    """Batch statistics note: BatchNormalization's batch mean / variance (and its backward) are taken over ONE
+    micro-batch of this rank, not over the whole global batch — Keras on one device normalises over the whole batch it
+    is fed (main.py:87 feeds 2 images). With N <= micro_batch on one rank the two agree exactly; larger batches are a
+    gradient-accumulation approximation, like per-replica statistics in Keras' own multi-GPU data parallelism. The
+    moving statistics move ONCE per optimizer step (from the step's last micro-batch), as in Keras.
+
+    `seed`: base of the Dropout mask stream (mixed with the step, the micro-batch and the data-parallel rank, so ranks
+    draw different masks); None draws one from os.urandom so that a resumed run does not replay the masks of the run
+    it continues (RMSprop checkpoints do not carry an iteration count, Keras 2.2.x keeps only the accumulators)."""
+
     def __init__(self, weights: Sequence[Dict[str, np.ndarray]], micro_batch: int = 8, image_hw=(512, 512),
-                 device: int = 0, optimizer: str = 'rmsprop', lr: Optional[float] = None, **opt_kwargs):
+                 device: int = 0, optimizer: str = 'rmsprop', lr: Optional[float] = None, seed: Optional[int] = 0,
+                 **opt_kwargs):
         import torch
         if not torch.cuda.is_available():
             raise _lib.ItmoError('the training step needs an sm_100a GPU: there is no CPU fallback')
@@ -174,7 +186,23 @@ class Trainer:
                                            self.params.data_ptr(), self.grads.data_ptr(), self.opt_state.data_ptr(),
                                            self.bn_moving.data_ptr()))
         self.set_weights(weights)
-        self.step_index = 0
+        self.seed_base = int.from_bytes(os.urandom(4), 'little') if seed is None else int(seed)
+        self._copy_stream = None
+
+    @property
+    def step_index(self) -> int:
+        """Optimizer steps taken so far = Keras' `optimizer.iterations`; the library's counter is the one source of truth
+        (Adam's bias correction reads it)."""
+        return int(_lib.load().itmo_train_get_step(self._h)) if self._h else 0
+
+    @step_index.setter
+    def step_index(self, value: int):
+        _lib.check(_lib.load().itmo_train_set_step(self._h, int(value)))
+
+    def micro_seed(self, step: int, i0: int) -> int:
+        """Dropout seed of the micro-batch starting at local image i0 of optimizer step `step` on this rank."""
+        _, rank = world_info()
+        return (self.seed_base * 2654435761 + step * 7919 + i0 + rank * 104729) & 0xFFFFFFFF
 
     # ---- plumbing ---------------------------------------------------------------------------------------------
     def _stream(self) -> int:
@@ -242,7 +270,7 @@ class Trainer:
         state, it = optimizer_weights_to_flat(weights, self.layout, self.optimizer, self.n_params)
         self.opt_state.copy_(self._torch.from_numpy(state))
         if self.optimizer != 'rmsprop':
-            self.step_index = it
+            self.step_index = it     # itmo_train_set_step: the resumed step continues Adam's bias-correction schedule
 
     def get_grads(self) -> List[Dict[str, np.ndarray]]:
         self._torch.cuda.synchronize(self._dev)
@@ -279,7 +307,6 @@ class Trainer:
         o = self.opt
         _lib.check(_lib.load().itmo_train_update(self._h, _OPTIMIZERS[self.optimizer], o['lr'], o['beta1'], o['beta2'],
                                                  o['eps'], float(grad_scale), self._stream()))
-        self.step_index += 1
 
     def metrics(self, reset: bool = True) -> Tuple[float, float]:
         sq, hits = ctypes.c_double(), ctypes.c_double()
@@ -290,7 +317,8 @@ class Trainer:
     def train_on_batch(self, x, y, seed: Optional[int] = None, dropout: bool = True) -> List[float]:
         """One optimizer step on HOST arrays x [N,h,w,3] (uint8, or float in [0,1]) and y [N,h,w,3] (float target): this
         rank's share of the batch. Returns [loss, accuracy] of the whole (all-rank) batch, like Keras' train_on_batch
-        with metrics=['accuracy']."""
+        with metrics=['accuracy']. The H2D copy of micro-batch i+1 runs on a side stream while micro-batch i computes
+        (asynchronous only from pinned arrays — model.pinned_empty)."""
         import torch
         import torch.distributed as dist
         x = np.ascontiguousarray(x if np.asarray(x).dtype == np.uint8 else np.asarray(x, np.float32))
@@ -299,12 +327,33 @@ class Trainer:
         world, _ = world_info()
         n_global = n * world
         loss_count = global_loss_count(n, self.h, self.w, world)
-        seed = self.step_index if seed is None else seed
+        step = self.step_index if seed is None else seed
+        if self._copy_stream is None:
+            self._copy_stream = torch.cuda.Stream(self._dev)
+        main = torch.cuda.current_stream(self._dev)
+        starts = list(range(0, n, self.micro_batch))
+
+        def upload(i0):
+            # staged on the side stream; the tensors are handed to the compute stream through an event
+            with torch.cuda.stream(self._copy_stream):
+                xs = torch.from_numpy(x[i0:i0 + self.micro_batch]).to(self._dev, non_blocking=True)
+                ys = torch.from_numpy(y[i0:i0 + self.micro_batch]).to(self._dev, non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(self._copy_stream)
+            return xs, ys, ev
+
         self.zero_grad()
-        for i0 in range(0, n, self.micro_batch):
-            xs = torch.from_numpy(x[i0:i0 + self.micro_batch]).to(self._dev, non_blocking=True)
-            ys = torch.from_numpy(y[i0:i0 + self.micro_batch]).to(self._dev, non_blocking=True)
-            self.backward(xs, ys, loss_count, seed=seed * 7919 + i0, dropout=dropout)
+        nxt = upload(starts[0])
+        for k, i0 in enumerate(starts):
+            xs, ys, ev = nxt
+            if k + 1 < len(starts):
+                nxt = upload(starts[k + 1])
+            main.wait_event(ev)
+            # BN moving statistics move once per optimizer step (Keras updates them once per batch): last micro-batch only
+            self.backward(xs, ys, loss_count, seed=self.micro_seed(step, i0), dropout=dropout,
+                          freeze_moving=(k + 1 < len(starts)))
+            xs.record_stream(main)
+            ys.record_stream(main)
         self.allreduce_grads()
         self.update()
         sq, hits = self.metrics()

@@ -577,17 +577,24 @@ def inverse_reinhard_np(img_u8: np.ndarray, as_written: bool = False, key: float
       :12-16 G_E = exp(P log(G_X)/PB1 - PB2 log(a)/PB1), PB1 = #(I==0), PB2 = #(I~=0)  (divides by the count of
              zero-luminance pixels)     :17 E = G_E X / a     :18 NaN -> realmin     :19 clamp at 2^32
       :20-23 out_c = ImgIn_c * E / I
-    as_written=False is the repaired form implemented as the product's default: X = I/(1-I), E = key * X / G_X
-    (the recovered luminance is normalised to geometric mean `key`, mirroring Reinhard.m:19-21), zero-luminance
-    pixels stay black instead of NaN."""
+    as_written=False is the repaired form implemented as the product's default: X = I'/(1-I') with
+    I' = min(I, 1 - 0.5/255) (a saturated pixel must not drive the geometric mean to infinity), E = key * X / G_X
+    with G_X the geometric mean of X over the NON-ZERO-luminance pixels (the recovered luminance is normalised to
+    `key`, mirroring Reinhard.m:19-21; black pixels are left out of the log-average instead of contributing
+    log(realmin) each), zero-luminance pixels stay black instead of NaN."""
     realmin = np.finfo(np.float64).tiny
     img = (img_u8.astype(np.float64) / 255.0) ** 2.2
     I = 0.2126 * img[..., 0] + 0.7152 * img[..., 1] + 0.0722 * img[..., 2]
     with np.errstate(divide='ignore', invalid='ignore', over='ignore'):
-        X = I / (I - 1.0) if as_written else I / (1.0 - I)
+        Ic = np.minimum(I, 1.0 - 0.5 / 255.0)
+        X = I / (I - 1.0) if as_written else Ic / (1.0 - Ic)
         Xc = np.where(np.isnan(X), realmin, np.maximum(X, realmin))   # MATLAB max(NaN, realmin) = realmin
         P = float(I.size)
-        G_X = np.exp(np.log(Xc).sum() / P)
+        if as_written:
+            G_X = np.exp(np.log(Xc).sum() / P)
+        else:
+            nz = I != 0
+            G_X = np.exp(np.log(Xc[nz]).sum() / float(nz.sum())) if nz.any() else 1.0
         if as_written:
             PB1 = float((I == 0).sum())
             PB2 = P - PB1

@@ -74,6 +74,19 @@ def test_inverse_reinhard_restatement():
     assert np.nanmax(np.abs(bad)) < 1e-300
 
 
+def test_inverse_reinhard_restatement_saturated_and_black():
+    """Repaired variant on a frame with saturated and black pixels: finite, black stays black, key preserved."""
+    img = R.synthetic_images_u8(1, seed=21, size=64)[0]
+    img[:8, :8] = 255
+    img[40:44, :] = 0
+    hdr = R.inverse_reinhard_np(img, key=0.18)
+    assert np.isfinite(hdr).all() and hdr.max() < 2.0 ** 31
+    assert (hdr[40:44] == 0).all() and hdr[:8, :8].min() > 1.0
+    lum = hdr @ np.array([0.2126, 0.7152, 0.0722])
+    assert abs(np.exp(np.log(lum[lum > 0]).mean()) - 0.18) < 1e-9
+    assert (R.inverse_reinhard_np(np.zeros((16, 16, 3), np.uint8)) == 0).all()
+
+
 def test_shard_functions():
     for n in (0, 1, 7, 16, 84):
         for world in (1, 2, 3, 8):

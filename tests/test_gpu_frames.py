@@ -63,6 +63,26 @@ def test_inverse_reinhard_matches_restatement(as_written):
         assert np.allclose(got[i][~nan_g], want[~nan_w], rtol=2e-5, atol=1e-30)
 
 
+def test_inverse_reinhard_saturated_and_black_pixels():
+    """The repaired inverse must survive what inverse tone mapping is for: saturated highlights (255,255,255) and black
+    pixels in the same frame (one saturated pixel used to zero the whole frame, 1 % black pixels used to
+    push it into the 2^32 clip)."""
+    from cnn_itmo_b200 import frames
+    img = R.synthetic_images_u8(1, seed=21, size=128)
+    img[0, :16, :16] = 255
+    img[0, 100:113, 7:107] = 0                      # ~8 % black pixels
+    got = frames.inverse_reinhard(img, as_written=False, key=0.18)[0]
+    want = R.inverse_reinhard_np(img[0], as_written=False, key=0.18).astype(np.float32)
+    assert np.isfinite(got).all() and got.max() < 2.0 ** 31
+    assert np.allclose(got, want, rtol=2e-5, atol=1e-30)
+    assert (got[100:113, 7:107] == 0).all() and got[:16, :16].min() > 1.0     # black stays black, highlights expand
+    lum = got.astype(np.float64) @ np.array([0.2126, 0.7152, 0.0722])
+    nz = lum > 0
+    assert abs(np.exp(np.log(lum[nz]).mean()) - 0.18) < 1e-3                  # key of the non-black pixels
+    black = np.zeros((1, 64, 64, 3), np.uint8)
+    assert (frames.inverse_reinhard(black, as_written=False)[0] == 0).all()   # an all-black frame stays black
+
+
 def test_fused_hdr_output_equals_u8_then_inverse(model, frame):
     """out='hdr' (statistics fused into the tile scatter) == inverse Reinhard applied to the uint8 frame."""
     from cnn_itmo_b200 import frames

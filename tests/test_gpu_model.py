@@ -64,11 +64,45 @@ def test_predict_11bit_modes_psnr(pkg, calibrated_weights, images, oracle_out, p
     m.close()
 
 
-def test_predict_bf16_psnr(pkg, calibrated_weights, images, oracle_out):
-    """bf16 mode (8-bit significand). PSNR >= 45 dB holds on the network exactly as the reference builds it
-    (U_net(): he_normal kernels, identity BatchNormalization; measured ~76 dB). On the calibrated stress checkpoint
-    bf16 operand rounding alone — emulated on the CPU in oracle.forward_torch(emulate='bf16') — costs 33 dB, so
-    there the device is held to the emulation's level, not to 45 dB (use fp16 for that)."""
+def test_default_precision_is_fp16_and_meets_the_bar(pkg, calibrated_weights, images, oracle_out):
+    """The mode a user gets without asking (Model(), load_model(), the predict CLI, bench.py) is fp16 and holds the
+    north-star's PSNR >= 45 dB on the calibrated checkpoint, with no saturation."""
+    import warnings
+    m = pkg.Model(calibrated_weights, max_batch=3)
+    assert m.precision == 'fp16'
+    with warnings.catch_warnings():
+        warnings.simplefilter('error', RuntimeWarning)   # neither the load-time range check nor the device counter may fire
+        out = m.predict(R.preprocess_u8(images))
+    assert R.psnr(out, oracle_out[0][18]) >= 45.0
+    assert m.saturation_count() == 0
+    m.close()
+
+
+def test_fp16_saturation_is_counted_not_silent(pkg, calibrated_weights, images):
+    """A checkpoint whose activations leave fp16's range: the load-time check flags it and the device counter sees the
+    clamped stores (the output is still finite: the pack saturates instead of producing inf)."""
+    import warnings
+    ws = [dict(w) for w in calibrated_weights]
+    ws[3] = dict(ws[3], gamma=(ws[3]['gamma'] * 3.0e5).astype(np.float32))     # conv2d_4: |y| ~ 1e5 > 65504
+    m = pkg.Model(ws, precision='fp16', max_batch=1)
+    with warnings.catch_warnings(record=True) as rec:
+        warnings.simplefilter('always')
+        out = m.predict(R.preprocess_u8(images[:1]))
+    msgs = [str(r.message) for r in rec]
+    assert any('conv2d_4' in t and '65504' in t for t in msgs), msgs       # static range report
+    assert any('saturated' in t for t in msgs), msgs                         # device counter
+    assert np.isfinite(out).all()
+    m.close()
+    # the same weights in an fp32-range mode do not saturate
+    m = pkg.Model(ws, precision='tf32', max_batch=1)
+    m.predict(R.preprocess_u8(images[:1]))
+    assert m.saturation_count() == 0
+    m.close()
+
+
+def test_predict_bf16_psnr_on_the_network_as_built(pkg, images):
+    """bf16 (8-bit significand, opt-in): PSNR >= 45 dB on the network exactly as the reference builds it (U_net():
+    he_normal kernels, identity BatchNormalization; measured ~76 dB)."""
     init = pkg.initial_weights(seed=218)
     x = R.preprocess_u8(images[:2])
     ref_init = R.forward_torch(R.TorchWeights(init), x)
@@ -76,35 +110,37 @@ def test_predict_bf16_psnr(pkg, calibrated_weights, images, oracle_out):
     out = m.predict(x)
     assert R.psnr(out, ref_init) >= 45.0, R.psnr(out, ref_init)
     m.close()
+
+
+@pytest.mark.xfail(reason='FAILED BAR, kept visible: bf16 storage reaches ~32 dB on the calibrated stress checkpoint '
+                          '(operand rounding alone, emulated on the CPU, costs 33 dB). bf16 is opt-in; the default is '
+                          'fp16, which meets 45 dB (DESIGN.md 4.2, BASELINE.md)', strict=False)
+def test_predict_bf16_psnr_on_calibrated_checkpoint(pkg, calibrated_weights, images, oracle_out):
     m = pkg.Model(calibrated_weights, precision='bf16', max_batch=2)
     out = m.predict(R.preprocess_u8(images))
-    ref = oracle_out[0][18]
-    xq = torch.from_numpy(R.preprocess_u8(images)).to(torch.bfloat16).float().numpy()   # the float API reads bf16
-    emu = R.forward_torch(R.TorchWeights(calibrated_weights, emulate='bf16'), xq)
-    assert R.psnr(out, ref) >= R.psnr(emu, ref) - 1.5, (R.psnr(out, ref), R.psnr(emu, ref))
     m.close()
+    assert R.psnr(out, oracle_out[0][18]) >= 45.0, R.psnr(out, oracle_out[0][18])
 
 
-@pytest.mark.parametrize('prec', ['fp32', 'tf32', 'fp16', 'bf16'])
+@pytest.mark.parametrize('prec', ['fp32', 'tf32', 'fp16'])
 def test_predict_u8_is_predict_py_flow(pkg, calibrated_weights, images, prec):
-    """predict.py:59-64: u8/255 -> predict -> trunc(p*255). The fused u8-in/u8-out path must equal the float path
-    of the same precision exactly (same kernels, only the load/store differ)."""
+    """predict.py:59-64: u8/255 -> predict -> trunc(p*255). The fused u8-in/u8-out path against (a) the float path
+    of the same precision (same kernels, only the load/store differ) and (b) the oracle's predict.py flow, at the
+    north-star tolerances: +-1 LSB in the fp32 mode, PSNR >= 45 dB in the reduced-precision modes."""
     m = pkg.Model(calibrated_weights, precision=prec, max_batch=4)
     u8 = m.predict_u8(images)
     via_float = R.postprocess_u8(m.predict(R.preprocess_u8(images)))
     assert u8.dtype == np.uint8 and u8.shape == images.shape
     if prec in ('fp32', 'tf32'):
         np.testing.assert_array_equal(u8, via_float)
-    else:  # 16-bit modes: raw pixels enter exactly, normalised floats are rounded to the 16-bit operand type
-        assert R.psnr(u8 / 255.0, via_float / 255.0) >= (40.0 if prec == 'fp16' else 28.0)
+    else:  # fp16: raw pixels enter the first layer exactly, normalised floats are rounded to fp16 first
+        assert R.psnr(u8 / 255.0, via_float / 255.0) >= 45.0
     ref = R.predict_like_reference(R.TorchWeights(calibrated_weights), images, one_at_a_time=False)
     d = np.abs(u8.astype(np.int32) - ref.astype(np.int32))
     if prec == 'fp32':
         assert d.max() <= 1 and (d != 0).mean() < 0.02
-    elif prec in ('tf32', 'fp16'):
-        assert R.psnr(u8 / 255.0, ref / 255.0) >= 45.0
     else:
-        assert R.psnr(u8 / 255.0, ref / 255.0) >= 30.0
+        assert R.psnr(u8 / 255.0, ref / 255.0) >= 45.0
     m.close()
 
 
