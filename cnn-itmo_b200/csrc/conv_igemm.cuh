@@ -77,9 +77,12 @@ struct ConvParams {
   int cout_log2;       // log2(cout) when cout is a power of two, else -1
   int identity_epi;    // 1 (with no_relu): bias = 0, scale = 1, shift = 0 — the epilogue stores the accumulator as is
   int no_relu;         // 1: y = (acc + bias) * scale + shift without the ReLU (data-gradient convolutions of the training step)
-  double* stats;       // training forward (16-bit modes): per-channel sum [cout] and sum of squares [cout] of the stored
-                       // output z = ReLU(acc + bias) are accumulated here (BatchNormalization batch statistics,
-                       // model.py:196); the BN affine is then the identity and bn_scale / bn_shift are not read
+  float* stats;        // training forward (16-bit modes): BatchNormalization batch statistics (model.py:196) of the stored
+                       // output z = ReLU(acc + bias). Every CTA writes ITS per-channel sum [cout] and sum of squares [cout]
+                       // to stats[blockIdx.x][2*cout]; bn_finalize_kernel adds the CTAs' rows in index order. No atomics
+                       // anywhere on the way (each epilogue warp owns a shared-memory row, rows are added in warp order), so
+                       // the statistics — and everything downstream of them — are bit-reproducible run to run. The BN
+                       // affine is then the identity and bn_scale / bn_shift are not read
   // Narrow 3x3 layers of a loaded context (cout == BLOCK_N <= 64, plain ConvBN epilogue): the affine vectors BY VALUE
   // (the fused head's weights stay in shared memory: as constant operands they measured 4 % slower on conv2d_14). Kernel parameters sit in the constant bank, so the epilogue's FADD / FFMA take them
   // as immediate-indexed constant operands: no shared-memory broadcast reads on the L1 data pipe these layers are
@@ -342,6 +345,7 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
   float* s_scale = s_bias + kMaxCout;
   float* s_shift = s_scale + kMaxCout;
   float* s_head = s_shift + kMaxCout;                       // [3*64 weights][3 bias]
+  float* s_stat = reinterpret_cast<float*>(aux + kAuxBytes); // training forward: [kNumEpiWarps][2][cout] (see ConvParams::stats)
 
   // warp index made provably warp-uniform: with a uniform role branch and elect.sync the compiler issues
   // UTCHMMA / UBLKCP straight from uniform registers instead of a per-thread ELECT/BRA loop around every one
@@ -386,12 +390,14 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
   if (warp_idx == 2) {
     sm100::tmem_alloc(tmem_ptr_smem, tmem_cols);
   }
-  const bool with_stats = p.stats != nullptr;   // then s_scale / s_shift hold this CTA's sum / sum of squares
+  const bool with_stats = p.stats != nullptr;
   for (int i = threadIdx.x; i < p.cout; i += blockDim.x) {
     s_bias[i] = p.bias[i];
-    s_scale[i] = with_stats ? 0.f : p.bn_scale[i];
+    s_scale[i] = with_stats ? 1.f : p.bn_scale[i];
     s_shift[i] = with_stats ? 0.f : p.bn_shift[i];
   }
+  if (with_stats)
+    for (int i = threadIdx.x; i < kNumEpiWarps * 2 * p.cout; i += blockDim.x) s_stat[i] = 0.f;
   if (p.head_dtype != kHeadNone) {
     for (int i = threadIdx.x; i < 3 * 64 + 3; i += blockDim.x)
       s_head[i] = (i < 3 * 64) ? p.head_w[i] : p.head_b[i - 3 * 64];
@@ -681,8 +687,9 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
                 }
                 const float tsum = warp_transpose_sum32(sv, lane);
                 const float tsq = warp_transpose_sum32(sq, lane);
-                atomicAdd(&s_scale[co0 + lane], tsum);
-                atomicAdd(&s_shift[co0 + lane], tsq);
+                float* row = s_stat + ew * 2 * p.cout;     // this warp's own row: plain adds in program order
+                row[co0 + lane] += tsum;
+                row[p.cout + co0 + lane] += tsq;
               }
             }
             // The four lanes of a quad hold four horizontally adjacent pixels (64 B of channels each). A 4x4
@@ -778,9 +785,12 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
   sm100::tc_fence_before_sync();
   __syncthreads();
   if (with_stats) {
-    for (int i = threadIdx.x; i < p.cout; i += blockDim.x) {
-      atomicAdd(&p.stats[i], double(s_scale[i]));
-      atomicAdd(&p.stats[p.cout + i], double(s_shift[i]));
+    float* dst = p.stats + size_t(blockIdx.x) * 2 * p.cout;
+    for (int i = threadIdx.x; i < 2 * p.cout; i += blockDim.x) {
+      float acc = 0.f;
+#pragma unroll
+      for (int w = 0; w < kNumEpiWarps; ++w) acc += s_stat[w * 2 * p.cout + i];   // fixed warp order
+      dst[i] = acc;
     }
   }
   if (warp_idx == 2) {

@@ -370,7 +370,9 @@ struct ConvArgs {
   long long row_stride[2];   // source 0 / 1 viewed with these row / image strides (elements, 0 = dense)
   long long img_stride[2];
   int w_tap_stride_rows;     // rows between two taps of the packed weights (0 = the rows this launch uses)
-  double* stats;             // per-channel sum / sum of squares of the output (training forward), see ConvParams
+  float* stats;              // per-CTA per-channel sum / sum of squares of the output (training forward), see ConvParams:
+                             // [grid][2*cout] floats, grid <= number of SMs
+  int* stats_blocks;         // out: the grid size = rows of `stats` this launch wrote
   // HOST copies of bias / scale / shift [cout]: when given and the layer is narrow enough they travel as kernel
   // parameters (ConvParams::const_affine)
   const float* h_bias;
@@ -434,7 +436,8 @@ int run_conv(const ConvArgs& a, cudaStream_t stream) {
   const int b_stage = block_n * swz;
   const int kmult = k_mult(a.precision);
   const int kb_total = kmult * cin / bk;
-  const int budget = itmo::kSmemLimit - 1024 - itmo::kAuxBytes;
+  const int stats_bytes = a.stats ? itmo::kNumEpiWarps * 2 * a.cout * 4 : 0;   // per-warp statistic rows (ConvParams::stats)
+  const int budget = itmo::kSmemLimit - 1024 - itmo::kAuxBytes - stats_bytes;
   const int n_tiles = rows / block_n;
   int n_a, n_b, resident = 0;
   if (!no_resident && n_tiles == 1 && kb_total * taps * b_stage + 2 * a_stage <= budget) {
@@ -448,7 +451,7 @@ int run_conv(const ConvArgs& a, cudaStream_t stream) {
     const int left = budget - n_a * a_stage - n_b * b_stage;
     if (left >= a_stage) n_a = 3;
   }
-  const int smem_bytes = 1024 + n_a * a_stage + n_b * b_stage + itmo::kAuxBytes;
+  const int smem_bytes = 1024 + n_a * a_stage + n_b * b_stage + itmo::kAuxBytes + stats_bytes;
 
   itmo::ConvParams p;
   memset(&p, 0, sizeof(p));
@@ -520,6 +523,7 @@ int run_conv(const ConvArgs& a, cudaStream_t stream) {
   p.head_out = a.head_out;
   p.head_dtype = a.head_dtype;
   const int total_tiles = a.n * (a.h / itmo::kBlkH) * (a.w / (itmo::kBlkW * nm)) * n_tiles;
+  if (a.stats_blocks) *a.stats_blocks = std::min(total_tiles, num_sms());   // = launch_conv_t's grid
   if (a.precision == ITMO_PREC_BF16) {
     if (swz == 128) return launch_conv_n<__nv_bfloat16, 128>(block_n, p, total_tiles, smem_bytes, stream);
     return launch_conv_n<__nv_bfloat16, 64>(block_n, p, total_tiles, smem_bytes, stream);

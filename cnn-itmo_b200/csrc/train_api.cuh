@@ -84,7 +84,12 @@ struct WgradArgs {
   int conv3x3;     // 1: nine taps with 'same' padding on `a`; 0: one tap
   float* dw;
   int ld_m, ld_n, m_off, n_off;
+  float* ws;          // split-K workspace (wgrad_igemm.cuh) and its capacity in bytes
+  size_t ws_bytes;
 };
+
+constexpr int kPartialRows = 2048;   // rows of the per-block partial-sum workspaces (grids are clamped to this)
+inline size_t wgrad_ws_bytes() { return size_t(num_sms()) * 9 * 128 * 32 * 4 * 2; }   // >= grid * tg * 128 * BN * 4 for every layer
 
 template <int BN>
 int launch_wgrad_t(const itmo::WgradParams& p, int grid, int smem_bytes, cudaStream_t stream) {
@@ -148,12 +153,26 @@ int run_wgrad(const WgradArgs& a, cudaStream_t stream) {
   p.n_off = a.n_off;
   const int smem = 1024 + p.n_stages * p.stage_bytes + slack + 256;
   const int grid = tiles * p.ksplit;
-  switch (bn) {
-    case 32: return launch_wgrad_t<32>(p, grid, smem, stream);
-    case 64: return launch_wgrad_t<64>(p, grid, smem, stream);
-    case 128: return launch_wgrad_t<128>(p, grid, smem, stream);
+  if (p.ksplit > 1) {
+    const size_t need = size_t(grid) * p.tg * 128 * bn * 4;
+    if (!a.ws || a.ws_bytes < need)
+      return fail(ITMO_ERR_INVALID, "wgrad: split-K workspace of %zu bytes needed, %zu given", need, a.ws_bytes);
+    p.ws = a.ws;
   }
-  return fail(ITMO_ERR_INVALID, "wgrad: BN %d unsupported", bn);
+  int rc2;
+  switch (bn) {
+    case 32: rc2 = launch_wgrad_t<32>(p, grid, smem, stream); break;
+    case 64: rc2 = launch_wgrad_t<64>(p, grid, smem, stream); break;
+    case 128: rc2 = launch_wgrad_t<128>(p, grid, smem, stream); break;
+    default: return fail(ITMO_ERR_INVALID, "wgrad: BN %d unsupported", bn);
+  }
+  if (rc2 || p.ksplit == 1) return rc2;
+  // slices added in slice order, then ONE addition into the gradient (deterministic split-K)
+  const size_t items = size_t(tiles) * p.tg * 128 * (bn / 4);
+  itmo::wgrad_reduce_kernel<<<int(std::min<size_t>((items + 255) / 256, size_t(num_sms()) * 8)), 256, 0, stream>>>(
+      p.ws, tiles, p.ksplit, p.tg, bn, p.m_blocks, p.n_blocks, p.ca, p.dw, p.ld_m, p.ld_n, p.m_off, p.n_off);
+  ITMO_CUDA(cudaGetLastError());
+  return ITMO_OK;
 }
 
 enum TrainPhase { kPhFwdConv = 0, kPhDgrad = 1, kPhWgrad = 2, kPhOther = 3, kPhCount = 4 };
@@ -183,7 +202,10 @@ struct itmo_trainer {
   __nv_bfloat16* gp = nullptr;  // dpre
   __nv_bfloat16* gq = nullptr;  // pooled gradient
   float* bn_vec = nullptr;      // per layer: mean, invstd, scale, shift (4 x 512 each)
-  double* stats = nullptr;      // per layer 2 x 512 (forward) + 2 x 512 (backward)
+  double* stats = nullptr;      // per layer 2 x 512: totals of the BN-backward reductions
+  float* part = nullptr;        // per-block partial sums [kPartialRows][2 x 512] (BN statistics / BN backward / head)
+  float* part2 = nullptr;       // per-block partial sums of the bias gradient [kPartialRows][512]
+  float* wg_ws = nullptr;       // split-K workspace of the weight-gradient GEMM
   float* consts = nullptr;      // [512 ones][512 zeros]
   double* metrics = nullptr;    // [loss sum, hits, pixels]
   uint32_t drop_seed[ITMO_NUM_LAYERS] = {};
@@ -239,18 +261,17 @@ int tr_alloc(itmo_trainer* t, T** out, size_t count) {
 }
 
 float* bnv(itmo_trainer* t, int li, int which) { return t->bn_vec + (size_t(li) * 4 + which) * 512; }
-double* fstats(itmo_trainer* t, int li) { return t->stats + size_t(li) * 2048; }
-double* bstats(itmo_trainer* t, int li) { return t->stats + size_t(li) * 2048 + 1024; }
+double* bstats(itmo_trainer* t, int li) { return t->stats + size_t(li) * 1024; }
 
 int train_forward(itmo_trainer* t, const void* x, int x_dtype, int nb, int flags, cudaStream_t s) {
   const TrainLayout& lay = train_layout();
   const float* ones = t->consts;
   const float* zeros = t->consts + 512;
-  ITMO_CUDA(cudaMemsetAsync(t->stats, 0, sizeof(double) * 2048 * ITMO_NUM_LAYERS, s));
   static const bool fuse_stats = env_int("ITMO_TRAIN_FUSE_STATS", 1) != 0;
   for (int li = 0; li < 18; ++li) {
     const LayerDef& L = kLayers[li];
     const int hi = lay_hin(t, L), wi = lay_win(t, L), ho = lay_hout(t, L), wo = lay_wout(t, L);
+    int stat_rows = 0;   // rows of t->part the statistics of this layer occupy
     if (L.kind == kRgbConv) {
       PhaseStamp ps(t, kPhFwdConv, s, __LINE__);
       int rc = run_rgb_conv(ITMO_PREC_BF16, x, x_dtype, nb, hi, wi, t->params + lay.kernel[li], t->params + lay.bias[li],
@@ -275,7 +296,8 @@ int train_forward(itmo_trainer* t, const void* x, int x_dtype, int nb, int flags
       a.cout = L.cout;
       a.out = t->z[li];
       a.head_dtype = itmo::kHeadNone;
-      a.stats = fuse_stats ? fstats(t, li) : nullptr;   // BN batch statistics accumulated by the conv epilogue
+      a.stats = fuse_stats ? t->part : nullptr;   // BN batch statistics: per-CTA rows written by the conv epilogue
+      a.stats_blocks = &stat_rows;
       PhaseStamp ps(t, kPhFwdConv, s, __LINE__);
       int rc = run_conv(a, s);
       if (rc) return rc;
@@ -284,12 +306,13 @@ int train_forward(itmo_trainer* t, const void* x, int x_dtype, int nb, int flags
     const bool dropout = (li == 7 || li == 9) && !(flags & ITMO_TRAIN_NO_DROPOUT);
     {
       PhaseStamp ps(t, kPhOther, s, __LINE__);
-      static const int g_stats = full_wave_grid(itmo::bn_stats_kernel, size_t(1) << 30);
-      if (!(fuse_stats && L.kind != kRgbConv))
-        itmo::bn_stats_kernel<<<int(std::min<size_t>(g_stats, (npix + 63) / 64)), 256, 0, s>>>(t->z[li], npix, L.cout,
-                                                                                           fstats(t, li));
+      static const int g_stats = full_wave_grid(itmo::bn_stats_kernel, kPartialRows);
+      if (!(fuse_stats && L.kind != kRgbConv)) {
+        stat_rows = int(std::min<size_t>(g_stats, (npix + 63) / 64));
+        itmo::bn_stats_kernel<<<stat_rows, 256, 0, s>>>(t->z[li], npix, L.cout, t->part);
+      }
       itmo::bn_finalize_kernel<<<(L.cout + 127) / 128, 128, 0, s>>>(
-          fstats(t, li), L.cout, double(npix), 1e-3f, 0.99f, t->params + lay.gamma[li], t->params + lay.beta[li],
+          t->part, stat_rows, L.cout, double(npix), 1e-3f, 0.99f, t->params + lay.gamma[li], t->params + lay.beta[li],
           bnv(t, li, 0), bnv(t, li, 1), bnv(t, li, 2), bnv(t, li, 3),
           (flags & ITMO_TRAIN_FREEZE_MOVING) ? nullptr : t->bn_moving + lay.bn[li],
           (flags & ITMO_TRAIN_FREEZE_MOVING) ? nullptr : t->bn_moving + lay.bn_total + lay.bn[li]);
@@ -312,9 +335,13 @@ int train_backward(itmo_trainer* t, const void* x, int x_dtype, const float* y, 
   {
     const size_t npix = size_t(nb) * t->H * t->W;
     PhaseStamp ps(t, kPhOther, s, __LINE__);
-    itmo::head_train_kernel<<<int(std::min<size_t>(num_sms() * 4, (npix + 127) / 128)), 128, 0, s>>>(
-        t->a[17], y, (const float*)t->wfwd[18], t->params + lay.bias[18], npix, float(1.0 / loss_count), t->g[0], pred, t->metrics,
-        t->grads + lay.kernel[18], t->grads + lay.bias[18]);
+    static const int g_head = full_wave_grid(itmo::head_train_kernel, kPartialRows);
+    const int grid_h = int(std::min<size_t>(g_head, (npix + 31) / 32));
+    itmo::head_train_kernel<<<grid_h, 256, 0, s>>>(t->a[17], y, (const float*)t->wfwd[18], t->params + lay.bias[18], npix,
+                                                   float(1.0 / loss_count), t->g[0], pred, t->part);
+    itmo::head_finalize_kernel<<<1, 256, 0, s>>>(t->part, grid_h, t->grads + lay.kernel[18], t->grads + lay.bias[18],
+                                                 t->metrics);
+    t->launches += 1;
     ITMO_CUDA(cudaGetLastError());
   }
   for (int li = 17; li >= 0; --li) {
@@ -334,18 +361,19 @@ int train_backward(itmo_trainer* t, const void* x, int x_dtype, const float* y, 
     }
     {
       PhaseStamp ps(t, kPhOther, s, __LINE__);
-      static const int g_red = full_wave_grid(itmo::bn_bwd_reduce_kernel, size_t(1) << 30);
-      static const int g_app = full_wave_grid(itmo::bn_bwd_apply_kernel, size_t(1) << 30);
+      static const int g_red = full_wave_grid(itmo::bn_bwd_reduce_kernel, kPartialRows);
+      static const int g_app = full_wave_grid(itmo::bn_bwd_apply_kernel, kPartialRows);
       const int grid_r = int(std::min<size_t>(g_red, (npix + 63) / 64));
       const int grid = int(std::min<size_t>(g_app, (npix + 63) / 64));
       itmo::bn_bwd_reduce_kernel<<<grid_r, 256, 0, s>>>(dA, t->z[li], npix, L.cout, bnv(t, li, 0), bnv(t, li, 1),
-                                                      t->drop_seed[li], dropout ? 1 : 0, bstats(t, li));
+                                                      t->drop_seed[li], dropout ? 1 : 0, t->part);
+      itmo::bn_bwd_finalize_kernel<<<(L.cout + 127) / 128, 128, 0, s>>>(t->part, grid_r, L.cout, bstats(t, li),
+                                                                        t->grads + lay.gamma[li], t->grads + lay.beta[li]);
       itmo::bn_bwd_apply_kernel<<<grid, 256, 0, s>>>(dA, t->z[li], t->gp, npix, L.cout, t->params + lay.gamma[li],
                                                      bnv(t, li, 0), bnv(t, li, 1), bstats(t, li), double(npix),
-                                                     t->drop_seed[li], dropout ? 1 : 0, t->grads + lay.bias[li]);
-      itmo::bn_param_grad_kernel<<<(L.cout + 127) / 128, 128, 0, s>>>(bstats(t, li), L.cout, t->grads + lay.gamma[li],
-                                                                      t->grads + lay.beta[li]);
-      t->launches += 2;
+                                                     t->drop_seed[li], dropout ? 1 : 0, t->part2);
+      itmo::vec_partials_add_kernel<<<(L.cout + 127) / 128, 128, 0, s>>>(t->part2, grid, L.cout, t->grads + lay.bias[li]);
+      t->launches += 3;
       ITMO_CUDA(cudaGetLastError());
     }
     if (flags & ITMO_TRAIN_KEEP_GRADS)
@@ -375,6 +403,8 @@ int train_backward(itmo_trainer* t, const void* x, int x_dtype, const float* y, 
       w.dw = t->grads + lay.kernel[li];
       w.ld_m = 3;
       w.ld_n = L.cout;
+      w.ws = t->wg_ws;
+      w.ws_bytes = wgrad_ws_bytes();
       PhaseStamp ps(t, kPhWgrad, s, __LINE__);
       int rc = run_wgrad(w, s);
       if (rc) return rc;
@@ -394,6 +424,8 @@ int train_backward(itmo_trainer* t, const void* x, int x_dtype, const float* y, 
         w.ld_m = L.cin0 + L.cin1;
         w.ld_n = L.cout;
         w.m_off = src == 0 ? 0 : L.cin0;
+        w.ws = t->wg_ws;
+        w.ws_bytes = wgrad_ws_bytes();
         PhaseStamp ps(t, kPhWgrad, s, __LINE__);
         int rc = run_wgrad(w, s);
         if (rc) return rc;
@@ -415,6 +447,8 @@ int train_backward(itmo_trainer* t, const void* x, int x_dtype, const float* y, 
         w.dw = t->grads + lay.kernel[li] + size_t(ph) * 2 * L.cout * L.cin0;
         w.ld_m = 2 * L.cout;
         w.ld_n = L.cin0;
+        w.ws = t->wg_ws;
+        w.ws_bytes = wgrad_ws_bytes();
         PhaseStamp ps(t, kPhWgrad, s, __LINE__);
         int rc = run_wgrad(w, s);
         if (rc) return rc;
@@ -580,7 +614,10 @@ int itmo_trainer_create(itmo_trainer** out, int device, int micro_batch, int h, 
   if (rc == ITMO_OK) rc = tr_alloc(t, &t->gp, gmax);
   if (rc == ITMO_OK) rc = tr_alloc(t, &t->gq, qmax);
   if (rc == ITMO_OK) rc = tr_alloc(t, &t->bn_vec, size_t(ITMO_NUM_LAYERS) * 4 * 512);
-  if (rc == ITMO_OK) rc = tr_alloc(t, &t->stats, size_t(ITMO_NUM_LAYERS) * 2048);
+  if (rc == ITMO_OK) rc = tr_alloc(t, &t->stats, size_t(ITMO_NUM_LAYERS) * 1024);
+  if (rc == ITMO_OK) rc = tr_alloc(t, &t->part, size_t(kPartialRows) * 1024);
+  if (rc == ITMO_OK) rc = tr_alloc(t, &t->part2, size_t(kPartialRows) * 512);
+  if (rc == ITMO_OK) rc = tr_alloc(t, (char**)&t->wg_ws, wgrad_ws_bytes());
   if (rc == ITMO_OK) rc = tr_alloc(t, &t->consts, size_t(1024));
   if (rc == ITMO_OK) rc = tr_alloc(t, &t->metrics, size_t(4));
   if (rc == ITMO_OK) rc = tr_alloc(t, (float**)&t->wfwd[18], size_t(192));  // head weights [3][64] fp32
@@ -779,7 +816,12 @@ int itmo_wgrad3x3(const void* x, int cin, const void* g, int cout, int n, int h,
   a.dw = dw;
   a.ld_m = cin;
   a.ld_n = cout;
-  return run_wgrad(a, (cudaStream_t)stream);
+  cudaStream_t s = (cudaStream_t)stream;
+  ITMO_CUDA(cudaMallocAsync((void**)&a.ws, wgrad_ws_bytes(), s));
+  a.ws_bytes = wgrad_ws_bytes();
+  const int rc = run_wgrad(a, s);
+  cudaFreeAsync(a.ws, s);
+  return rc;
 }
 
 /* Stateless data gradient of one ConvBN layer: g [n,h,w,cout] bf16, kernel fp32 HWIO [3][3][cin][cout] (device),

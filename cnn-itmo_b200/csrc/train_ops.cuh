@@ -46,61 +46,80 @@ __device__ __forceinline__ bool drop_keep(uint32_t e, uint32_t seed) {
   return (h >> 15) & 1u;
 }
 
-// ---- BN training statistics: sum / sum of squares per channel of z = ReLU(conv + b) ------------------------------
-// grid-stride over pixels; blockDim = 256; thread -> (pixel lane, 8-channel group). stats[0..C) = sum, [C..2C) = sumsq.
-__global__ void __launch_bounds__(256, 4) bn_stats_kernel(const __nv_bfloat16* __restrict__ z, size_t npix, int C,
-                                                       double* __restrict__ stats) {
-  __shared__ float s_sum[512], s_sq[512];
-  for (int i = threadIdx.x; i < C; i += blockDim.x) s_sum[i] = s_sq[i] = 0.f;
+// ---- deterministic reductions --------------------------------------------------------------------------------------
+// No kernel of the training step uses floating-point atomics: every per-channel reduction is (1) a per-thread sum in
+// program order, (2) a block reduction in thread-index order through shared memory, (3) one row of per-block partial
+// sums in a workspace, (4) a finalize kernel that adds the rows in block-index order (in double). Grids are fixed
+// functions of the shapes, so two runs of the same step give bit-identical gradients (tests/test_gpu_train.py::
+// test_backward_is_bit_reproducible), and a gradient buffer receives exactly ONE addition per micro-batch and tensor,
+// which makes "two micro-batches on one rank" == "one micro-batch on each of two ranks + all-reduce" bit for bit.
+
+// Thread (pl, cg) of a 256-thread block holds v[8] for channels cg*8 .. cg*8+7 (groups = C/8 divides 256, lanes =
+// 256 / groups). out_row[c] = sum over pl = 0 .. lanes-1, in that order. s_red: 256 * 8 floats.
+__device__ __forceinline__ void block_reduce_channels(const float (&v)[8], float* s_red, int C, int lanes, int pl, int cg,
+                                                      float* __restrict__ out_row) {
   __syncthreads();
+#pragma unroll
+  for (int i = 0; i < 8; ++i) s_red[pl * C + cg * 8 + i] = v[i];
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    float acc = 0.f;
+    for (int l = 0; l < lanes; ++l) acc += s_red[l * C + c];
+    out_row[c] = acc;
+  }
+}
+
+// ---- BN training statistics: sum / sum of squares per channel of z = ReLU(conv + b) ------------------------------
+// grid-stride over pixels; blockDim = 256; thread -> (pixel lane, 8-channel group).
+// partials[blockIdx.x][0..C) = sum, [C..2C) = sumsq of this block's pixels.
+__global__ void __launch_bounds__(256, 4) bn_stats_kernel(const __nv_bfloat16* __restrict__ z, size_t npix, int C,
+                                                       float* __restrict__ partials) {
+  __shared__ float s_red[256 * 8];
   const int groups = C >> 3;
   const int cg = threadIdx.x % groups;
   const int lanes = blockDim.x / groups;   // pixels per block iteration (C <= 512 -> groups <= 64 -> lanes >= 4)
   const int pl = threadIdx.x / groups;
   float a[8] = {}, q[8] = {};
-  if (pl < lanes) {
-    const size_t stride = size_t(gridDim.x) * lanes;
-    for (size_t pix = size_t(blockIdx.x) * lanes + pl; pix < npix; pix += 4 * stride) {
-      Bf8 v[4];   // four independent 16-byte loads in flight per thread
+  const size_t stride = size_t(gridDim.x) * lanes;
+  for (size_t pix = size_t(blockIdx.x) * lanes + pl; pix < npix; pix += 4 * stride) {
+    Bf8 v[4];   // four independent 16-byte loads in flight per thread
 #pragma unroll
-      for (int u = 0; u < 4; ++u)
-        if (pix + u * stride < npix) v[u] = ld8(z + (pix + u * stride) * C + cg * 8);
+    for (int u = 0; u < 4; ++u)
+      if (pix + u * stride < npix) v[u] = ld8(z + (pix + u * stride) * C + cg * 8);
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        if (pix + u * stride >= npix) break;
-        float f[8];
-        v[u].get(f);
+    for (int u = 0; u < 4; ++u) {
+      if (pix + u * stride >= npix) break;
+      float f[8];
+      v[u].get(f);
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          a[i] += f[i];
-          q[i] = fmaf(f[i], f[i], q[i]);
-        }
+      for (int i = 0; i < 8; ++i) {
+        a[i] += f[i];
+        q[i] = fmaf(f[i], f[i], q[i]);
       }
     }
-#pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      atomicAdd(&s_sum[cg * 8 + i], a[i]);
-      atomicAdd(&s_sq[cg * 8 + i], q[i]);
-    }
   }
-  __syncthreads();
-  for (int i = threadIdx.x; i < C; i += blockDim.x) {
-    atomicAdd(&stats[i], double(s_sum[i]));
-    atomicAdd(&stats[C + i], double(s_sq[i]));
-  }
+  float* row = partials + size_t(blockIdx.x) * 2 * C;
+  block_reduce_channels(a, s_red, C, lanes, pl, cg, row);
+  block_reduce_channels(q, s_red, C, lanes, pl, cg, row + C);
 }
 
 // mean / biased variance -> the affine bn_apply uses, the values backward needs, and the moving statistics
 // (Keras BatchNormalization: momentum 0.99; the moving variance takes the sample variance var * M / (M - (1 + eps))).
-__global__ void bn_finalize_kernel(const double* __restrict__ stats, int C, double M, float eps, float momentum,
-                                   const float* __restrict__ gamma, const float* __restrict__ beta,
+// partials: [nblocks][2*C] per-block sums (bn_stats_kernel or the conv epilogue), added here in block order.
+__global__ void bn_finalize_kernel(const float* __restrict__ partials, int nblocks, int C, double M, float eps,
+                                   float momentum, const float* __restrict__ gamma, const float* __restrict__ beta,
                                    float* __restrict__ mean, float* __restrict__ invstd, float* __restrict__ scale,
                                    float* __restrict__ shift, float* __restrict__ moving_mean,
                                    float* __restrict__ moving_var) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= C) return;
-  const double m = stats[i] / M;
-  double v = stats[C + i] / M - m * m;
+  double sum = 0.0, sq = 0.0;
+  for (int b = 0; b < nblocks; ++b) {
+    sum += double(partials[size_t(b) * 2 * C + i]);
+    sq += double(partials[size_t(b) * 2 * C + C + i]);
+  }
+  const double m = sum / M;
+  double v = sq / M - m * m;
   if (v < 0) v = 0;
   const float is = float(1.0 / sqrt(v + double(eps)));
   mean[i] = float(m);
@@ -197,275 +216,275 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const __nv_bfloat16* __re
 }
 
 // ---- head: Conv2D(3, 1, sigmoid) (model.py:276) + mse (model.py:281), forward and backward in one pass -----------------
-// One warp = 32 consecutive pixels. acc[0] += sum (p-y)^2, acc[1] += #pixels with argmax_k p == argmax_k y (Keras
-// 'accuracy' resolves to categorical_accuracy for this output). d_a = (2/count) (p-y) p (1-p) W; dW[k][c], db[k] accumulate.
-// y: target in [0,1], float32 [P,3]. pred (optional): float32 [P,3].
-__global__ void __launch_bounds__(128) head_train_kernel(const __nv_bfloat16* __restrict__ a, const float* __restrict__ y,
+// A warp covers 4 pixels x 8 channel groups per iteration: lane = (pixel slot lane >> 3, channel group lane & 7), so every
+// load / store instruction of the 64-channel tensors moves 512 contiguous bytes per warp and a thread keeps only ITS 8
+// channels: 24 head weights + 24 weight-gradient accumulators in registers (the first version kept all 64 channels of a
+// pixel per thread: 255 registers, 12 % occupancy, half-used sectors, 22 % of DRAM peak). The three pre-activations are
+// reduced over the 8 lanes of a pixel with xor shuffles. Per block: partials[blockIdx.x][0..191] = dW[k][c] (index
+// k*64 + c), [192..194] = db, [195] = sum (p-y)^2, [196] = #pixels with argmax_k p == argmax_k y (Keras 'accuracy'
+// resolves to categorical_accuracy for this output); head_finalize_kernel adds the blocks in index order.
+// d_a = (2/count) (p-y) p (1-p) W. y: target in [0,1], float32 [P,3]. pred (optional): float32 [P,3].
+constexpr int kHeadPartials = 200;
+__global__ void __launch_bounds__(256) head_train_kernel(const __nv_bfloat16* __restrict__ a, const float* __restrict__ y,
                                                          const float* __restrict__ wh,   // [3][64]
                                                          const float* __restrict__ bh, size_t npix, float inv_count,
                                                          __nv_bfloat16* __restrict__ d_a, float* __restrict__ pred,
-                                                         double* __restrict__ acc, float* __restrict__ dwh,
-                                                         float* __restrict__ dbh) {
-  __shared__ __align__(16) float s_w[3 * 64 + 4];
-  __shared__ float s_a[4][32][65];
-  __shared__ float s_dl[4][32][3];
-  __shared__ float s_dw[3 * 64 + 3];
-  for (int i = threadIdx.x; i < 195; i += blockDim.x) {
-    s_w[i] = i < 192 ? wh[i] : bh[i - 192];
-    s_dw[i] = 0.f;
-  }
-  __syncthreads();
+                                                         float* __restrict__ partials) {
+  __shared__ float s_w[8][8][27];    // [warp][channel group][24 dW + 3 db]
+  __shared__ float s_m[8][2];        // [warp][loss, hits]
   const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  float g[6] = {};      // this lane's 6 of the 192 weight gradients: index j*32 + lane -> (k = idx / 64, c = idx % 64)
-  float gb = 0.f;       // lanes 0..2: bias gradient
+  const int cg = lane & 7, ps = lane >> 3;
+  float w[3][8], bk[3];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    bk[k] = bh[k];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) w[k][i] = wh[k * 64 + cg * 8 + i];
+  }
+  float g[3][8] = {}, gb[3] = {};
   float loss = 0.f, hits = 0.f;
-  const size_t nwarps = size_t(gridDim.x) * 4;
-  for (size_t base = (size_t(blockIdx.x) * 4 + wid) * 32; base < npix; base += nwarps * 32) {
-    const size_t pix = base + lane;
+  const size_t per_iter = size_t(gridDim.x) * 32;   // 8 warps x 4 pixels per block
+  const size_t n_iter = (npix + per_iter - 1) / per_iter;
+  for (size_t it = 0; it < n_iter; ++it) {
+    const size_t pix = it * per_iter + size_t(blockIdx.x) * 32 + wid * 4 + ps;
     const bool ok = pix < npix;
-    float av[64];
-    if (ok) {
+    float av[8];
+    if (ok) ld8(a + pix * 64 + cg * 8).get(av);
+    else {
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        float f[8];
-        ld8(a + pix * 64 + j * 8).get(f);
-#pragma unroll
-        for (int i = 0; i < 8; ++i) av[j * 8 + i] = f[i];
-      }
-    } else {
-#pragma unroll
-      for (int i = 0; i < 64; ++i) av[i] = 0.f;
+      for (int i = 0; i < 8; ++i) av[i] = 0.f;
     }
-    float z0 = s_w[192], z1 = s_w[193], z2 = s_w[194];
+    float z[3];
 #pragma unroll
-    for (int c = 0; c < 64; c += 4) {   // 128-bit broadcast reads of the head weights; same summation order as scalar
-      const float4 w0 = *reinterpret_cast<const float4*>(s_w + c);
-      const float4 w1 = *reinterpret_cast<const float4*>(s_w + 64 + c);
-      const float4 w2 = *reinterpret_cast<const float4*>(s_w + 128 + c);
-      z0 = fmaf(av[c + 3], w0.w, fmaf(av[c + 2], w0.z, fmaf(av[c + 1], w0.y, fmaf(av[c], w0.x, z0))));
-      z1 = fmaf(av[c + 3], w1.w, fmaf(av[c + 2], w1.z, fmaf(av[c + 1], w1.y, fmaf(av[c], w1.x, z1))));
-      z2 = fmaf(av[c + 3], w2.w, fmaf(av[c + 2], w2.z, fmaf(av[c + 1], w2.y, fmaf(av[c], w2.x, z2))));
+    for (int k = 0; k < 3; ++k) {
+      float t = 0.f;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) t = fmaf(av[i], w[k][i], t);
+      t += __shfl_xor_sync(0xFFFFFFFFu, t, 1);
+      t += __shfl_xor_sync(0xFFFFFFFFu, t, 2);
+      t += __shfl_xor_sync(0xFFFFFFFFu, t, 4);
+      z[k] = t + bk[k];
     }
-    const float p0 = 1.f / (1.f + expf(-z0)), p1 = 1.f / (1.f + expf(-z1)), p2 = 1.f / (1.f + expf(-z2));
-    float dl0 = 0.f, dl1 = 0.f, dl2 = 0.f;
+    const float p0 = 1.f / (1.f + expf(-z[0])), p1 = 1.f / (1.f + expf(-z[1])), p2 = 1.f / (1.f + expf(-z[2]));
     if (ok) {
       const float y0 = y[pix * 3], y1 = y[pix * 3 + 1], y2 = y[pix * 3 + 2];
       const float e0 = p0 - y0, e1 = p1 - y1, e2 = p2 - y2;
-      loss += e0 * e0 + e1 * e1 + e2 * e2;
-      const int ap = p0 >= p1 ? (p0 >= p2 ? 0 : 2) : (p1 >= p2 ? 1 : 2);   // first maximum, like argmax
-      const int ay = y0 >= y1 ? (y0 >= y2 ? 0 : 2) : (y1 >= y2 ? 1 : 2);
-      hits += ap == ay ? 1.f : 0.f;
-      dl0 = 2.f * inv_count * e0 * p0 * (1.f - p0);
-      dl1 = 2.f * inv_count * e1 * p1 * (1.f - p1);
-      dl2 = 2.f * inv_count * e2 * p2 * (1.f - p2);
-      if (pred) {
-        pred[pix * 3] = p0;
-        pred[pix * 3 + 1] = p1;
-        pred[pix * 3 + 2] = p2;
+      const float dl0 = 2.f * inv_count * e0 * p0 * (1.f - p0);
+      const float dl1 = 2.f * inv_count * e1 * p1 * (1.f - p1);
+      const float dl2 = 2.f * inv_count * e2 * p2 * (1.f - p2);
+      if (cg == 0) {
+        loss += e0 * e0 + e1 * e1 + e2 * e2;
+        const int ap = p0 >= p1 ? (p0 >= p2 ? 0 : 2) : (p1 >= p2 ? 1 : 2);   // first maximum, like argmax
+        const int ay = y0 >= y1 ? (y0 >= y2 ? 0 : 2) : (y1 >= y2 ? 1 : 2);
+        hits += ap == ay ? 1.f : 0.f;
+        gb[0] += dl0;
+        gb[1] += dl1;
+        gb[2] += dl2;
       }
+      if (pred && cg < 3) pred[pix * 3 + cg] = cg == 0 ? p0 : cg == 1 ? p1 : p2;
+      float f[8];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        float f[8];
-#pragma unroll
-        for (int i = 0; i < 8; i += 4) {
-          const int c = j * 8 + i;
-          const float4 w0 = *reinterpret_cast<const float4*>(s_w + c);
-          const float4 w1 = *reinterpret_cast<const float4*>(s_w + 64 + c);
-          const float4 w2 = *reinterpret_cast<const float4*>(s_w + 128 + c);
-          f[i] = dl0 * w0.x + dl1 * w1.x + dl2 * w2.x;
-          f[i + 1] = dl0 * w0.y + dl1 * w1.y + dl2 * w2.y;
-          f[i + 2] = dl0 * w0.z + dl1 * w1.z + dl2 * w2.z;
-          f[i + 3] = dl0 * w0.w + dl1 * w1.w + dl2 * w2.w;
-        }
-        Bf8 o;
-        o.set(f);
-        st8(d_a + pix * 64 + j * 8, o);
+      for (int i = 0; i < 8; ++i) {
+        f[i] = dl0 * w[0][i] + dl1 * w[1][i] + dl2 * w[2][i];
+        g[0][i] = fmaf(dl0, av[i], g[0][i]);
+        g[1][i] = fmaf(dl1, av[i], g[1][i]);
+        g[2][i] = fmaf(dl2, av[i], g[2][i]);
       }
+      Bf8 o;
+      o.set(f);
+      st8(d_a + pix * 64 + cg * 8, o);
     }
-    // weight gradient: stage this warp's 32 pixels, then every lane reduces its 6 (k, c) pairs over them
+  }
+  // the 4 pixel slots of a warp (lanes cg, cg+8, cg+16, cg+24): fixed xor tree
 #pragma unroll
-    for (int c = 0; c < 64; ++c) s_a[wid][lane][c] = av[c];
-    s_dl[wid][lane][0] = dl0;
-    s_dl[wid][lane][1] = dl1;
-    s_dl[wid][lane][2] = dl2;
-    __syncwarp();
-    {
-      // g[j] belongs to index j*32 + lane -> k = j >> 1, c = (j & 1) * 32 + lane: per staged pixel two activation
-      // reads and three (broadcast) dl reads feed all six products, in the same q order as a per-output loop
-      float sg[6] = {};
-      for (int q = 0; q < 32; ++q) {
-        const float a_lo = s_a[wid][q][lane], a_hi = s_a[wid][q][32 + lane];
-        const float d0 = s_dl[wid][q][0], d1 = s_dl[wid][q][1], d2 = s_dl[wid][q][2];
-        sg[0] = fmaf(d0, a_lo, sg[0]);
-        sg[1] = fmaf(d0, a_hi, sg[1]);
-        sg[2] = fmaf(d1, a_lo, sg[2]);
-        sg[3] = fmaf(d1, a_hi, sg[3]);
-        sg[4] = fmaf(d2, a_lo, sg[4]);
-        sg[5] = fmaf(d2, a_hi, sg[5]);
-      }
+  for (int k = 0; k < 3; ++k) {
 #pragma unroll
-      for (int j = 0; j < 6; ++j) g[j] += sg[j];
+    for (int i = 0; i < 8; ++i) {
+      g[k][i] += __shfl_xor_sync(0xFFFFFFFFu, g[k][i], 8);
+      g[k][i] += __shfl_xor_sync(0xFFFFFFFFu, g[k][i], 16);
     }
-    if (lane < 3) {
-      float s = 0.f;
-      for (int q = 0; q < 32; ++q) s += s_dl[wid][q][lane];
-      gb += s;
-    }
-    __syncwarp();
+    gb[k] += __shfl_xor_sync(0xFFFFFFFFu, gb[k], 8);
+    gb[k] += __shfl_xor_sync(0xFFFFFFFFu, gb[k], 16);
   }
 #pragma unroll
-  for (int j = 0; j < 6; ++j) atomicAdd(&s_dw[j * 32 + lane], g[j]);
-  if (lane < 3) atomicAdd(&s_dw[192 + lane], gb);
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
+  for (int o = 8; o <= 16; o <<= 1) {
     loss += __shfl_xor_sync(0xFFFFFFFFu, loss, o);
     hits += __shfl_xor_sync(0xFFFFFFFFu, hits, o);
   }
-  if (lane == 0) {
-    atomicAdd(&acc[0], double(loss));
-    atomicAdd(&acc[1], double(hits));
+  if (ps == 0) {
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) s_w[wid][cg][k * 8 + i] = g[k][i];
+      s_w[wid][cg][24 + k] = gb[k];
+    }
+    if (cg == 0) {
+      s_m[wid][0] = loss;
+      s_m[wid][1] = hits;
+    }
   }
   __syncthreads();
-  for (int i = threadIdx.x; i < 195; i += blockDim.x) {
-    if (i < 192) atomicAdd(&dwh[(i & 63) * 3 + (i >> 6)], s_dw[i]);   // Keras head kernel layout [64][3]
-    else atomicAdd(&dbh[i - 192], s_dw[i]);
+  float* row = partials + size_t(blockIdx.x) * kHeadPartials;
+  const int t = threadIdx.x;
+  if (t < 197) {
+    float acc = 0.f;
+    if (t < 192) {
+      const int k = t >> 6, c = t & 63;
+      for (int wv = 0; wv < 8; ++wv) acc += s_w[wv][c >> 3][k * 8 + (c & 7)];
+    } else if (t < 195) {
+      for (int wv = 0; wv < 8; ++wv) acc += s_w[wv][0][24 + (t - 192)];
+    } else {
+      for (int wv = 0; wv < 8; ++wv) acc += s_m[wv][t - 195];
+    }
+    row[t] = acc;
   }
 }
 
+// adds the blocks' rows in index order: head kernel / bias gradients (Keras layout [64][3]) and the loss / accuracy sums
+__global__ void head_finalize_kernel(const float* __restrict__ partials, int nblocks, float* __restrict__ dwh,
+                                     float* __restrict__ dbh, double* __restrict__ acc) {
+  const int t = threadIdx.x;
+  if (t >= 197) return;
+  double s = 0.0;
+  for (int b = 0; b < nblocks; ++b) s += double(partials[size_t(b) * kHeadPartials + t]);
+  if (t < 192) dwh[(t & 63) * 3 + (t >> 6)] += float(s);
+  else if (t < 195) dbh[t - 192] += float(s);
+  else acc[t - 195] += s;
+}
+
 // ---- BN backward, pass 1: per-channel sums of dA' and dA' * zhat (dA' = dA through the dropout mask) ---------------
-// sums[0..C) = sum dA', sums[C..2C) = sum dA' * (z - mean) * invstd
+// partials[blockIdx.x][0..C) = sum dA', [C..2C) = sum dA' * (z - mean) * invstd over this block's pixels
 __global__ void __launch_bounds__(256, 4) bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dA,
                                                             const __nv_bfloat16* __restrict__ z, size_t npix, int C,
                                                             const float* __restrict__ mean, const float* __restrict__ invstd,
-                                                            uint32_t drop_seed, int dropout, double* __restrict__ sums) {
-  __shared__ float s_a[512], s_b[512];
-  for (int i = threadIdx.x; i < C; i += blockDim.x) s_a[i] = s_b[i] = 0.f;
-  __syncthreads();
+                                                            uint32_t drop_seed, int dropout, float* __restrict__ partials) {
+  __shared__ float s_red[256 * 8];
   const int groups = C >> 3;
   const int cg = threadIdx.x % groups;
   const int lanes = blockDim.x / groups;
   const int pl = threadIdx.x / groups;
-  if (pl < lanes) {
-    float mu[8], is[8], sa[8] = {}, sb[8] = {};
+  float mu[8], is[8], sa[8] = {}, sb[8] = {};
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      mu[i] = mean[cg * 8 + i];
-      is[i] = invstd[cg * 8 + i];
-    }
-    const size_t stride = size_t(gridDim.x) * lanes;
-    for (size_t pix = size_t(blockIdx.x) * lanes + pl; pix < npix; pix += 2 * stride) {
-      Bf8 vd[2], vz[2];
+  for (int i = 0; i < 8; ++i) {
+    mu[i] = mean[cg * 8 + i];
+    is[i] = invstd[cg * 8 + i];
+  }
+  const size_t stride = size_t(gridDim.x) * lanes;
+  for (size_t pix = size_t(blockIdx.x) * lanes + pl; pix < npix; pix += 2 * stride) {
+    Bf8 vd[2], vz[2];
 #pragma unroll
-      for (int u = 0; u < 2; ++u)
-        if (pix + u * stride < npix) {
-          const size_t e0 = (pix + u * stride) * C + cg * 8;
-          vd[u] = ld8(dA + e0);
-          vz[u] = ld8(z + e0);
-        }
-#pragma unroll
-      for (int u = 0; u < 2; ++u) {
-        if (pix + u * stride >= npix) break;
+    for (int u = 0; u < 2; ++u)
+      if (pix + u * stride < npix) {
         const size_t e0 = (pix + u * stride) * C + cg * 8;
-        float d[8], f[8];
-        vd[u].get(d);
-        vz[u].get(f);
+        vd[u] = ld8(dA + e0);
+        vz[u] = ld8(z + e0);
+      }
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          float dv = d[i];
-          if (dropout) dv = drop_keep(uint32_t(e0 + i), drop_seed) ? 2.f * dv : 0.f;
-          sa[i] += dv;
-          sb[i] = fmaf(dv, (f[i] - mu[i]) * is[i], sb[i]);
-        }
+    for (int u = 0; u < 2; ++u) {
+      if (pix + u * stride >= npix) break;
+      const size_t e0 = (pix + u * stride) * C + cg * 8;
+      float d[8], f[8];
+      vd[u].get(d);
+      vz[u].get(f);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        float dv = d[i];
+        if (dropout) dv = drop_keep(uint32_t(e0 + i), drop_seed) ? 2.f * dv : 0.f;
+        sa[i] += dv;
+        sb[i] = fmaf(dv, (f[i] - mu[i]) * is[i], sb[i]);
       }
     }
-#pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      atomicAdd(&s_a[cg * 8 + i], sa[i]);
-      atomicAdd(&s_b[cg * 8 + i], sb[i]);
-    }
   }
-  __syncthreads();
-  for (int i = threadIdx.x; i < C; i += blockDim.x) {
-    atomicAdd(&sums[i], double(s_a[i]));
-    atomicAdd(&sums[C + i], double(s_b[i]));
+  float* row = partials + size_t(blockIdx.x) * 2 * C;
+  block_reduce_channels(sa, s_red, C, lanes, pl, cg, row);
+  block_reduce_channels(sb, s_red, C, lanes, pl, cg, row + C);
+}
+
+// totals of pass 1 in block order -> sums[0..2C) (double, read by pass 2) and the BN parameter gradients:
+// dgamma += sum dA' zhat, dbeta += sum dA'  (ONE addition per micro-batch into the gradient buffer)
+__global__ void bn_bwd_finalize_kernel(const float* __restrict__ partials, int nblocks, int C, double* __restrict__ sums,
+                                       float* __restrict__ dgamma, float* __restrict__ dbeta) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= C) return;
+  double s0 = 0.0, s1 = 0.0;
+  for (int b = 0; b < nblocks; ++b) {
+    s0 += double(partials[size_t(b) * 2 * C + i]);
+    s1 += double(partials[size_t(b) * 2 * C + C + i]);
   }
+  sums[i] = s0;
+  sums[C + i] = s1;
+  dbeta[i] += float(s0);
+  dgamma[i] += float(s1);
 }
 
 // ---- BN backward, pass 2 (+ ReLU backward): dpre = [z > 0] * gamma*invstd * (dA' - mean(dA') - zhat * mean(dA' zhat)) --
-// also accumulates the bias gradient sum(dpre) per channel (of the bf16-rounded dpre the GEMMs consume).
+// also writes this block's share of the bias gradient sum(dpre) per channel (of the bf16-rounded dpre the GEMMs consume)
+// to db_partials[blockIdx.x][C]; vec_partials_add_kernel adds the rows to the gradient buffer in block order.
 __global__ void __launch_bounds__(256, 3) bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dA,
                                                            const __nv_bfloat16* __restrict__ z,
                                                            __nv_bfloat16* __restrict__ dpre, size_t npix, int C,
                                                            const float* __restrict__ gamma, const float* __restrict__ mean,
                                                            const float* __restrict__ invstd, const double* __restrict__ sums,
                                                            double M, uint32_t drop_seed, int dropout,
-                                                           float* __restrict__ dbias) {
-  __shared__ float s_db[512];
-  for (int i = threadIdx.x; i < C; i += blockDim.x) s_db[i] = 0.f;
-  __syncthreads();
+                                                           float* __restrict__ db_partials) {
+  __shared__ float s_red[256 * 8];
   const int groups = C >> 3;
   const int cg = threadIdx.x % groups;
   const int lanes = blockDim.x / groups;
   const int pl = threadIdx.x / groups;
-  if (pl < lanes) {
-    // dz = gs * (dA' - m1 - (z - mu) * is * m2) = gs * dA' + kz * z + k0   with kz = -gs*is*m2, k0 = gs * (mu*is*m2 - m1)
-    float gs[8], kz[8], k0[8], db[8] = {};
+  // dz = gs * (dA' - m1 - (z - mu) * is * m2) = gs * dA' + kz * z + k0   with kz = -gs*is*m2, k0 = gs * (mu*is*m2 - m1)
+  float gs[8], kz[8], k0[8], db[8] = {};
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const int c = cg * 8 + i;
-      const float mu = mean[c], is = invstd[c];
-      const float m1 = float(sums[c] / M), m2 = float(sums[C + c] / M);
-      gs[i] = gamma[c] * is;
-      kz[i] = -gs[i] * is * m2;
-      k0[i] = gs[i] * (mu * is * m2 - m1);
-    }
-    const size_t stride = size_t(gridDim.x) * lanes;
-    for (size_t pix = size_t(blockIdx.x) * lanes + pl; pix < npix; pix += 2 * stride) {
-      Bf8 vd[2], vz[2];
-#pragma unroll
-      for (int u = 0; u < 2; ++u)
-        if (pix + u * stride < npix) {
-          const size_t e0 = (pix + u * stride) * C + cg * 8;
-          vd[u] = ld8(dA + e0);
-          vz[u] = ld8(z + e0);
-        }
-#pragma unroll
-      for (int u = 0; u < 2; ++u) {
-        if (pix + u * stride >= npix) break;
-        const size_t e0 = (pix + u * stride) * C + cg * 8;
-        float d[8], f[8], o[8];
-        vd[u].get(d);
-        vz[u].get(f);
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          float dv = d[i];
-          if (dropout) dv = drop_keep(uint32_t(e0 + i), drop_seed) ? 2.f * dv : 0.f;
-          const float dz = fmaf(gs[i], dv, fmaf(kz[i], f[i], k0[i]));
-          o[i] = f[i] > 0.f ? dz : 0.f;
-        }
-        Bf8 ov;
-        ov.set(o);
-        st8(dpre + e0, ov);
-        ov.get(o);
-#pragma unroll
-        for (int i = 0; i < 8; ++i) db[i] += o[i];
-      }
-    }
-#pragma unroll
-    for (int i = 0; i < 8; ++i) atomicAdd(&s_db[cg * 8 + i], db[i]);
+  for (int i = 0; i < 8; ++i) {
+    const int c = cg * 8 + i;
+    const float mu = mean[c], is = invstd[c];
+    const float m1 = float(sums[c] / M), m2 = float(sums[C + c] / M);
+    gs[i] = gamma[c] * is;
+    kz[i] = -gs[i] * is * m2;
+    k0[i] = gs[i] * (mu * is * m2 - m1);
   }
-  __syncthreads();
-  for (int i = threadIdx.x; i < C; i += blockDim.x) atomicAdd(&dbias[i], s_db[i]);
+  const size_t stride = size_t(gridDim.x) * lanes;
+  for (size_t pix = size_t(blockIdx.x) * lanes + pl; pix < npix; pix += 2 * stride) {
+    Bf8 vd[2], vz[2];
+#pragma unroll
+    for (int u = 0; u < 2; ++u)
+      if (pix + u * stride < npix) {
+        const size_t e0 = (pix + u * stride) * C + cg * 8;
+        vd[u] = ld8(dA + e0);
+        vz[u] = ld8(z + e0);
+      }
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      if (pix + u * stride >= npix) break;
+      const size_t e0 = (pix + u * stride) * C + cg * 8;
+      float d[8], f[8], o[8];
+      vd[u].get(d);
+      vz[u].get(f);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        float dv = d[i];
+        if (dropout) dv = drop_keep(uint32_t(e0 + i), drop_seed) ? 2.f * dv : 0.f;
+        const float dz = fmaf(gs[i], dv, fmaf(kz[i], f[i], k0[i]));
+        o[i] = f[i] > 0.f ? dz : 0.f;
+      }
+      Bf8 ov;
+      ov.set(o);
+      st8(dpre + e0, ov);
+      ov.get(o);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) db[i] += o[i];
+    }
+  }
+  block_reduce_channels(db, s_red, C, lanes, pl, cg, db_partials + size_t(blockIdx.x) * C);
 }
 
-// dgamma += sum dA' zhat, dbeta += sum dA'
-__global__ void bn_param_grad_kernel(const double* __restrict__ sums, int C, float* __restrict__ dgamma,
-                                     float* __restrict__ dbeta) {
+// dst[i] += sum over blocks (in index order) of partials[b][i]
+__global__ void vec_partials_add_kernel(const float* __restrict__ partials, int nblocks, int n, float* __restrict__ dst) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < C) {
-    dbeta[i] += float(sums[i]);
-    dgamma[i] += float(sums[C + i]);
-  }
+  if (i >= n) return;
+  double s = 0.0;
+  for (int b = 0; b < nblocks; ++b) s += double(partials[size_t(b) * n + i]);
+  dst[i] += float(s);
 }
 
 // ---- MaxPool backward + skip add: dA = dSkip + route(dPooled -> first maximum of the 2x2 window of a) -----------------

@@ -17,9 +17,12 @@
 //   K block              : 128 pixels (16 rows x 8 columns) = 8 MMAs of K = 16 (two pixel rows each).
 //
 // A CTA owns one output tile (128 A-channels x BN B-channels x the TG taps of one kernel row: TG accumulators of
-// BN fp32 columns in TMEM) and one slice of the pixel range (split-K over CTAs so that tiles x slices ~ SM count);
-// it adds its partial tile into the fp32 gradient tensor with red.global.add. The gradient buffer therefore
-// accumulates across launches (micro-batches) until the optimizer step zeroes it.
+// BN fp32 columns in TMEM) and one slice of the pixel range (split-K over CTAs so that tiles x slices ~ SM count).
+// Deterministic split-K: with more than one slice every CTA writes its partial tile to a workspace
+// ws[tile][slice][tap][row][col] and wgrad_reduce_kernel adds the slices IN SLICE ORDER, then adds the total to the
+// fp32 gradient tensor once; with one slice the CTA owns its part of the gradient and adds to it directly. No atomics:
+// two runs give bit-identical gradients, and the gradient buffer receives one addition per launch (micro-batch), so
+// it accumulates across micro-batches until the optimizer step zeroes it.
 #pragma once
 #include <cuda_bf16.h>
 #include "sm100_ptx.cuh"
@@ -49,6 +52,7 @@ struct WgradParams {
   int ksplit;        // pixel-range slices
   int ca;            // valid A channels (rows written)
   int m64;           // 1: UMMA M = 64 (ca <= 64): half the A operand bytes per MMA at the same MMA duration
+  float* ws;         // split-K workspace [tiles][ksplit][tg][128][BN] fp32 (ksplit > 1), else null
   float* dw;         // [n_groups*tg][ld_m][ld_n] fp32, accumulated
   int ld_m, ld_n;    // rows / columns of one tap's matrix
   int m_off, n_off;  // where this launch's (A-channel, B-channel) block starts inside it
@@ -189,9 +193,29 @@ __global__ void __launch_bounds__(kWgThreads, 1) wgrad_igemm_kernel(const __grid
         sm100::tmem_ld_32x32b_x32(taddr + uint32_t(t * BN + chunk * 32), v);
         sm100::tmem_ld_wait();
         if (row < p.ca) {
-          float* dst = p.dw + (size_t(tap) * p.ld_m + p.m_off + row) * p.ld_n + p.n_off + nb * BN + chunk * 32;
+          if (p.ws != nullptr) {
+            // partial tile of this slice; row index inside the 128-row tile
+            const int rl = row - mb * 128;
+            float4* dst = reinterpret_cast<float4*>(
+                p.ws + ((size_t(blockIdx.x) * p.tg + t) * 128 + rl) * BN + chunk * 32);   // blockIdx.x = tile * ksplit + split
 #pragma unroll
-          for (int i = 0; i < 32; ++i) atomicAdd(dst + i, __uint_as_float(v[i]));
+            for (int i = 0; i < 8; ++i)
+              dst[i] = make_float4(__uint_as_float(v[4 * i]), __uint_as_float(v[4 * i + 1]), __uint_as_float(v[4 * i + 2]),
+                                   __uint_as_float(v[4 * i + 3]));
+          } else {
+            // single slice: this CTA is the only writer of its part of the gradient
+            float4* dst = reinterpret_cast<float4*>(p.dw + (size_t(tap) * p.ld_m + p.m_off + row) * p.ld_n + p.n_off +
+                                                    nb * BN + chunk * 32);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              float4 o = dst[i];
+              o.x += __uint_as_float(v[4 * i]);
+              o.y += __uint_as_float(v[4 * i + 1]);
+              o.z += __uint_as_float(v[4 * i + 2]);
+              o.w += __uint_as_float(v[4 * i + 3]);
+              dst[i] = o;
+            }
+          }
         }
       }
     }
@@ -201,6 +225,44 @@ __global__ void __launch_bounds__(kWgThreads, 1) wgrad_igemm_kernel(const __grid
   if (warp_idx == 1) {
     sm100::tc_fence_after_sync();
     sm100::tmem_dealloc(tmem_base, tmem_cols);
+  }
+}
+
+// Second half of the deterministic split-K: dw += sum over slices (in slice order) of the partial tiles.
+// One thread = 4 consecutive columns of one (tile, tap, row).
+__global__ void __launch_bounds__(256) wgrad_reduce_kernel(const float* __restrict__ ws, int n_tiles, int ksplit, int tg,
+                                                           int bn, int m_blocks, int n_blocks, int ca, float* __restrict__ dw,
+                                                           int ld_m, int ld_n, int m_off, int n_off) {
+  const int c4 = bn >> 2;
+  const size_t total = size_t(n_tiles) * tg * 128 * c4;
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < total; i += size_t(gridDim.x) * blockDim.x) {
+    const int col = int(i % c4) * 4;
+    size_t r = i / c4;
+    const int rl = int(r % 128);
+    r /= 128;
+    const int t = int(r % tg);
+    const int tile = int(r / tg);
+    const int nb = tile % n_blocks;
+    const int mb = (tile / n_blocks) % m_blocks;
+    const int g = tile / (n_blocks * m_blocks);
+    const int row = mb * 128 + rl;
+    if (row >= ca) continue;
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int sp = 0; sp < ksplit; ++sp) {
+      const float4 v = *reinterpret_cast<const float4*>(
+          ws + (((size_t(tile) * ksplit + sp) * tg + t) * 128 + rl) * bn + col);
+      acc.x += v.x;
+      acc.y += v.y;
+      acc.z += v.z;
+      acc.w += v.w;
+    }
+    float4* dst = reinterpret_cast<float4*>(dw + (size_t(g * tg + t) * ld_m + m_off + row) * ld_n + n_off + nb * bn + col);
+    float4 o = *dst;
+    o.x += acc.x;
+    o.y += acc.y;
+    o.z += acc.z;
+    o.w += acc.w;
+    *dst = o;
   }
 }
 

@@ -1,6 +1,9 @@
 """Data-parallel training check on N GPUs (run under torchrun): the all-reduced flat gradient of N ranks must equal the
-gradient one rank accumulates over the same shards as micro-batches, and every rank must end the step with identical
-parameters.  python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 tools/dp_check.py"""
+gradient one rank accumulates over the same shards as micro-batches — BIT FOR BIT at N = 2 (the kernels use no
+floating-point atomics and every gradient tensor receives one addition per micro-batch, so rank0 + rank1 is the same
+fp32 sum as micro-batch 0 + micro-batch 1; for N > 2 NCCL's reduction tree may associate differently, so the bar there
+is 1e-6 relative) — the single-rank path must reproduce itself exactly run to run, and every rank must end the step
+with identical parameters.  python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 tools/dp_check.py"""
 import json, os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch, torch.distributed as dist
@@ -43,15 +46,16 @@ for r in range(world):
 torch.cuda.synchronize()
 g_ref = tr2.grads.clone()
 rel = float((g_dp - g_ref).norm() / g_ref.norm())
-# run-to-run noise floor of the single-rank path itself: the split-K / statistics reductions use floating-point atomics
-# (summation order varies), a last-bit change flips bf16 roundings downstream and the 18-layer ReLU->BN stack amplifies it
+exact = bool(torch.equal(g_dp, g_ref))
+# run-to-run: the single-rank path must reproduce itself exactly (fixed-order reductions everywhere)
 tr2.zero_grad()
 for r in range(world):
     bb, ee = train.shard_range(per * world, world, r)
     tr2.backward(torch.from_numpy(x[bb:ee]).to(dev), torch.from_numpy(y[bb:ee]).to(dev), count, seed=0, dropout=False)
 torch.cuda.synchronize()
 noise = float((tr2.grads - g_ref).norm() / g_ref.norm())
-out = {'world': world, 'rank': rank, 'grad_rel_vs_single_rank': rel, 'single_rank_run_to_run_rel': noise,
+out = {'world': world, 'rank': rank, 'grad_rel_vs_single_rank': rel, 'grad_bit_identical_to_single_rank': exact,
+       'single_rank_run_to_run_rel': noise,
        'grad_max_abs_diff_vs_rank0': same,
        'param_max_abs_diff_vs_rank0': same_p, 'grad_norm': float(g_dp.norm())}
 if world > 1:
@@ -60,7 +64,8 @@ if world > 1:
     out = gathered
 if rank == 0:
     print(json.dumps(out))
-    ok = all(o['grad_rel_vs_single_rank'] <= 3 * o['single_rank_run_to_run_rel'] + 1e-3 and
+    ok = all((o['grad_bit_identical_to_single_rank'] if world <= 2 else o['grad_rel_vs_single_rank'] <= 1e-6) and
+             o['single_rank_run_to_run_rel'] == 0.0 and
              o['grad_max_abs_diff_vs_rank0'] == 0.0 and
              o['param_max_abs_diff_vs_rank0'] == 0.0 for o in (out if isinstance(out, list) else [out]))
     print('dp_check', 'OK' if ok else 'FAILED')
