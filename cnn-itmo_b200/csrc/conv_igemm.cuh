@@ -54,6 +54,17 @@ enum StoreMode : int { kStorePlain = 0, kStoreTf32Rna = 1, kStoreSplit = 2 };
 struct ConvParams {
   CUtensorMap tmA[4];  // activation sources: dims (C, W, H, N), box (BK, 8*NM+2*pad, 16+2*pad, 1)
   CUtensorMap tmB;     // packed weights: dims (K_total, rows, taps), box (BK, BLOCK_N, 1)
+  // TMA-store epilogue (16-bit element types): every epilogue warp stages its 4 x 8 pixels x 64 (32) channels in a
+  // swizzled shared-memory tile and one lane issues cp.async.bulk.tensor stores — no per-lane global stores, no
+  // transposition shuffles on the L1 data pipe the tensor core's operand reads share.
+  //   tmOut[0]: 3x3 conv: the output (C, W, H, N), box (64 | 32 channels, 8, 4, 1).
+  //   tmOut[a], a = 0 / 1: transposed conv: output rows 2y + a viewed as ((b, co) = 2C, W, H, N) with a row stride of
+  //             two output rows — the 2x2 pixel shuffle is then a plain tile store, N columns a*2C .. (a+1)*2C - 1.
+  //   tmPool:   the 2x2-max-pooled copy (C, W/2, H/2, N), box (64 | 32, 4, 2, 1).
+  CUtensorMap tmOut[2];
+  CUtensorMap tmPool;
+  int tma_store;       // 1: use the maps above
+  int epi_bytes;       // shared memory of the staging tiles (0 when tma_store == 0)
   int H, W, NB;        // input spatial size and batch
   int n_seg;           // K segments; segment s reads seg_kb[s] channel blocks from tmA[seg_map[s]]
   int seg_map[kMaxSeg];
@@ -133,11 +144,17 @@ __device__ __forceinline__ uint32_t pack2<__nv_bfloat16>(float a, float b) {
 }
 template <>
 __device__ __forceinline__ uint32_t pack2<__half>(float a, float b) {
-  // saturate instead of overflowing to inf: fp16 tops out at 65504
-  a = fminf(fmaxf(a, -65504.f), 65504.f);
-  b = fminf(fmaxf(b, -65504.f), 65504.f);
-  __half2 h = __floats2half2_rn(a, b);
-  return *reinterpret_cast<uint32_t*>(&h);
+  // saturate instead of overflowing to inf (fp16 tops out at 65504): one F2FP.SATFINITE, no separate clamps (the
+  // fminf / fmaxf pairs cost the HBM-bound layers 15-20 % in the fp16 mode)
+  uint32_t r;
+  asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(b), "f"(a));
+  return r;
+}
+// max over |halves| of two packed fp16 pairs (HMNMX2.XORSIGN with |.| operands): magnitude bits only are meaningful
+__device__ __forceinline__ uint32_t absmax2_f16(uint32_t m, uint32_t v) {
+  uint32_t r;
+  asm("max.xorsign.abs.f16x2 %0, %1, %2;" : "=r"(r) : "r"(m), "r"(v));
+  return r;
 }
 __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) { return pack2<__nv_bfloat16>(a, b); }
 
@@ -333,7 +350,8 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
   const int n_a = p.n_a_stages, n_b = p.n_b_stages;
   uint8_t* smem_a = smem;                                   // n_a x halo tile
   uint8_t* smem_b = smem + n_a * p.a_stage_bytes;           // n_b x [BLOCK_N rows x SWZ bytes]
-  uint8_t* aux = smem_b + n_b * Cfg::kBBytes;
+  uint8_t* epi_stage = smem_b + n_b * Cfg::kBBytes;         // TMA-store staging: [kNumEpiWarps][40 rows][kEpiRowB], 1 KB aligned
+  uint8_t* aux = epi_stage + p.epi_bytes;
   uint64_t* a_full = reinterpret_cast<uint64_t*>(aux);      // [kMaxAStages]
   uint64_t* a_empty = a_full + kMaxAStages;
   uint64_t* b_full = a_empty + kMaxAStages;                 // [kMaxBStages]  (resident: b_full[0] only)
@@ -371,6 +389,11 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
   if (warp_idx == 0 && lane == 0) {
     for (int s = 0; s < 4; ++s) sm100::tma_prefetch_desc(&p.tmA[s]);
     sm100::tma_prefetch_desc(&p.tmB);
+    if (p.tma_store) {
+      sm100::tma_prefetch_desc(&p.tmOut[0]);
+      sm100::tma_prefetch_desc(&p.tmOut[1]);
+      sm100::tma_prefetch_desc(&p.tmPool);
+    }
   }
   if (warp_idx == 1 && lane == 0) {
     for (int i = 0; i < kMaxAStages; ++i) {
@@ -583,13 +606,15 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
       // the two warp sets split the tile: by M block when there are several, else by column chunk; a fused
       // head needs every channel of a pixel in one thread, so a lone block then stays with set 0
       const bool split_by_chunk = nm == 1 && kChunksPerBlk > 1 && p.head_dtype == kHeadNone;
+      // staged rows hold 64 channels = two chunks: with TMA stores the sets split a lone block by chunk PAIR
+      const int split_shift = (p.tma_store && BLOCK_N >= 64) ? 1 : 0;
       for (int j = 0; j < ((p.dbg & 32) ? 0 : nm); ++j) {  // dbg 32: timing experiment without the epilogue
         if (nm > 1 ? (j & 1) != ws : (!split_by_chunk && ws != 0)) continue;
         const int x = tx * tile_w + j * kBlkW + c;
         float h0 = 0.f, h1 = 0.f, h2 = 0.f;
 #pragma unroll 1
         for (int chunk = 0; chunk < kChunksPerBlk; ++chunk) {
-          if (split_by_chunk && (chunk & 1) != ws) continue;
+          if (split_by_chunk && ((chunk >> split_shift) & 1) != ws) continue;
           uint32_t v[kChunk];
           sm100::tmem_ld_32x32b_x32(taddr + uint32_t(j * BLOCK_N + chunk * kChunk), v);
           // output coordinates and the bias vector while the TMEM load is in flight
@@ -663,17 +688,19 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
           const bool pool_writer = (lane & 9) == 0;          // even row, even column of the block
           const size_t ppix = (size_t(img) * (p.H / 2) + (y >> 1)) * (p.W / 2) + (x >> 1);
           if constexpr (sizeof(Elem) == 2) {
-            if constexpr (ElemTraits<Elem>::kFmt == sm100::kFmtF16) {
-              if (p.sat_count != nullptr && (p.out != nullptr || p.pooled != nullptr)) {
-                float amax = 0.f;
-#pragma unroll
-                for (int i = 0; i < kChunk; ++i) amax = fmaxf(amax, fabsf(f[i]));
-                if (amax > 65504.f) atomicAdd(p.sat_count, 1ull);
-              }
-            }
             uint32_t pk[kChunk / 2];
 #pragma unroll
             for (int i = 0; i < kChunk / 2; ++i) pk[i] = pack2<Elem>(f[2 * i], f[2 * i + 1]);
+            if constexpr (ElemTraits<Elem>::kFmt == sm100::kFmtF16) {
+              // a value the saturating pack clamped reads back as +-65504 (0x7BFF): 16 packed |max| instead of 32 compares
+              if (p.sat_count != nullptr && (p.out != nullptr || p.pooled != nullptr)) {
+                uint32_t m2 = 0;
+#pragma unroll
+                for (int i = 0; i < kChunk / 2; ++i) m2 = absmax2_f16(m2, pk[i]);
+                m2 &= 0x7FFF7FFFu;
+                if ((m2 & 0xFFFFu) >= 0x7BFFu || (m2 >> 16) >= 0x7BFFu) atomicAdd(p.sat_count, 1ull);
+              }
+            }
             if constexpr (sizeof(Elem) == 2 && ElemTraits<Elem>::kFmt == sm100::kFmtBF16) {
               if (with_stats) {
                 // statistics of the ROUNDED values (what bn_apply and the backward read back from HBM)
@@ -692,6 +719,63 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
                 row[p.cout + co0 + lane] += tsq;
               }
             }
+            if (p.tma_store) {
+              // ---- staged TMA store. Row of the staging tile = one pixel (lane), kEpiRowB bytes of channels; the 16-byte
+              // pieces are XOR-swizzled exactly like the tensor map's SWIZZLE_128B / _64B mode, so the writes of a
+              // quarter warp hit 8 different bank groups.
+              constexpr int kRowB = BLOCK_N >= 64 ? 128 : 64;
+              uint8_t* st_out = epi_stage + ew * (40 * kRowB);
+              uint8_t* st_pool = st_out + 32 * kRowB;
+              const int half = kRowB == 128 ? (chunk & 1) : 0;
+              if (half == 0) {   // the previous group's bulk stores must have finished READING the staging tile
+                if (lane == 0) sm100::tma_store_wait_read<0>();
+                __syncwarp();
+              }
+              const int sw_out = kRowB == 128 ? (lane & 7) : ((lane >> 1) & 3);
+#pragma unroll
+              for (int k = 0; k < 4; ++k)
+                *reinterpret_cast<uint4*>(st_out + lane * kRowB + (((half * 4 + k) ^ sw_out) << 4)) =
+                    make_uint4(pk[4 * k], pk[4 * k + 1], pk[4 * k + 2], pk[4 * k + 3]);
+              if (p.pooled != nullptr) {
+                // 2x2 max-pool of the warp's 4 x 8 pixels out of the staging tile: lane = (pooled pixel, 16-byte piece)
+                __syncwarp();
+                const int pp = lane >> 2, k = lane & 3;
+                const int p00 = (2 * (pp >> 2)) * 8 + 2 * (pp & 3);
+                uint4 m4;
+                {
+                  const int pa = p00, pb = p00 + 1, pc = p00 + 8, pd = p00 + 9;
+                  auto piece = [&](int px) {
+                    const int sw = kRowB == 128 ? (px & 7) : ((px >> 1) & 3);
+                    return *reinterpret_cast<const uint4*>(st_out + px * kRowB + (((half * 4 + k) ^ sw) << 4));
+                  };
+                  const uint4 a4 = piece(pa), b4v = piece(pb), c4 = piece(pc), d4 = piece(pd);
+                  m4.x = max2<Elem>(max2<Elem>(a4.x, b4v.x), max2<Elem>(c4.x, d4.x));
+                  m4.y = max2<Elem>(max2<Elem>(a4.y, b4v.y), max2<Elem>(c4.y, d4.y));
+                  m4.z = max2<Elem>(max2<Elem>(a4.z, b4v.z), max2<Elem>(c4.z, d4.z));
+                  m4.w = max2<Elem>(max2<Elem>(a4.w, b4v.w), max2<Elem>(c4.w, d4.w));
+                }
+                const int sw_p = kRowB == 128 ? (pp & 7) : ((pp >> 1) & 3);
+                *reinterpret_cast<uint4*>(st_pool + pp * kRowB + (((half * 4 + k) ^ sw_p) << 4)) = m4;
+              }
+              if (kRowB == 64 || half == 1) {
+                sm100::fence_proxy_async_smem();   // generic-proxy writes -> visible to the TMA (async proxy)
+                __syncwarp();
+                if (lane == 0) {
+                  const int ng = (n_tile * BLOCK_N + chunk * kChunk) & ~(kRowB / 2 - 1);   // first column of the staged group
+                  const int x0 = tx * tile_w + j * kBlkW, y0 = ty * kBlkH + 4 * q;
+                  if (p.out != nullptr) {
+                    if (p.mode == kModeConvT2x2) {
+                      const int a_row = ng >> (p.cout_log2 + 1);                       // kernel row a of this column group
+                      sm100::tma_store_4d(&p.tmOut[a_row], st_out, ng - (a_row << (p.cout_log2 + 1)), x0, y0, img);
+                    } else {
+                      sm100::tma_store_4d(&p.tmOut[0], st_out, ng, x0, y0, img);
+                    }
+                  }
+                  if (p.pooled != nullptr) sm100::tma_store_4d(&p.tmPool, st_pool, ng, x0 >> 1, y0 >> 1, img);
+                  sm100::tma_store_commit();
+                }
+              }
+            } else {
             // The four lanes of a quad hold four horizontally adjacent pixels (64 B of channels each). A 4x4
             // transposition of the 16-byte pieces inside the quad lets every store instruction write 64
             // contiguous bytes per pixel (8 lines per request instead of 32 half-written sectors' worth of lines).
@@ -726,6 +810,7 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
                 *reinterpret_cast<uint4*>(pb + pp0 * p.cout) = make_uint4(m[0], m[1], m[2], m[3]);
                 *reinterpret_cast<uint4*>(pb + (pp0 + 1) * p.cout) = make_uint4(m[4], m[5], m[6], m[7]);
               }
+            }
             }
           } else {
             if (p.out != nullptr) {
@@ -779,6 +864,7 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
       acc ^= 1;
       if (acc == 0) acc_phase ^= 1;
     }
+    if (p.tma_store && lane == 0) sm100::tma_store_wait_all<0>();   // staging tiles stay valid until the TMA has read them
   }
 
   // ---------------------------------------------------------------- teardown

@@ -437,7 +437,16 @@ int run_conv(const ConvArgs& a, cudaStream_t stream) {
   const int kmult = k_mult(a.precision);
   const int kb_total = kmult * cin / bk;
   const int stats_bytes = a.stats ? itmo::kNumEpiWarps * 2 * a.cout * 4 : 0;   // per-warp statistic rows (ConvParams::stats)
-  const int budget = itmo::kSmemLimit - 1024 - itmo::kAuxBytes - stats_bytes;
+  // TMA-store epilogue: 16-bit element types, a materialised output, power-of-two channel counts (ITMO_TMA_STORE=0: A/B)
+  static const int allow_tma_store = env_int("ITMO_TMA_STORE", 1);
+  int cout_log2 = -1;
+  for (int b = 0; b < 16; ++b)
+    if ((1 << b) == a.cout) cout_log2 = b;
+  const bool tma_store = allow_tma_store && prec_is16(a.precision) && (a.out != nullptr || a.pooled != nullptr) &&
+                         cout_log2 >= 5 && (conv || a.cout >= 64);
+  const int epi_row = block_n >= 64 ? 128 : 64;
+  const int epi_bytes = tma_store ? itmo::kNumEpiWarps * 40 * epi_row : 0;
+  const int budget = itmo::kSmemLimit - 1024 - itmo::kAuxBytes - stats_bytes - epi_bytes;
   const int n_tiles = rows / block_n;
   int n_a, n_b, resident = 0;
   if (!no_resident && n_tiles == 1 && kb_total * taps * b_stage + 2 * a_stage <= budget) {
@@ -451,7 +460,7 @@ int run_conv(const ConvArgs& a, cudaStream_t stream) {
     const int left = budget - n_a * a_stage - n_b * b_stage;
     if (left >= a_stage) n_a = 3;
   }
-  const int smem_bytes = 1024 + n_a * a_stage + n_b * b_stage + itmo::kAuxBytes + stats_bytes;
+  const int smem_bytes = 1024 + n_a * a_stage + n_b * b_stage + epi_bytes + itmo::kAuxBytes + stats_bytes;
 
   itmo::ConvParams p;
   memset(&p, 0, sizeof(p));
@@ -465,6 +474,26 @@ int run_conv(const ConvArgs& a, cudaStream_t stream) {
   }
   int rc = make_weight_map(&p.tmB, a.wpacked, a.precision, kmult * cin, rows, taps, block_n, swz, a.w_tap_stride_rows);
   if (rc) return rc;
+  if (tma_store) {
+    p.tma_store = 1;
+    p.epi_bytes = epi_bytes;
+    if (a.out != nullptr) {
+      if (conv) {
+        rc = make_act_map(&p.tmOut[0], a.out, a.precision, a.cout, a.w, a.h, a.n, epi_row, 8, 4);
+        p.tmOut[1] = p.tmOut[0];
+      } else {
+        // output rows 2y + arow as ((b, co) = 2C, W, H, N): pixel stride 2C, row stride two output rows
+        for (int arow = 0; arow < 2 && rc == ITMO_OK; ++arow)
+          rc = make_act_map(&p.tmOut[arow], (const char*)a.out + size_t(arow) * 2 * a.w * a.cout * es, a.precision,
+                            2 * a.cout, a.w, a.h, a.n, epi_row, 8, 4, 4ll * a.w * a.cout, 4ll * a.h * a.w * a.cout);
+      }
+      if (rc) return rc;
+    }
+    if (a.pooled != nullptr) {
+      rc = make_act_map(&p.tmPool, a.pooled, a.precision, a.cout, a.w / 2, a.h / 2, a.n, epi_row, 4, 2);
+      if (rc) return rc;
+    }
+  }
   // K segments, in the order the weights are packed: [src0 | src1] x {w_hi, w_lo, (x_lo) w_hi}
   int ns = 0;
   for (int part = 0; part < kmult; ++part) {

@@ -311,7 +311,7 @@ int train_forward(itmo_trainer* t, const void* x, int x_dtype, int nb, int flags
         stat_rows = int(std::min<size_t>(g_stats, (npix + 63) / 64));
         itmo::bn_stats_kernel<<<stat_rows, 256, 0, s>>>(t->z[li], npix, L.cout, t->part);
       }
-      itmo::bn_finalize_kernel<<<(L.cout + 127) / 128, 128, 0, s>>>(
+      itmo::bn_finalize_kernel<<<(L.cout + 7) / 8, 256, 0, s>>>(
           t->part, stat_rows, L.cout, double(npix), 1e-3f, 0.99f, t->params + lay.gamma[li], t->params + lay.beta[li],
           bnv(t, li, 0), bnv(t, li, 1), bnv(t, li, 2), bnv(t, li, 3),
           (flags & ITMO_TRAIN_FREEZE_MOVING) ? nullptr : t->bn_moving + lay.bn[li],
@@ -339,7 +339,7 @@ int train_backward(itmo_trainer* t, const void* x, int x_dtype, const float* y, 
     const int grid_h = int(std::min<size_t>(g_head, (npix + 31) / 32));
     itmo::head_train_kernel<<<grid_h, 256, 0, s>>>(t->a[17], y, (const float*)t->wfwd[18], t->params + lay.bias[18], npix,
                                                    float(1.0 / loss_count), t->g[0], pred, t->part);
-    itmo::head_finalize_kernel<<<1, 256, 0, s>>>(t->part, grid_h, t->grads + lay.kernel[18], t->grads + lay.bias[18],
+    itmo::head_finalize_kernel<<<25, 256, 0, s>>>(t->part, grid_h, t->grads + lay.kernel[18], t->grads + lay.bias[18],
                                                  t->metrics);
     t->launches += 1;
     ITMO_CUDA(cudaGetLastError());
@@ -367,12 +367,12 @@ int train_backward(itmo_trainer* t, const void* x, int x_dtype, const float* y, 
       const int grid = int(std::min<size_t>(g_app, (npix + 63) / 64));
       itmo::bn_bwd_reduce_kernel<<<grid_r, 256, 0, s>>>(dA, t->z[li], npix, L.cout, bnv(t, li, 0), bnv(t, li, 1),
                                                       t->drop_seed[li], dropout ? 1 : 0, t->part);
-      itmo::bn_bwd_finalize_kernel<<<(L.cout + 127) / 128, 128, 0, s>>>(t->part, grid_r, L.cout, bstats(t, li),
+      itmo::bn_bwd_finalize_kernel<<<(L.cout + 7) / 8, 256, 0, s>>>(t->part, grid_r, L.cout, bstats(t, li),
                                                                         t->grads + lay.gamma[li], t->grads + lay.beta[li]);
       itmo::bn_bwd_apply_kernel<<<grid, 256, 0, s>>>(dA, t->z[li], t->gp, npix, L.cout, t->params + lay.gamma[li],
                                                      bnv(t, li, 0), bnv(t, li, 1), bstats(t, li), double(npix),
                                                      t->drop_seed[li], dropout ? 1 : 0, t->part2);
-      itmo::vec_partials_add_kernel<<<(L.cout + 127) / 128, 128, 0, s>>>(t->part2, grid, L.cout, t->grads + lay.bias[li]);
+      itmo::vec_partials_add_kernel<<<(L.cout + 7) / 8, 256, 0, s>>>(t->part2, grid, L.cout, t->grads + lay.bias[li]);
       t->launches += 3;
       ITMO_CUDA(cudaGetLastError());
     }

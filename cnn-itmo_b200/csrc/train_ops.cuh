@@ -69,6 +69,25 @@ __device__ __forceinline__ void block_reduce_channels(const float (&v)[8], float
   }
 }
 
+// Finalize kernels: a block of 256 threads = 8 columns x 32 row groups. Row group g adds rows g, g+32, ... of the
+// partial-sum workspace (in double), the 32 group sums are then added in group order: a fixed summation order with
+// nrows/32 dependent loads per thread instead of nrows (a one-thread-per-column loop over ~600 rows cost ~25 us per
+// launch, x 55 launches per micro-batch). The result is valid in the threads of row group 0 (threadIdx.x < 8).
+__device__ __forceinline__ double reduce_rows_8x32(const float* __restrict__ partials, int nrows, int stride, int col,
+                                                   bool col_ok, double* s_red /* [256] */) {
+  const int g = threadIdx.x >> 3;
+  double acc = 0.0;
+  if (col_ok)
+    for (int b = g; b < nrows; b += 32) acc += double(partials[size_t(b) * stride + col]);
+  __syncthreads();
+  s_red[threadIdx.x] = acc;
+  __syncthreads();
+  double tot = 0.0;
+  if (g == 0)
+    for (int k = 0; k < 32; ++k) tot += s_red[k * 8 + (threadIdx.x & 7)];
+  return tot;
+}
+
 // ---- BN training statistics: sum / sum of squares per channel of z = ReLU(conv + b) ------------------------------
 // grid-stride over pixels; blockDim = 256; thread -> (pixel lane, 8-channel group).
 // partials[blockIdx.x][0..C) = sum, [C..2C) = sumsq of this block's pixels.
@@ -106,18 +125,17 @@ __global__ void __launch_bounds__(256, 4) bn_stats_kernel(const __nv_bfloat16* _
 // mean / biased variance -> the affine bn_apply uses, the values backward needs, and the moving statistics
 // (Keras BatchNormalization: momentum 0.99; the moving variance takes the sample variance var * M / (M - (1 + eps))).
 // partials: [nblocks][2*C] per-block sums (bn_stats_kernel or the conv epilogue), added here in block order.
-__global__ void bn_finalize_kernel(const float* __restrict__ partials, int nblocks, int C, double M, float eps,
-                                   float momentum, const float* __restrict__ gamma, const float* __restrict__ beta,
-                                   float* __restrict__ mean, float* __restrict__ invstd, float* __restrict__ scale,
-                                   float* __restrict__ shift, float* __restrict__ moving_mean,
-                                   float* __restrict__ moving_var) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= C) return;
-  double sum = 0.0, sq = 0.0;
-  for (int b = 0; b < nblocks; ++b) {
-    sum += double(partials[size_t(b) * 2 * C + i]);
-    sq += double(partials[size_t(b) * 2 * C + C + i]);
-  }
+__global__ void __launch_bounds__(256) bn_finalize_kernel(const float* __restrict__ partials, int nblocks, int C, double M,
+                                                          float eps, float momentum, const float* __restrict__ gamma,
+                                                          const float* __restrict__ beta, float* __restrict__ mean,
+                                                          float* __restrict__ invstd, float* __restrict__ scale,
+                                                          float* __restrict__ shift, float* __restrict__ moving_mean,
+                                                          float* __restrict__ moving_var) {
+  __shared__ double s_red[256];
+  const int i = blockIdx.x * 8 + (threadIdx.x & 7);     // grid = ceil(C / 8)
+  const double sum = reduce_rows_8x32(partials, nblocks, 2 * C, i, i < C, s_red);
+  const double sq = reduce_rows_8x32(partials, nblocks, 2 * C, C + i, i < C, s_red);
+  if (threadIdx.x >= 8 || i >= C) return;
   const double m = sum / M;
   double v = sq / M - m * m;
   if (v < 0) v = 0;
@@ -341,12 +359,13 @@ __global__ void __launch_bounds__(256) head_train_kernel(const __nv_bfloat16* __
 }
 
 // adds the blocks' rows in index order: head kernel / bias gradients (Keras layout [64][3]) and the loss / accuracy sums
-__global__ void head_finalize_kernel(const float* __restrict__ partials, int nblocks, float* __restrict__ dwh,
-                                     float* __restrict__ dbh, double* __restrict__ acc) {
-  const int t = threadIdx.x;
-  if (t >= 197) return;
-  double s = 0.0;
-  for (int b = 0; b < nblocks; ++b) s += double(partials[size_t(b) * kHeadPartials + t]);
+__global__ void __launch_bounds__(256) head_finalize_kernel(const float* __restrict__ partials, int nblocks,
+                                                            float* __restrict__ dwh, float* __restrict__ dbh,
+                                                            double* __restrict__ acc) {
+  __shared__ double s_red[256];
+  const int t = blockIdx.x * 8 + (threadIdx.x & 7);     // grid = ceil(197 / 8) = 25
+  const double s = reduce_rows_8x32(partials, nblocks, kHeadPartials, t, t < 197, s_red);
+  if (threadIdx.x >= 8 || t >= 197) return;
   if (t < 192) dwh[(t & 63) * 3 + (t >> 6)] += float(s);
   else if (t < 195) dbh[t - 192] += float(s);
   else acc[t - 195] += s;
@@ -402,15 +421,14 @@ __global__ void __launch_bounds__(256, 4) bn_bwd_reduce_kernel(const __nv_bfloat
 
 // totals of pass 1 in block order -> sums[0..2C) (double, read by pass 2) and the BN parameter gradients:
 // dgamma += sum dA' zhat, dbeta += sum dA'  (ONE addition per micro-batch into the gradient buffer)
-__global__ void bn_bwd_finalize_kernel(const float* __restrict__ partials, int nblocks, int C, double* __restrict__ sums,
-                                       float* __restrict__ dgamma, float* __restrict__ dbeta) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= C) return;
-  double s0 = 0.0, s1 = 0.0;
-  for (int b = 0; b < nblocks; ++b) {
-    s0 += double(partials[size_t(b) * 2 * C + i]);
-    s1 += double(partials[size_t(b) * 2 * C + C + i]);
-  }
+__global__ void __launch_bounds__(256) bn_bwd_finalize_kernel(const float* __restrict__ partials, int nblocks, int C,
+                                                              double* __restrict__ sums, float* __restrict__ dgamma,
+                                                              float* __restrict__ dbeta) {
+  __shared__ double s_red[256];
+  const int i = blockIdx.x * 8 + (threadIdx.x & 7);     // grid = ceil(C / 8)
+  const double s0 = reduce_rows_8x32(partials, nblocks, 2 * C, i, i < C, s_red);
+  const double s1 = reduce_rows_8x32(partials, nblocks, 2 * C, C + i, i < C, s_red);
+  if (threadIdx.x >= 8 || i >= C) return;
   sums[i] = s0;
   sums[C + i] = s1;
   dbeta[i] += float(s0);
@@ -479,12 +497,12 @@ __global__ void __launch_bounds__(256, 3) bn_bwd_apply_kernel(const __nv_bfloat1
 }
 
 // dst[i] += sum over blocks (in index order) of partials[b][i]
-__global__ void vec_partials_add_kernel(const float* __restrict__ partials, int nblocks, int n, float* __restrict__ dst) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  double s = 0.0;
-  for (int b = 0; b < nblocks; ++b) s += double(partials[size_t(b) * n + i]);
-  dst[i] += float(s);
+__global__ void __launch_bounds__(256) vec_partials_add_kernel(const float* __restrict__ partials, int nblocks, int n,
+                                                               float* __restrict__ dst) {
+  __shared__ double s_red[256];
+  const int i = blockIdx.x * 8 + (threadIdx.x & 7);     // grid = ceil(n / 8)
+  const double s = reduce_rows_8x32(partials, nblocks, n, i, i < n, s_red);
+  if (threadIdx.x < 8 && i < n) dst[i] += float(s);
 }
 
 // ---- MaxPool backward + skip add: dA = dSkip + route(dPooled -> first maximum of the 2x2 window of a) -----------------
