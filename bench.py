@@ -383,7 +383,7 @@ def layer_table(graph, layer_times, steps, B, precision, peaks):
     return per_layer, igemm_flops, igemm_ms
 
 
-def run_batch_leg(a, hz, precision=None, batch=None, steps=None, with_e2e=True, with_parity=True, warm_s=2.5):
+def run_batch_leg(a, hz, precision=None, batch=None, steps=None, with_e2e=True, with_parity=True, warm_s=None):
     """Full U-Net forward over `batch` images per GPU. Returns the JSON line (rank 0) or None."""
     import numpy as np
     torch = hz.torch
@@ -405,7 +405,7 @@ def run_batch_leg(a, hz, precision=None, batch=None, steps=None, with_e2e=True, 
     def step():
         model.forward_device(x.data_ptr(), 'u8', y.data_ptr(), 'u8', B, stream=hz.stream.cuda_stream)
 
-    n_warm = warm_up(step, torch.cuda.synchronize, max(a.warmup, 3), warm_s)
+    n_warm = warm_up(step, torch.cuda.synchronize, max(a.warmup, 3), a.warm_seconds if warm_s is None else warm_s)
     hz.barrier()
     model.set_profiling(True)
     model.layer_times(reset=True)
@@ -794,6 +794,9 @@ def main(argv=None) -> int:
                          "'4k' / 'train' = that leg alone, printed as the JSON line")
     ap.add_argument('--frames', type=int, default=2, help='4K frames per GPU per step')
     ap.add_argument('--no-secondary', action='store_true', help='headline leg only')
+    ap.add_argument('--warm-seconds', type=float, default=2.5,
+                    help='minimum duration of the untimed warm-up of the headline leg (0 for profiler runs)')
+    ap.add_argument('--no-parity', action='store_true', help='skip the parity leg (profiler runs)')
     ap.add_argument('--secondary-steps', type=int, default=3, help='timed steps of each secondary leg')
     a = ap.parse_args(argv)
     if a.impl == 'reference':
@@ -804,7 +807,7 @@ def main(argv=None) -> int:
     elif a.workload == 'train':
         line = run_train_leg(a, hz)
     else:
-        line, ws = run_batch_leg(a, hz)
+        line, ws = run_batch_leg(a, hz, with_parity=not a.no_parity, with_e2e=not a.no_parity)
         secondary = {}
         if not a.no_secondary:
             t0 = time.perf_counter()

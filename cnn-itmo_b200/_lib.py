@@ -25,6 +25,14 @@ class LayerWeights(ctypes.Structure):
                 ('kernel', 'bias', 'gamma', 'beta', 'moving_mean', 'moving_variance')]
 
 
+class CameraParams(ctypes.Structure):
+    _fields_ = [('v', c_double), ('n', c_double), ('y', c_double)]
+
+
+class AffineParams(ctypes.Structure):
+    _fields_ = [(k, c_double) for k in ('m00', 'm01', 'm10', 'm11', 'off0', 'off1')] + [('flip_h', c_int), ('flip_v', c_int)]
+
+
 class ItmoError(RuntimeError):
     pass
 
@@ -79,6 +87,11 @@ SIGNATURES = {
     'itmo_train_set_profiling': (c_int, [c_void_p, c_int]),
     'itmo_train_phase_times': (c_int, [c_void_p, POINTER(c_double), POINTER(c_longlong), c_int]),
     'itmo_train_launch_count': (c_longlong, [c_void_p]),
+    # training-data synthesis / augmentation
+    'itmo_synth_hdr_field': (c_int, [c_void_p, c_int, c_int, c_int, c_uint, c_void_p]),
+    'itmo_virtual_camera': (c_int, [c_void_p, c_int, c_int, c_int, POINTER(CameraParams), c_void_p, c_int, c_void_p]),
+    'itmo_reinhard_target': (c_int, [c_void_p, c_int, c_int, c_int, c_double, c_void_p, c_int, c_void_p]),
+    'itmo_augment': (c_int, [c_void_p, c_int, c_int, c_int, c_int, POINTER(AffineParams), c_void_p, c_float, c_void_p]),
     'itmo_wgrad3x3': (c_int, [c_void_p, c_int, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
     'itmo_dgrad3x3': (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_int, c_void_p, c_void_p]),
 }

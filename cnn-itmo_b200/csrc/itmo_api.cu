@@ -1445,3 +1445,4 @@ int itmo_conv3x3_bn_rgb(int precision, const void* in, int in_dtype, int n, int 
 }  // extern "C"
 
 #include "train_api.cuh"
+#include "datagen_api.cuh"

@@ -238,6 +238,38 @@ int itmo_wgrad3x3(const void* x, int cin, const void* g, int cout, int n, int h,
 int itmo_dgrad3x3(const void* g, int cout, int n, int h, int w, const float* kernel_hwio, int cin, void* dx,
                   void* stream);
 
+/* ---- training-data synthesis and augmentation (BASELINE configs[3], [4]: "synthetic SDR/HDR pairs") -----------
+ * The reference prepares its data offline in MATLAB and augments on the host in Keras; these entry points run the same
+ * arithmetic as CUDA kernels so a training / 4K run can be fed without leaving the GPU. All *_dev pointers are device
+ * memory, images are NHWC [n,h,w,3]; parameter arrays are HOST memory, one entry per image. Asynchronous on `stream`
+ * after an internal synchronisation for the parameter upload. */
+/* Seeded log-normal HDR radiance field, float32 (stands in for the EXR corpus the reference does not ship). */
+int itmo_synth_hdr_field(float* hdr_dev, int n, int h, int w, unsigned seed, void* stream);
+/* One virtual camera per image (m-files/virtual_camera.m:13, 21-22): v ~ U[-4,4] stops, n ~ N(0.6, sqrt 0.1),
+ * y ~ N(0.9, sqrt 0.1). */
+typedef struct itmo_camera_params {
+  double v, n, y;
+} itmo_camera_params;
+/* m-files/virtual_camera.m:12-37: HDR -> SDR network input. G = exp(mean log max(Y, realmin)), X = 0.18 * 2^v / G * Y,
+ * a = (1+n) X^y / (n + X^y), min(1, a), colour by the luminance ratio, imwrite's 8-bit rounding.
+ * out_dtype ITMO_DT_U8: the PNG's pixel values; ITMO_DT_F32: those / 255 (Keras rescale=1/255, main.py:71). */
+int itmo_virtual_camera(const float* hdr_dev, int n, int h, int w, const itmo_camera_params* cams_host, void* sdr_dev,
+                        int out_dtype, void* stream);
+/* m-files/Reinhard.m:12-31: HDR -> tone-mapped training target. X = key / G * Y (key 0.18, :20), L = X / (1 + X) (:22),
+ * colour by L / Y, imwrite's 8-bit rounding; out_dtype as above. */
+int itmo_reinhard_target(const float* hdr_dev, int n, int h, int w, double key, void* out_dev, int out_dtype, void* stream);
+/* main.py:71-76: ImageDataGenerator's random transform for one batch. Per image: input (row, col) = M * output (row, col)
+ * + off — the matrix keras_preprocessing builds from rotation and zoom around its image centre — sampled bilinearly
+ * with edge replication (scipy.ndimage.affine_transform order=1, mode='nearest'), then the horizontal / vertical flips.
+ * Use the SAME params for the input batch and the target batch (the reference gives both generators seed=1,
+ * main.py:78-100). in: uint8 or float32; out float32 = value * scale (1/255 = rescale). */
+typedef struct itmo_affine_params {
+  double m00, m01, m10, m11, off0, off1;
+  int flip_h, flip_v;
+} itmo_affine_params;
+int itmo_augment(const void* in_dev, int in_dtype, int n, int h, int w, const itmo_affine_params* params_host,
+                 float* out_dev, float scale, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
