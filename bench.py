@@ -135,7 +135,7 @@ class ClockSampler:
 def calibrated_checkpoint(hz, seed: int = 218) -> str:
     """Path of the Keras-layout HDF5 file holding the calibrated synthetic checkpoint; rank 0 writes it (fixture
     generation by oracle/unet_ref.py, outside every timed region), the other ranks wait for it."""
-    path = os.path.join(ROOT, 'gpurun_out', f'calibrated-{seed}.hdf5')
+    path = os.path.join(tempfile.gettempdir(), f'itmo_calibrated-{seed}.hdf5')   # 45 MB: not under gpurun_out/
     if hz.rank == 0 and not os.path.exists(path):
         from oracle import unet_ref as R
         import cnn_itmo_b200 as M

@@ -77,8 +77,18 @@ __device__ __forceinline__ double reduce_rows_8x32(const float* __restrict__ par
                                                    bool col_ok, double* s_red /* [256] */) {
   const int g = threadIdx.x >> 3;
   double acc = 0.0;
-  if (col_ok)
-    for (int b = g; b < nrows; b += 32) acc += double(partials[size_t(b) * stride + col]);
+  if (col_ok) {
+    int b = g;
+    for (; b + 96 < nrows; b += 128) {   // four independent loads in flight, added in row order
+      const float v0 = partials[size_t(b) * stride + col], v1 = partials[size_t(b + 32) * stride + col];
+      const float v2 = partials[size_t(b + 64) * stride + col], v3 = partials[size_t(b + 96) * stride + col];
+      acc += double(v0);
+      acc += double(v1);
+      acc += double(v2);
+      acc += double(v3);
+    }
+    for (; b < nrows; b += 32) acc += double(partials[size_t(b) * stride + col]);
+  }
   __syncthreads();
   s_red[threadIdx.x] = acc;
   __syncthreads();
@@ -261,56 +271,74 @@ __global__ void __launch_bounds__(256) head_train_kernel(const __nv_bfloat16* __
   }
   float g[3][8] = {}, gb[3] = {};
   float loss = 0.f, hits = 0.f;
+  // Each lane handles kU pixels per iteration (pixel groups a whole grid stride apart): kU independent 16-byte loads in
+  // flight per thread. With one load per iteration the kernel was latency-bound at 1.7 TB/s (8 KB in flight per SM).
+  constexpr int kU = 4;
   const size_t per_iter = size_t(gridDim.x) * 32;   // 8 warps x 4 pixels per block
-  const size_t n_iter = (npix + per_iter - 1) / per_iter;
+  const size_t n_iter = (npix + per_iter * kU - 1) / (per_iter * kU);
   for (size_t it = 0; it < n_iter; ++it) {
-    const size_t pix = it * per_iter + size_t(blockIdx.x) * 32 + wid * 4 + ps;
-    const bool ok = pix < npix;
-    float av[8];
-    if (ok) ld8(a + pix * 64 + cg * 8).get(av);
-    else {
+    const size_t pix0 = it * per_iter * kU + size_t(blockIdx.x) * 32 + wid * 4 + ps;
+    Bf8 raw[kU];
+    float yv[kU][3];
 #pragma unroll
-      for (int i = 0; i < 8; ++i) av[i] = 0.f;
-    }
-    float z[3];
-#pragma unroll
-    for (int k = 0; k < 3; ++k) {
-      float t = 0.f;
-#pragma unroll
-      for (int i = 0; i < 8; ++i) t = fmaf(av[i], w[k][i], t);
-      t += __shfl_xor_sync(0xFFFFFFFFu, t, 1);
-      t += __shfl_xor_sync(0xFFFFFFFFu, t, 2);
-      t += __shfl_xor_sync(0xFFFFFFFFu, t, 4);
-      z[k] = t + bk[k];
-    }
-    const float p0 = 1.f / (1.f + expf(-z[0])), p1 = 1.f / (1.f + expf(-z[1])), p2 = 1.f / (1.f + expf(-z[2]));
-    if (ok) {
-      const float y0 = y[pix * 3], y1 = y[pix * 3 + 1], y2 = y[pix * 3 + 2];
-      const float e0 = p0 - y0, e1 = p1 - y1, e2 = p2 - y2;
-      const float dl0 = 2.f * inv_count * e0 * p0 * (1.f - p0);
-      const float dl1 = 2.f * inv_count * e1 * p1 * (1.f - p1);
-      const float dl2 = 2.f * inv_count * e2 * p2 * (1.f - p2);
-      if (cg == 0) {
-        loss += e0 * e0 + e1 * e1 + e2 * e2;
-        const int ap = p0 >= p1 ? (p0 >= p2 ? 0 : 2) : (p1 >= p2 ? 1 : 2);   // first maximum, like argmax
-        const int ay = y0 >= y1 ? (y0 >= y2 ? 0 : 2) : (y1 >= y2 ? 1 : 2);
-        hits += ap == ay ? 1.f : 0.f;
-        gb[0] += dl0;
-        gb[1] += dl1;
-        gb[2] += dl2;
+    for (int u = 0; u < kU; ++u) {
+      const size_t pix = pix0 + u * per_iter;
+      if (pix < npix) {
+        raw[u] = ld8(a + pix * 64 + cg * 8);
+        yv[u][0] = y[pix * 3];
+        yv[u][1] = y[pix * 3 + 1];
+        yv[u][2] = y[pix * 3 + 2];
+      } else {
+        raw[u].raw = make_uint4(0u, 0u, 0u, 0u);
+        yv[u][0] = yv[u][1] = yv[u][2] = 0.f;
       }
-      if (pred && cg < 3) pred[pix * 3 + cg] = cg == 0 ? p0 : cg == 1 ? p1 : p2;
-      float f[8];
+    }
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        f[i] = dl0 * w[0][i] + dl1 * w[1][i] + dl2 * w[2][i];
-        g[0][i] = fmaf(dl0, av[i], g[0][i]);
-        g[1][i] = fmaf(dl1, av[i], g[1][i]);
-        g[2][i] = fmaf(dl2, av[i], g[2][i]);
+    for (int u = 0; u < kU; ++u) {
+      const size_t pix = pix0 + u * per_iter;
+      const bool ok = pix < npix;
+      float av[8];
+      raw[u].get(av);
+      float z[3];
+#pragma unroll
+      for (int k = 0; k < 3; ++k) {
+        float t = 0.f;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) t = fmaf(av[i], w[k][i], t);
+        t += __shfl_xor_sync(0xFFFFFFFFu, t, 1);
+        t += __shfl_xor_sync(0xFFFFFFFFu, t, 2);
+        t += __shfl_xor_sync(0xFFFFFFFFu, t, 4);
+        z[k] = t + bk[k];
       }
-      Bf8 o;
-      o.set(f);
-      st8(d_a + pix * 64 + cg * 8, o);
+      const float p0 = 1.f / (1.f + expf(-z[0])), p1 = 1.f / (1.f + expf(-z[1])), p2 = 1.f / (1.f + expf(-z[2]));
+      if (ok) {
+        const float y0 = yv[u][0], y1 = yv[u][1], y2 = yv[u][2];
+        const float e0 = p0 - y0, e1 = p1 - y1, e2 = p2 - y2;
+        const float dl0 = 2.f * inv_count * e0 * p0 * (1.f - p0);
+        const float dl1 = 2.f * inv_count * e1 * p1 * (1.f - p1);
+        const float dl2 = 2.f * inv_count * e2 * p2 * (1.f - p2);
+        if (cg == 0) {
+          loss += e0 * e0 + e1 * e1 + e2 * e2;
+          const int ap = p0 >= p1 ? (p0 >= p2 ? 0 : 2) : (p1 >= p2 ? 1 : 2);   // first maximum, like argmax
+          const int ay = y0 >= y1 ? (y0 >= y2 ? 0 : 2) : (y1 >= y2 ? 1 : 2);
+          hits += ap == ay ? 1.f : 0.f;
+          gb[0] += dl0;
+          gb[1] += dl1;
+          gb[2] += dl2;
+        }
+        if (pred && cg < 3) pred[pix * 3 + cg] = cg == 0 ? p0 : cg == 1 ? p1 : p2;
+        float f[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          f[i] = dl0 * w[0][i] + dl1 * w[1][i] + dl2 * w[2][i];
+          g[0][i] = fmaf(dl0, av[i], g[0][i]);
+          g[1][i] = fmaf(dl1, av[i], g[1][i]);
+          g[2][i] = fmaf(dl2, av[i], g[2][i]);
+        }
+        Bf8 o;
+        o.set(f);
+        st8(d_a + pix * 64 + cg * 8, o);
+      }
     }
   }
   // the 4 pixel slots of a warp (lanes cg, cg+8, cg+16, cg+24): fixed xor tree

@@ -248,9 +248,23 @@ __global__ void __launch_bounds__(256) wgrad_reduce_kernel(const float* __restri
     const int row = mb * 128 + rl;
     if (row >= ca) continue;
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int sp = 0; sp < ksplit; ++sp) {
-      const float4 v = *reinterpret_cast<const float4*>(
-          ws + (((size_t(tile) * ksplit + sp) * tg + t) * 128 + rl) * bn + col);
+    const float* src = ws + ((size_t(tile) * ksplit * tg + t) * 128 + rl) * bn + col;
+    const size_t sp_stride = size_t(tg) * 128 * bn;
+    int sp = 0;
+    for (; sp + 4 <= ksplit; sp += 4) {   // four independent loads in flight, added in slice order
+      float4 v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) v[u] = *reinterpret_cast<const float4*>(src + (sp + u) * sp_stride);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        acc.x += v[u].x;
+        acc.y += v[u].y;
+        acc.z += v[u].z;
+        acc.w += v[u].w;
+      }
+    }
+    for (; sp < ksplit; ++sp) {
+      const float4 v = *reinterpret_cast<const float4*>(src + sp * sp_stride);
       acc.x += v.x;
       acc.y += v.y;
       acc.z += v.z;
