@@ -9,6 +9,8 @@ and fails loudly if it is missing — there is no CPU fallback.
 from .graph import LAYERS, count_params, forward_flops_per_image, summary_text  # noqa: F401
 from .model import Model, U_net, initial_weights, load_model  # noqa: F401
 from . import frames  # noqa: F401
+from . import callbacks  # noqa: F401
+from . import datagen  # noqa: F401
 from . import train  # noqa: F401
 from .checkpoint import read_checkpoint, write_checkpoint  # noqa: F401
 

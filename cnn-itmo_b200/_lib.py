@@ -50,6 +50,7 @@ SIGNATURES = {
     'itmo_predict_host': (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_int, c_uint]),
     'itmo_launch_count': (c_longlong, [c_void_p]),
     'itmo_saturation_count': (c_int, [c_void_p, POINTER(ctypes.c_ulonglong), c_int]),
+    'itmo_set_graph_capture': (c_int, [c_void_p, c_int]),
     'itmo_host_alloc': (c_int, [POINTER(c_void_p), c_size_t]),
     'itmo_host_free': (None, [c_void_p]),
     'itmo_set_profiling': (c_int, [c_void_p, c_int]),

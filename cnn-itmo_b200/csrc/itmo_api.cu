@@ -8,6 +8,8 @@
 #include <cuda_bf16.h>
 
 #include <algorithm>
+#include <map>
+#include <tuple>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -724,6 +726,10 @@ struct itmo_ctx {
   int frm_rects_cap = 0;
   itmo::FrameStats* frm_stats = nullptr;
 
+  // CUDA graphs of the 18-launch forward of one arena chunk (itmo_set_graph_capture), keyed by
+  // (images, in dtype, out dtype, staging slot): itmo_predict_host replays them instead of re-launching
+  bool use_graph = false;
+  std::map<std::tuple<int, int, int, int>, cudaGraphExec_t> graphs;
   // per-layer device timing (itmo_set_profiling): event pairs recorded around every layer launch
   bool profiling = false;
   struct Stamp { int layer; cudaEvent_t beg, end; };
@@ -821,6 +827,46 @@ int forward_chunk(itmo_ctx* ctx, const void* in_dev, int in_dtype, void* out_dev
     if (rc) return rc;
     ctx->launches++;
   }
+  ctx->last_chunk = nb;
+  return ITMO_OK;
+}
+
+void drop_graphs(itmo_ctx* ctx) {
+  for (auto& kv : ctx->graphs) cudaGraphExecDestroy(kv.second);
+  ctx->graphs.clear();
+}
+
+// One arena chunk of itmo_predict_host through a captured CUDA graph: the 18 launches (tensor maps and the by-value
+// affine vectors baked into the kernel nodes) are recorded once per (chunk size, dtypes, staging slot) and replayed
+// with ONE cudaGraphLaunch. For the reference's batch-1 loop (predict.py:50-62) the 18 launches of 10-100 us are
+// latency-bound on the host side; the graph removes the per-launch host work.
+int forward_chunk_graph(itmo_ctx* ctx, int slot, int in_dtype, int out_dtype, int nb) {
+  const auto key = std::make_tuple(nb, in_dtype, out_dtype, slot);
+  auto it = ctx->graphs.find(key);
+  if (it == ctx->graphs.end()) {
+    // eager once: sets the kernels' function attributes (not allowed inside a capture) and validates the launch
+    int rc = forward_chunk(ctx, ctx->dev_in[slot], in_dtype, ctx->dev_out[slot], out_dtype, nb, ctx->own_stream);
+    if (rc) return rc;
+    ITMO_CUDA(cudaStreamSynchronize(ctx->own_stream));
+    const long long launches0 = ctx->launches;
+    ITMO_CUDA(cudaStreamBeginCapture(ctx->own_stream, cudaStreamCaptureModeThreadLocal));
+    rc = forward_chunk(ctx, ctx->dev_in[slot], in_dtype, ctx->dev_out[slot], out_dtype, nb, ctx->own_stream);
+    cudaGraph_t graph = nullptr;
+    cudaError_t e = cudaStreamEndCapture(ctx->own_stream, &graph);
+    ctx->launches = launches0;   // recorded, not launched
+    if (rc) {
+      if (graph) cudaGraphDestroy(graph);
+      return rc;
+    }
+    if (e != cudaSuccess) return fail(ITMO_ERR_CUDA, "graph capture failed: %s", cudaGetErrorString(e));
+    cudaGraphExec_t exec = nullptr;
+    e = cudaGraphInstantiate(&exec, graph, 0);
+    cudaGraphDestroy(graph);
+    if (e != cudaSuccess) return fail(ITMO_ERR_CUDA, "cudaGraphInstantiate failed: %s", cudaGetErrorString(e));
+    it = ctx->graphs.emplace(key, exec).first;
+  }
+  ITMO_CUDA(cudaGraphLaunch(it->second, ctx->own_stream));
+  ctx->launches += ITMO_NUM_LAYERS - 1;   // kernels the replay launches
   ctx->last_chunk = nb;
   return ITMO_OK;
 }
@@ -933,6 +979,7 @@ void itmo_destroy(itmo_ctx* ctx) {
   if (!ctx) return;
   cudaSetDevice(ctx->device);
   cudaDeviceSynchronize();
+  drop_graphs(ctx);
   for (int li = 0; li < ITMO_NUM_LAYERS; ++li) {
     cudaFree(ctx->wpacked[li]);
     cudaFree(ctx->bias[li]);
@@ -968,6 +1015,7 @@ int itmo_load_weights(itmo_ctx* ctx, const itmo_layer_weights* layers, int n_lay
   if (!ctx || !layers) return fail(ITMO_ERR_INVALID, "null argument");
   if (n_layers != ITMO_NUM_LAYERS) return fail(ITMO_ERR_INVALID, "expected %d layers, got %d", ITMO_NUM_LAYERS, n_layers);
   ITMO_CUDA(cudaSetDevice(ctx->device));
+  drop_graphs(ctx);   // captured launches carry the old by-value affine vectors
   cudaStream_t s = ctx->own_stream;
   float* tmp = nullptr;  // fp32 staging for the largest kernel (conv2d_11: 9*768*512)
   const size_t tmp_elems = size_t(9) * 768 * 512;
@@ -1093,6 +1141,7 @@ int itmo_predict_host(itmo_ctx* ctx, const void* in_host, int in_dtype, void* ou
   const size_t in_img = size_t(ITMO_IMG) * ITMO_IMG * 3 * (in_dtype == ITMO_DT_U8 ? 1 : 4);
   const size_t out_img = size_t(ITMO_IMG) * ITMO_IMG * 3 * (out_dtype == ITMO_DT_U8 ? 1 : 4);
   const size_t need_in = in_img * ctx->cap, need_out = out_img * ctx->cap;
+  if (ctx->stage_in_bytes < need_in || ctx->stage_out_bytes < need_out) drop_graphs(ctx);   // staging pointers change
   if (ctx->stage_in_bytes < need_in) {
     for (int b = 0; b < 2; ++b) {
       cudaFree(ctx->dev_in[b]);
@@ -1124,7 +1173,9 @@ int itmo_predict_host(itmo_ctx* ctx, const void* in_host, int in_dtype, void* ou
     ITMO_CUDA(cudaEventRecord(ctx->ev_in_ready[b], ctx->h2d_stream));
     ITMO_CUDA(cudaStreamWaitEvent(ctx->own_stream, ctx->ev_in_ready[b], 0));
     if (c >= 2) ITMO_CUDA(cudaStreamWaitEvent(ctx->own_stream, ctx->ev_out_free[b], 0));      // dev_out[b] drained
-    int rc = forward_chunk(ctx, ctx->dev_in[b], in_dtype, ctx->dev_out[b], out_dtype, nb, ctx->own_stream);
+    int rc = (ctx->use_graph && !ctx->profiling)
+                 ? forward_chunk_graph(ctx, b, in_dtype, out_dtype, nb)
+                 : forward_chunk(ctx, ctx->dev_in[b], in_dtype, ctx->dev_out[b], out_dtype, nb, ctx->own_stream);
     if (rc) return rc;
     ITMO_CUDA(cudaEventRecord(ctx->ev_compute_done[b], ctx->own_stream));
     ITMO_CUDA(cudaStreamWaitEvent(ctx->d2h_stream, ctx->ev_compute_done[b], 0));
@@ -1303,6 +1354,13 @@ int itmo_layer_times(itmo_ctx* ctx, double* ms_sum, long long* calls, int reset)
 }
 
 long long itmo_launch_count(const itmo_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+int itmo_set_graph_capture(itmo_ctx* ctx, int enable) {
+  if (!ctx) return fail(ITMO_ERR_INVALID, "null argument");
+  ctx->use_graph = enable != 0;
+  if (!enable) drop_graphs(ctx);
+  return ITMO_OK;
+}
 
 int itmo_saturation_count(itmo_ctx* ctx, unsigned long long* count, int reset) {
   if (!ctx || !count) return fail(ITMO_ERR_INVALID, "null argument");

@@ -155,6 +155,7 @@ class Model:
         if not self._ctx:
             _lib.check(lib.itmo_create(ctypes.byref(self._ctx), self.device, _PRECISIONS[self.precision],
                                        self.max_batch))
+            _lib.check(lib.itmo_set_graph_capture(self._ctx, int(self.use_cuda_graph)))
         if not self._uploaded:
             arr = (_lib.LayerWeights * graph.NUM_LAYERS)()
             keep = []
@@ -386,6 +387,9 @@ class Model:
             self._optimizer_weights = None
         return self._trainer
 
+    # predict() / predict_u8() replay a captured CUDA graph of the 18-launch forward (itmo_set_graph_capture); set to
+    # False before the first call to launch the kernels one by one ($ITMO_CUDA_GRAPH=0 does the same)
+    use_cuda_graph = os.environ.get('ITMO_CUDA_GRAPH', '1') != '0'
     train_micro_batch = 8
     train_seed: Optional[int] = None     # Dropout mask stream of the training engine; None = fresh entropy per engine
 
@@ -416,13 +420,28 @@ class Model:
                       validation_data=None, validation_steps=None, **kwargs):
         """model.fit_generator(train_generator, steps_per_epoch, epochs, validation_data, validation_steps, callbacks)
         (main.py:126-132). `generator` yields (x, y) batches (main.py:111's zip of two flows). Callbacks: objects with
-        on_epoch_end(epoch, logs) (ModelCheckpoint / CSVLogger stand-ins). Returns {'loss': [...], 'acc': [...],
+        the keras.callbacks.Callback hooks (cnn_itmo_b200.callbacks has CSVLogger / ModelCheckpoint / LambdaCallback with
+        main.py:69,121-124's arguments); on_epoch_end sees the TRAINED weights through model.predict / model.save. Returns {'loss': [...], 'acc': [...],
         'val_loss': [...], 'val_acc': [...]} per epoch like History.history."""
         if steps_per_epoch is None:
             raise ValueError('steps_per_epoch is required for a generator')
         history: Dict[str, List[float]] = {'loss': [], 'acc': []}
         it = iter(generator)
+        callbacks = list(callbacks or [])
+        for cb in callbacks:
+            if hasattr(cb, 'set_model'):
+                cb.set_model(self)
+            if hasattr(cb, 'set_params'):
+                cb.set_params({'epochs': int(epochs), 'steps': int(steps_per_epoch), 'verbose': verbose,
+                               'do_validation': validation_data is not None,
+                               'metrics': ['loss', 'acc'] + (['val_loss', 'val_acc'] if validation_data is not None else [])})
+        for cb in callbacks:
+            if hasattr(cb, 'on_train_begin'):
+                cb.on_train_begin({})
         for epoch in range(int(epochs)):
+            for cb in callbacks:
+                if hasattr(cb, 'on_epoch_begin'):
+                    cb.on_epoch_begin(epoch, {})
             ls, ac = [], []
             for _ in range(int(steps_per_epoch)):
                 x, y = next(it)

@@ -104,6 +104,12 @@ int itmo_forward(itmo_ctx* ctx, const void* in_dev, int in_dtype, void* out_dev,
 int itmo_predict_host(itmo_ctx* ctx, const void* in_host, int in_dtype, void* out_host, int out_dtype, int n,
                       unsigned flags);
 
+/* CUDA-graph replay for itmo_predict_host: the 18 kernel launches of one arena chunk are captured once per (chunk size,
+ * dtypes, staging slot) and replayed with one cudaGraphLaunch — for the reference's batch-1 loop (predict.py:50-62) the
+ * launches are host-latency-bound. Graphs are dropped when weights are reloaded. Off by default at the ABI; the Python
+ * shim turns it on. Has no effect while itmo_set_profiling is on. */
+int itmo_set_graph_capture(itmo_ctx* ctx, int enable);
+
 /* Pinned (page-locked) host memory for itmo_predict_host's in/out buffers: copies from/to it are asynchronous
  * and overlap the kernels. Free with itmo_host_free(). */
 int itmo_host_alloc(void** out, size_t bytes);

@@ -228,3 +228,50 @@ def test_empty_batch_and_errors(pkg, calibrated_weights):
                              x.data_ptr(), x.data_ptr(), 32, x.data_ptr(), None, None)
     assert rc == -1
     m.close()
+
+
+def test_cuda_graph_replay_equals_eager_launches(pkg, calibrated_weights, images):
+    """itmo_set_graph_capture: predict_host through a replayed CUDA graph returns the bytes the 18 eager launches return —
+    for every chunk size / dtype pair (each gets its own graph), across repeated calls, and after new weights are loaded
+    (the graphs carry by-value affine vectors and must be dropped)."""
+    imgs = np.concatenate([images, images[::-1]])[:5]
+    eager = pkg.Model(calibrated_weights, max_batch=2)
+    eager.use_cuda_graph = False
+    graph_m = pkg.Model(calibrated_weights, max_batch=2)
+    graph_m.use_cuda_graph = True
+    for n in (1, 2, 5, 1):                       # 5 = chunks 2, 2, 1 through both staging slots
+        a = eager.predict_u8(imgs[:n])
+        b = graph_m.predict_u8(imgs[:n])
+        np.testing.assert_array_equal(a, b)
+        b2 = graph_m.predict_u8(imgs[:n])        # replay
+        np.testing.assert_array_equal(a, b2)
+    x = R.preprocess_u8(imgs[:3])
+    np.testing.assert_array_equal(eager.predict(x), graph_m.predict(x))
+    # new weights: stale graphs would keep producing the old image
+    ws2 = [dict(w) for w in calibrated_weights]
+    ws2[17] = dict(ws2[17], bias=ws2[17]['bias'] + np.float32(0.5))
+    e2 = pkg.Model(ws2, max_batch=2)
+    e2.use_cuda_graph = False
+    graph_m._install_weights(ws2)
+    want = e2.predict_u8(imgs[:2])
+    got = graph_m.predict_u8(imgs[:2])
+    np.testing.assert_array_equal(want, got)
+    assert not np.array_equal(got, eager.predict_u8(imgs[:2]))
+    for m in (eager, graph_m, e2):
+        m.close()
+
+
+def test_pipelined_predict_loop_equals_reference_loop(pkg, calibrated_weights, golden_dir, tmp_path):
+    """predict.run_pipelined (thread-pool PNG codec + double-buffered pinned batches) writes the same pixels as the
+    reference-shaped loop predict.run (predict.py:50-72), ragged last chunk included."""
+    from cnn_itmo_b200 import predict as P
+    files = P.list_inputs(os.path.join(golden_dir, 'images_to_predict', 'input'))
+    m = pkg.Model(calibrated_weights, max_batch=8)
+    wa = P.run(m, files, str(tmp_path / 'a'), batch=1, verbose=False)
+    stats = {}
+    wb = P.run_pipelined(m, files, str(tmp_path / 'b'), batch=5, workers=4, stats=stats)
+    assert [os.path.basename(p) for p in wa] == [os.path.basename(p) for p in wb] and len(wb) == 12
+    for pa, pb in zip(wa, wb):
+        np.testing.assert_array_equal(P.load_png(pa), P.load_png(pb))
+    assert stats['files'] == 12 and stats['gpu_seconds'] > 0
+    m.close()
