@@ -50,6 +50,13 @@ enum HeadDtype : int { kHeadNone = 0, kHeadF32 = 1, kHeadU8 = 2 };
 // how fp32 results are stored (Elem = float): as computed, rounded to TF32 (so the tensor core's
 // operand truncation is a no-op and the error is unbiased), or split into a TF32 head + residual.
 enum StoreMode : int { kStorePlain = 0, kStoreTf32Rna = 1, kStoreSplit = 2 };
+// Epilogue variant compiled into the kernel (template parameter EPI). 0 = the generic epilogue (every mode behind
+// run-time flags: training statistics, split accumulators, fp32 storage, linear / identity, odd tile shapes). The
+// others are the inference forward pass's four shapes as straight-line code for the 16-bit element types — ncu
+// counted ~480 warp instructions per 32-column chunk in the generic loop, ~46 of them branches, against ~150 the
+// arithmetic needs, and the HBM-bound layers were bound by exactly that issue stream (two epilogue warps per
+// scheduler). | kEpiConstAffine: bias / scale / shift as constant-bank operands (cout <= 64).
+enum EpiKind : int { kEpiGeneric = 0, kEpiConv = 1, kEpiConvPool = 2, kEpiConvT = 3, kEpiHead = 4, kEpiConstAffine = 16 };
 
 struct ConvParams {
   CUtensorMap tmA[4];  // activation sources: dims (C, W, H, N), box (BK, 8*NM+2*pad, 16+2*pad, 1)
@@ -65,6 +72,7 @@ struct ConvParams {
   CUtensorMap tmPool;
   int tma_store;       // 1: use the maps above
   int epi_bytes;       // shared memory of the staging tiles (0 when tma_store == 0)
+  int epi_bufs;        // staging tiles per epilogue warp (1, or 2: the next group is staged while the TMA reads the last)
   int H, W, NB;        // input spatial size and batch
   int n_seg;           // K segments; segment s reads seg_kb[s] channel blocks from tmA[seg_map[s]]
   int seg_map[kMaxSeg];
@@ -99,7 +107,9 @@ struct ConvParams {
   // as immediate-indexed constant operands: no shared-memory broadcast reads on the L1 data pipe these layers are
   // bound by (it is shared with the tensor core's operand reads).
   int const_affine;
-  float c_bias[64], c_scale[64], c_shift[64];
+  alignas(16) float c_bias[64];
+  alignas(16) float c_scale[64];
+  alignas(16) float c_shift[64];
   // fp16 storage only: incremented once per (thread, 32-channel chunk) in which a value was clamped to +-65504 by the
   // saturating pack, so a checkpoint whose activations leave fp16's range cannot clip silently (itmo_saturation_count)
   unsigned long long* sat_count;
@@ -225,6 +235,39 @@ __device__ __forceinline__ void quad_transpose_16B(uint32_t (&t)[16], int lane) 
   }
 }
 
+// Packed fp32 pairs (FADD2 / FFMA2 on sm_100: two lanes of fp32 arithmetic per issued instruction, same rounding as the
+// scalar forms). The specialised epilogues are bound by their instruction issue, so the affine and the head use them.
+__device__ __forceinline__ uint64_t f2_pack(float a, float b) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
+  return r;
+}
+__device__ __forceinline__ void f2_unpack(uint64_t v, float& a, float& b) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v));
+}
+__device__ __forceinline__ uint64_t f2_add(uint64_t a, uint64_t b) {
+  uint64_t r;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ uint64_t f2_fma(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
+// (r0, r1) = max(acc + bias, 0) for two adjacent channels
+__device__ __forceinline__ void relu_bias2(uint32_t v0, uint32_t v1, uint64_t b01, float& r0, float& r1) {
+  float u0, u1;
+  f2_unpack(f2_add(f2_pack(__uint_as_float(v0), __uint_as_float(v1)), b01), u0, u1);
+  r0 = fmaxf(u0, 0.f);
+  r1 = fmaxf(u1, 0.f);
+}
+__device__ __forceinline__ void relu_bias2(uint32_t v0, uint32_t v1, float b0, float b1, float& r0, float& r1) {
+  relu_bias2(v0, v1, f2_pack(b0, b1), r0, r1);
+}
+// adjacent pair of a by-value parameter vector as one 64-bit constant-bank operand
+__device__ __forceinline__ uint64_t cpair(const float* v, int i) { return *reinterpret_cast<const uint64_t*>(v + i); }
+
 // y = ReLU(acc + bias) * scale + shift on one 32-column accumulator chunk (kStats: training forward, identity
 // affine; kLinear: no ReLU, the data-gradient convolutions). The vectors are read as 128-bit broadcasts.
 template <bool kStats, bool kLinear>
@@ -336,7 +379,238 @@ __device__ __forceinline__ void issue_kb(uint32_t tmem_d, uint32_t a_lo, uint32_
 // images, the fp32 mode's split accumulators) take the generic issue loop.
 __host__ __device__ constexpr int natural_nm(int block_n) { return block_n >= 256 ? 1 : block_n == 128 ? 2 : 4; }
 
-template <typename Elem, int BLOCK_N, int SWZ>
+
+// ------------------------------------------------------------------------------------------------------------------
+// Specialised epilogues of the inference forward pass (EpiKind != kEpiGeneric), 16-bit element types, tile shape
+// nm == natural_nm(BLOCK_N), one accumulator per M block. Everything the generic loop decides per chunk at run time
+// is a template parameter here, the (M block, channel group, half) loops are fully unrolled, so column offsets — and
+// with kEpiConstAffine the bias / scale / shift operands — are compile-time constants.
+//   work item  = one M block (16 x 8 pixels) x one channel group (64 channels; 32 when BLOCK_N == 32); a warp handles
+//                its TMEM lane quarter = 4 rows x 8 pixels of the block. The two warp sets split the items.
+//   per item   : both tcgen05.ld of the group in flight together -> y = max(acc + b, 0) * s + t -> pack -> swizzled
+//                staging tile (row = pixel) [-> 2x2 max-pool of the 4 x 8 pixels out of the staging tile] -> one lane
+//                issues the cp.async.bulk.tensor store(s). With two staging tiles per warp the next item is staged
+//                while the TMA engine still reads the previous one.
+//   kEpiHead   : no activation store; the 64 -> 3 head (model.py:276), sigmoid and predict.py:64's truncation on the
+//                fp32 post-BN registers.
+template <typename Elem, int BLOCK_N, int EPI>
+__device__ __forceinline__ void epilogue_fast(const ConvParams& p, uint32_t tmem_base, uint64_t* tmem_full_bar,
+                                              uint64_t* tmem_empty_bar, uint8_t* epi_stage, const float* s_bias,
+                                              const float* s_scale, const float* s_shift, const float* s_head,
+                                              int warp_idx, int lane) {
+  constexpr int kKind = EPI & 15;
+  constexpr bool kConst = (EPI & kEpiConstAffine) != 0;
+  constexpr bool kPool = kKind == kEpiConvPool;
+  constexpr bool kHead = kKind == kEpiHead;
+  constexpr bool kConvT = kKind == kEpiConvT;
+  constexpr bool kF16 = ElemTraits<Elem>::kFmt == sm100::kFmtF16;
+  constexpr int NM = natural_nm(BLOCK_N);
+  constexpr int kRowB = BLOCK_N >= 64 ? 128 : 64;   // bytes of one staged pixel row
+  constexpr int kGroupCh = kRowB / 2;               // channels per work item
+  constexpr int kGroups = BLOCK_N / kGroupCh;
+  constexpr int kHalves = kGroupCh / 32;            // tcgen05.ld x32 per item
+  constexpr int kStageB = 40 * kRowB;               // 32 pixel rows + 8 pooled rows
+  constexpr int kTileW = kBlkW * NM;
+  static_assert(!kConst || kConvT || BLOCK_N <= 64, "constant-bank affine: cout <= 64");
+  static_assert(!kHead || (BLOCK_N == 64 && kConst), "fused head: conv2d_14 only");
+  static_assert(sizeof(Elem) == 2, "16-bit element types");
+
+  const int ew = warp_idx - 4;            // 0..7
+  const int q = warp_idx & 3;             // TMEM lane quarter this warp may read
+  const int ws = ew >> 2;                 // warp set 0 / 1
+  const int r = 4 * q + (lane >> 3);      // pixel row inside the 16x8 M block
+  const int c = lane & 7;                 // pixel column inside the M block
+  const int tiles_x = p.W / kTileW;
+  const int tiles_y = p.H / kBlkH;
+  const int total_tiles = p.NB * tiles_y * tiles_x * p.n_tiles;
+  constexpr uint32_t buf_cols = uint32_t(NM * BLOCK_N);
+  uint8_t* const stage0 = epi_stage + ew * p.epi_bufs * kStageB;
+  const int sw_out = kRowB == 128 ? (lane & 7) : ((lane >> 1) & 3);
+  const bool count_sat = kF16 && p.sat_count != nullptr;
+  int buf = 0;
+  int acc = 0;
+  uint32_t acc_phase = 0;
+  for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+    const int n_tile = tile % p.n_tiles;
+    int m = tile / p.n_tiles;
+    const int tx = m % tiles_x;
+    m /= tiles_x;
+    const int ty = m % tiles_y;
+    const int img = m / tiles_y;
+
+    sm100::mbar_wait_relaxed(&tmem_full_bar[acc], acc_phase, 200);
+    sm100::tc_fence_after_sync();
+    const uint32_t taddr = tmem_base + (uint32_t(32 * q) << 16) + uint32_t(acc) * buf_cols;
+    if (!(p.dbg & 32)) {   // 32: timing experiment without the epilogue work
+    // M blocks of this warp set; NOT unrolled (j only moves the TMEM column and the x coordinate): the item body is
+    // 150-500 instructions and the kernel already fills most of the instruction cache
+#pragma unroll 1
+    for (int j = (NM > 1 ? ws : 0); j < NM; j += (NM > 1 ? 2 : 1)) {
+      uint64_t hh0 = 0ull, hh1 = 0ull, hh2 = 0ull;   // head sums, (even channels, odd channels) as packed fp32 pairs
+#pragma unroll
+      for (int g = 0; g < kGroups; ++g) {
+        if (NM == 1 && (g & 1) != ws) continue;
+        uint32_t v[kHalves][32];
+#pragma unroll
+        for (int h = 0; h < kHalves; ++h)
+          sm100::tmem_ld_32x32b_x32(taddr + uint32_t(j * BLOCK_N + g * kGroupCh + h * 32), v[h]);
+        uint8_t* const st_out = stage0 + buf * kStageB;
+        if constexpr (!kHead) {
+          // the bulk store that last read this staging tile must be done with it
+          if (lane == 0) {
+            if (p.epi_bufs == 2) sm100::tma_store_wait_read<1>();
+            else sm100::tma_store_wait_read<0>();
+          }
+          __syncwarp();
+        }
+        sm100::tmem_ld_wait();
+        uint32_t m2 = 0;
+#pragma unroll
+        for (int h = 0; h < kHalves; ++h) {
+          const int col = g * kGroupCh + h * 32;                      // compile-time after unrolling
+          float f[32];
+          if constexpr (kHead) {
+            // the BN affine is folded into the head's weights (see the kernel's setup): only max(acc + b, 0) here
+#pragma unroll
+            for (int i = 0; i < 32; i += 2) relu_bias2(v[h][i], v[h][i + 1], cpair(p.c_bias, col + i), f[i], f[i + 1]);
+          } else if constexpr (kConst) {
+            const int cc = kConvT ? (col & 63) : col;                 // transposed conv: cout == 64
+#pragma unroll
+            for (int i = 0; i < 32; i += 2) {
+              float r0, r1;
+              relu_bias2(v[h][i], v[h][i + 1], cpair(p.c_bias, cc + i), r0, r1);
+              f2_unpack(f2_fma(f2_pack(r0, r1), cpair(p.c_scale, cc + i), cpair(p.c_shift, cc + i)), f[i], f[i + 1]);
+            }
+          } else {
+            const int co0 = kConvT ? ((n_tile * BLOCK_N + col) & (p.cout - 1)) : (n_tile * BLOCK_N + col);
+            const float4* bb = reinterpret_cast<const float4*>(s_bias + co0);
+            const float4* sc = reinterpret_cast<const float4*>(s_scale + co0);
+            const float4* sh = reinterpret_cast<const float4*>(s_shift + co0);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const float4 b4 = bb[i], s4 = sc[i], t4 = sh[i];
+              float r0, r1, r2, r3;
+              relu_bias2(v[h][4 * i], v[h][4 * i + 1], b4.x, b4.y, r0, r1);
+              relu_bias2(v[h][4 * i + 2], v[h][4 * i + 3], b4.z, b4.w, r2, r3);
+              f2_unpack(f2_fma(f2_pack(r0, r1), f2_pack(s4.x, s4.y), f2_pack(t4.x, t4.y)), f[4 * i], f[4 * i + 1]);
+              f2_unpack(f2_fma(f2_pack(r2, r3), f2_pack(s4.z, s4.w), f2_pack(t4.z, t4.w)), f[4 * i + 2], f[4 * i + 3]);
+            }
+          }
+          if constexpr (kHead) {
+            // even / odd channels accumulate in the two halves of a packed pair: 3 FFMA2 per channel pair
+#pragma unroll
+            for (int i = 0; i < 32; i += 4) {
+              const ulonglong2 w0 = *reinterpret_cast<const ulonglong2*>(s_head + 0 * 64 + col + i);
+              const ulonglong2 w1 = *reinterpret_cast<const ulonglong2*>(s_head + 1 * 64 + col + i);
+              const ulonglong2 w2 = *reinterpret_cast<const ulonglong2*>(s_head + 2 * 64 + col + i);
+              const uint64_t fa = f2_pack(f[i], f[i + 1]), fb = f2_pack(f[i + 2], f[i + 3]);
+              hh0 = f2_fma(fb, w0.y, f2_fma(fa, w0.x, hh0));
+              hh1 = f2_fma(fb, w1.y, f2_fma(fa, w1.x, hh1));
+              hh2 = f2_fma(fb, w2.y, f2_fma(fa, w2.x, hh2));
+            }
+          } else {
+            uint32_t pk[16];
+#pragma unroll
+            for (int i = 0; i < 16; ++i) pk[i] = pack2<Elem>(f[2 * i], f[2 * i + 1]);
+            if constexpr (kF16) {
+              // |max| of the packed pairs, two words per instruction (three-input VHMNMX with |.| operands)
+#pragma unroll
+              for (int i = 0; i < 16; i += 2) {
+                const __half2 a = __habs2(*reinterpret_cast<const __half2*>(&pk[i]));
+                const __half2 b = __habs2(*reinterpret_cast<const __half2*>(&pk[i + 1]));
+                const __half2 mm = __hmax2(__hmax2(*reinterpret_cast<const __half2*>(&m2), a), b);
+                m2 = *reinterpret_cast<const uint32_t*>(&mm);
+              }
+            }
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+              *reinterpret_cast<uint4*>(st_out + lane * kRowB + (((h * 4 + k) ^ sw_out) << 4)) =
+                  make_uint4(pk[4 * k], pk[4 * k + 1], pk[4 * k + 2], pk[4 * k + 3]);
+          }
+        }
+        if constexpr (!kHead) {
+          if constexpr (kF16) {
+            // a value the saturating pack clamped reads back as +-65504 (0x7BFF)
+            m2 &= 0x7FFF7FFFu;
+            if (count_sat && ((m2 & 0xFFFFu) >= 0x7BFFu || (m2 >> 16) >= 0x7BFFu)) atomicAdd(p.sat_count, 1ull);
+          }
+          if constexpr (kPool) {
+            // 2x2 max-pool of the warp's 4 x 8 pixels out of the staging tile: lane = (pooled pixel, 16-byte piece)
+            __syncwarp();
+            uint8_t* const st_pool = st_out + 32 * kRowB;
+            const int pp = lane >> 2, k = lane & 3;
+            const int p00 = (2 * (pp >> 2)) * 8 + 2 * (pp & 3);
+            const int sw_p = kRowB == 128 ? (pp & 7) : ((pp >> 1) & 3);
+#pragma unroll
+            for (int h = 0; h < kHalves; ++h) {
+              auto piece = [&](int px) {
+                const int sw = kRowB == 128 ? (px & 7) : ((px >> 1) & 3);
+                return *reinterpret_cast<const uint4*>(st_out + px * kRowB + (((h * 4 + k) ^ sw) << 4));
+              };
+              const uint4 a4 = piece(p00), b4v = piece(p00 + 1), c4 = piece(p00 + 8), d4 = piece(p00 + 9);
+              uint4 m4;
+              m4.x = max2<Elem>(max2<Elem>(a4.x, b4v.x), max2<Elem>(c4.x, d4.x));
+              m4.y = max2<Elem>(max2<Elem>(a4.y, b4v.y), max2<Elem>(c4.y, d4.y));
+              m4.z = max2<Elem>(max2<Elem>(a4.z, b4v.z), max2<Elem>(c4.z, d4.z));
+              m4.w = max2<Elem>(max2<Elem>(a4.w, b4v.w), max2<Elem>(c4.w, d4.w));
+              *reinterpret_cast<uint4*>(st_pool + pp * kRowB + (((h * 4 + k) ^ sw_p) << 4)) = m4;
+            }
+          }
+          sm100::fence_proxy_async_smem();   // generic-proxy writes -> visible to the TMA (async proxy)
+          __syncwarp();
+          if (lane == 0) {
+            const int ng = n_tile * BLOCK_N + g * kGroupCh;          // first column of the staged group
+            const int x0 = tx * kTileW + j * kBlkW, y0 = ty * kBlkH + 4 * q;
+            if constexpr (kConvT) {
+              const int a_row = ng >> (p.cout_log2 + 1);               // kernel row a of this column group
+              sm100::tma_store_4d(&p.tmOut[a_row], st_out, ng - (a_row << (p.cout_log2 + 1)), x0, y0, img);
+            } else {
+              sm100::tma_store_4d(&p.tmOut[0], st_out, ng, x0, y0, img);
+            }
+            if constexpr (kPool) sm100::tma_store_4d(&p.tmPool, st_out + 32 * kRowB, ng, x0 >> 1, y0 >> 1, img);
+            sm100::tma_store_commit();
+          }
+          buf ^= p.epi_bufs - 1;
+        }
+      }
+      if constexpr (kHead) {
+        // Conv2D(3, 1, activation='sigmoid') (model.py:276) on the post-BN fp32 values
+        const int y = ty * kBlkH + r, x = tx * kTileW + j * kBlkW + c;
+        float e0, o0, e1, o1, e2, o2;
+        f2_unpack(hh0, e0, o0);
+        f2_unpack(hh1, e1, o1);
+        f2_unpack(hh2, e2, o2);
+        const float z0 = (e0 + o0) + s_head[192], z1 = (e1 + o1) + s_head[193], z2 = (e2 + o2) + s_head[194];
+        const float q0 = 1.f / (1.f + expf(-z0)), q1 = 1.f / (1.f + expf(-z1)), q2 = 1.f / (1.f + expf(-z2));
+        const size_t pix = (size_t(img) * p.H + y) * p.W + x;
+        if (p.head_dtype == kHeadF32) {
+          float* dst = reinterpret_cast<float*>(p.head_out) + pix * 3;
+          dst[0] = q0;
+          dst[1] = q1;
+          dst[2] = q2;
+        } else {
+          // predict.py:64  (pred * 255).astype('uint8')  -> fp32 multiply, truncation toward zero
+          uint8_t* dst = reinterpret_cast<uint8_t*>(p.head_out) + pix * 3;
+          dst[0] = static_cast<uint8_t>(static_cast<int>(q0 * 255.f));
+          dst[1] = static_cast<uint8_t>(static_cast<int>(q1 * 255.f));
+          dst[2] = static_cast<uint8_t>(static_cast<int>(q2 * 255.f));
+        }
+      }
+    }
+    }
+    // accumulators drained: hand the TMEM buffer back to the MMA warp
+    sm100::tc_fence_before_sync();
+    __syncwarp();
+    if (lane == 0) sm100::mbar_arrive(&tmem_empty_bar[acc]);
+    acc ^= 1;
+    if (acc == 0) acc_phase ^= 1;
+  }
+  if constexpr (!kHead) {
+    if (lane == 0) sm100::tma_store_wait_all<0>();   // staging tiles stay valid until the TMA has read them
+  }
+}
+
+template <typename Elem, int BLOCK_N, int SWZ, int EPI = kEpiGeneric>
 __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid_constant__ ConvParams p) {
   using Cfg = ConvCfg<Elem, BLOCK_N, SWZ>;
   constexpr bool kTF32 = ElemTraits<Elem>::kTF32;
@@ -422,8 +696,23 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
   if (with_stats)
     for (int i = threadIdx.x; i < kNumEpiWarps * 2 * p.cout; i += blockDim.x) s_stat[i] = 0.f;
   if (p.head_dtype != kHeadNone) {
-    for (int i = threadIdx.x; i < 3 * 64 + 3; i += blockDim.x)
-      s_head[i] = (i < 3 * 64) ? p.head_w[i] : p.head_b[i - 3 * 64];
+    if constexpr ((EPI & 15) == kEpiHead) {
+      // specialised head: z_k = sum_c w_kc (r_c s_c + t_c) + b_k = sum_c (w_kc s_c) r_c + (b_k + sum_c w_kc t_c),
+      // r = max(acc + bias, 0): the BN affine of conv2d_14 moves into the head's weights (fp32, once per CTA)
+      for (int i = threadIdx.x; i < 3 * 64 + 3; i += blockDim.x) {
+        if (i < 3 * 64) {
+          s_head[i] = p.head_w[i] * p.c_scale[i & 63];
+        } else {
+          const int k = i - 3 * 64;
+          float acc = p.head_b[k];
+          for (int ch = 0; ch < 64; ++ch) acc = fmaf(p.head_w[k * 64 + ch], p.c_shift[ch], acc);
+          s_head[i] = acc;
+        }
+      }
+    } else {
+      for (int i = threadIdx.x; i < 3 * 64 + 3; i += blockDim.x)
+        s_head[i] = (i < 3 * 64) ? p.head_w[i] : p.head_b[i - 3 * 64];
+    }
   }
   sm100::tc_fence_before_sync();
   __syncthreads();
@@ -580,6 +869,10 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
     }
   } else if (warp_idx >= 4 && !(p.dbg & 256)) {  // 256: timing experiment without the epilogue warps
     // ===== epilogue warps: TMEM -> registers -> bias/ReLU/BN (-> pool / head) -> global =====
+    if constexpr (EPI != kEpiGeneric && sizeof(Elem) == 2) {
+      epilogue_fast<Elem, BLOCK_N, EPI>(p, tmem_base, tmem_full_bar, tmem_empty_bar, epi_stage, s_bias, s_scale, s_shift,
+                                        s_head, warp_idx, lane);
+    } else {
     const int ew = warp_idx - 4;            // 0..7
     const int q = warp_idx & 3;             // TMEM lane quarter this warp may read
     const int ws = ew >> 2;                 // warp set 0 / 1: the two sets split the tile's work items
@@ -865,6 +1158,7 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
       if (acc == 0) acc_phase ^= 1;
     }
     if (p.tma_store && lane == 0) sm100::tma_store_wait_all<0>();   // staging tiles stay valid until the TMA has read them
+    }
   }
 
   // ---------------------------------------------------------------- teardown

@@ -333,6 +333,43 @@ int launch_conv_t(const itmo::ConvParams& p, int total_tiles, int smem_bytes, cu
   return ITMO_OK;
 }
 
+// Specialised-epilogue instantiations (itmo::EpiKind): the shapes of the inference forward pass. Returns -1 when the
+// combination is not compiled (the caller then takes the generic kernel).
+template <typename Elem, int BLOCK_N, int SWZ, int EPI>
+int launch_conv_epi(const itmo::ConvParams& p, int total_tiles, int smem_bytes, cudaStream_t stream) {
+  auto kern = itmo::conv_igemm_kernel<Elem, BLOCK_N, SWZ, EPI>;
+  static bool configured = false;  // per template instantiation
+  if (!configured) {
+    ITMO_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, itmo::kSmemLimit));
+    configured = true;
+  }
+  const int grid = std::min(total_tiles, num_sms());
+  kern<<<grid, itmo::kNumThreads, smem_bytes, stream>>>(p);
+  ITMO_CUDA(cudaGetLastError());
+  return ITMO_OK;
+}
+
+template <typename Elem>
+int launch_conv_fast(int block_n, int swz, int epi, const itmo::ConvParams& p, int total_tiles, int smem_bytes,
+                     cudaStream_t stream) {
+  using namespace itmo;
+  constexpr int C = kEpiConstAffine;
+#define ITMO_FAST(BN, SW, EP) \
+  if (block_n == BN && swz == SW && epi == (EP)) return launch_conv_epi<Elem, BN, SW, (EP)>(p, total_tiles, smem_bytes, stream)
+  ITMO_FAST(32, 64, kEpiConvPool | C);    // conv2d_2
+  ITMO_FAST(64, 64, kEpiConv | C);        // conv2d_3
+  ITMO_FAST(64, 128, kEpiConvPool | C);   // conv2d_4
+  ITMO_FAST(128, 128, kEpiConv);          // conv2d_5, conv2d_13
+  ITMO_FAST(128, 128, kEpiConvPool);      // conv2d_6
+  ITMO_FAST(256, 128, kEpiConv);          // conv2d_7, 9 ... 12
+  ITMO_FAST(256, 128, kEpiConvPool);      // conv2d_8
+  ITMO_FAST(256, 128, kEpiConvT);         // conv2d_transpose_1 ... 3
+  ITMO_FAST(256, 128, kEpiConvT | C);     // conv2d_transpose_4 (cout 64)
+  ITMO_FAST(64, 64, kEpiHead | C);        // conv2d_14 + head
+#undef ITMO_FAST
+  return -1;
+}
+
 template <typename Elem, int SWZ>
 int launch_conv_n(int block_n, const itmo::ConvParams& p, int total_tiles, int smem_bytes, cudaStream_t stream) {
   switch (block_n) {
@@ -447,7 +484,35 @@ int run_conv(const ConvArgs& a, cudaStream_t stream) {
   const bool tma_store = allow_tma_store && prec_is16(a.precision) && (a.out != nullptr || a.pooled != nullptr) &&
                          cout_log2 >= 5 && (conv || a.cout >= 64);
   const int epi_row = block_n >= 64 ? 128 : 64;
-  const int epi_bytes = tma_store ? itmo::kNumEpiWarps * 40 * epi_row : 0;
+  // ---- specialised epilogue (itmo::EpiKind) for the inference forward pass's shapes (ITMO_FAST_EPI=0: A/B)
+  static const int allow_fast = env_int("ITMO_FAST_EPI", 1);
+  static const int dbg_env = env_int("ITMO_DBG", 0);
+  static const int allow_const_env = env_int("ITMO_CONST_AFFINE", 1);
+  int epi = itmo::kEpiGeneric;
+  const int natural_nm = block_n >= 256 ? 1 : block_n == 128 ? 2 : 4;
+  if (allow_fast && prec_is16(a.precision) && acc_split == 1 && nm == natural_nm && !a.stats && !a.no_relu && !a.one_tap &&
+      (dbg_env & ~32) == 0) {
+    const bool can_const = a.h_bias && a.h_scale && a.h_shift && allow_const_env;
+    if (conv && a.head_dtype != itmo::kHeadNone) {
+      static const int fast_head = env_int("ITMO_FAST_HEAD", 1);
+      if (fast_head && !a.out && !a.pooled && can_const) epi = itmo::kEpiHead | itmo::kEpiConstAffine;
+    } else if (tma_store && a.out != nullptr && a.head_dtype == itmo::kHeadNone) {
+      if (conv) {
+        epi = a.pooled ? itmo::kEpiConvPool : itmo::kEpiConv;
+        if (can_const && rows == block_n && block_n <= 64) epi |= itmo::kEpiConstAffine;
+      } else {
+        epi = itmo::kEpiConvT;
+        if (can_const && a.cout == 64 && block_n == 256) epi |= itmo::kEpiConstAffine;
+      }
+    }
+  }
+  static const int fast_bufs = std::max(1, std::min(2, env_int("ITMO_EPI_BUFS", 1)));
+  int epi_bufs = (epi != itmo::kEpiGeneric && tma_store) ? fast_bufs : 1;
+  const int epi_one = itmo::kNumEpiWarps * 40 * epi_row;
+  // the second staging tile only where it does not cost the pipeline a stage it needs (streamed weights: 2 halo + 2 weight stages)
+  if (epi_bufs == 2 && itmo::kSmemLimit - 1024 - itmo::kAuxBytes - stats_bytes - 2 * epi_one < 2 * a_stage + 3 * b_stage)
+    epi_bufs = 1;
+  const int epi_bytes = tma_store ? epi_one * epi_bufs : 0;
   const int budget = itmo::kSmemLimit - 1024 - itmo::kAuxBytes - stats_bytes - epi_bytes;
   const int n_tiles = rows / block_n;
   int n_a, n_b, resident = 0;
@@ -479,6 +544,7 @@ int run_conv(const ConvArgs& a, cudaStream_t stream) {
   if (tma_store) {
     p.tma_store = 1;
     p.epi_bytes = epi_bytes;
+    p.epi_bufs = epi_bufs;
     if (a.out != nullptr) {
       if (conv) {
         rc = make_act_map(&p.tmOut[0], a.out, a.precision, a.cout, a.w, a.h, a.n, epi_row, 8, 4);
@@ -534,8 +600,9 @@ int run_conv(const ConvArgs& a, cudaStream_t stream) {
                  : a.precision == ITMO_PREC_FP32 ? itmo::kStoreSplit
                                                  : itmo::kStorePlain;
   static const int allow_const = env_int("ITMO_CONST_AFFINE", 1);
-  if (allow_const && a.h_bias && a.h_scale && a.h_shift && conv && !a.one_tap && n_tiles == 1 && a.cout == block_n &&
-      block_n <= 64 && !a.no_relu && !a.stats) {
+  if ((epi & itmo::kEpiConstAffine) ||
+      (allow_const && a.h_bias && a.h_scale && a.h_shift && conv && !a.one_tap && n_tiles == 1 && a.cout == block_n &&
+       block_n <= 64 && !a.no_relu && !a.stats)) {
     p.const_affine = 1;
     memcpy(p.c_bias, a.h_bias, a.cout * sizeof(float));
     memcpy(p.c_scale, a.h_scale, a.cout * sizeof(float));
@@ -555,6 +622,14 @@ int run_conv(const ConvArgs& a, cudaStream_t stream) {
   p.head_dtype = a.head_dtype;
   const int total_tiles = a.n * (a.h / itmo::kBlkH) * (a.w / (itmo::kBlkW * nm)) * n_tiles;
   if (a.stats_blocks) *a.stats_blocks = std::min(total_tiles, num_sms());   // = launch_conv_t's grid
+  if (epi != itmo::kEpiGeneric) {
+    const int rcf = a.precision == ITMO_PREC_BF16
+                        ? launch_conv_fast<__nv_bfloat16>(block_n, swz, epi, p, total_tiles, smem_bytes, stream)
+                        : launch_conv_fast<__half>(block_n, swz, epi, p, total_tiles, smem_bytes, stream);
+    if (rcf != -1) return rcf;
+    // not compiled for this shape: the generic kernel reads the same parameters (one staging tile per warp is a
+    // prefix of two)
+  }
   if (a.precision == ITMO_PREC_BF16) {
     if (swz == 128) return launch_conv_n<__nv_bfloat16, 128>(block_n, p, total_tiles, smem_bytes, stream);
     return launch_conv_n<__nv_bfloat16, 64>(block_n, p, total_tiles, smem_bytes, stream);
