@@ -404,13 +404,13 @@ __device__ __forceinline__ void epilogue_fast(const ConvParams& p, uint32_t tmem
   constexpr bool kHead = kKind == kEpiHead;
   constexpr bool kConvT = kKind == kEpiConvT;
   constexpr bool kF16 = ElemTraits<Elem>::kFmt == sm100::kFmtF16;
-  constexpr int NM = natural_nm(BLOCK_N);
+  const int nm = p.nm;                              // M blocks per tile: natural_nm(BLOCK_N) or half of it
   constexpr int kRowB = BLOCK_N >= 64 ? 128 : 64;   // bytes of one staged pixel row
   constexpr int kGroupCh = kRowB / 2;               // channels per work item
   constexpr int kGroups = BLOCK_N / kGroupCh;
   constexpr int kHalves = kGroupCh / 32;            // tcgen05.ld x32 per item
   constexpr int kStageB = 40 * kRowB;               // 32 pixel rows + 8 pooled rows
-  constexpr int kTileW = kBlkW * NM;
+  const int kTileW = kBlkW * nm;
   static_assert(!kConst || kConvT || BLOCK_N <= 64, "constant-bank affine: cout <= 64");
   static_assert(!kHead || (BLOCK_N == 64 && kConst), "fused head: conv2d_14 only");
   static_assert(sizeof(Elem) == 2, "16-bit element types");
@@ -423,7 +423,7 @@ __device__ __forceinline__ void epilogue_fast(const ConvParams& p, uint32_t tmem
   const int tiles_x = p.W / kTileW;
   const int tiles_y = p.H / kBlkH;
   const int total_tiles = p.NB * tiles_y * tiles_x * p.n_tiles;
-  constexpr uint32_t buf_cols = uint32_t(NM * BLOCK_N);
+  const uint32_t buf_cols = uint32_t(nm * BLOCK_N);
   uint8_t* const stage0 = epi_stage + ew * p.epi_bufs * kStageB;
   const int sw_out = kRowB == 128 ? (lane & 7) : ((lane >> 1) & 3);
   const bool count_sat = kF16 && p.sat_count != nullptr;
@@ -445,11 +445,12 @@ __device__ __forceinline__ void epilogue_fast(const ConvParams& p, uint32_t tmem
     // M blocks of this warp set; NOT unrolled (j only moves the TMEM column and the x coordinate): the item body is
     // 150-500 instructions and the kernel already fills most of the instruction cache
 #pragma unroll 1
-    for (int j = (NM > 1 ? ws : 0); j < NM; j += (NM > 1 ? 2 : 1)) {
+    for (int j = (nm > 1 ? ws : 0); j < nm; j += (nm > 1 ? 2 : 1)) {
+      if (nm == 1 && kGroups == 1 && ws != 0) break;   // a lone block with a single group stays with set 0
       uint64_t hh0 = 0ull, hh1 = 0ull, hh2 = 0ull;   // head sums, (even channels, odd channels) as packed fp32 pairs
 #pragma unroll
       for (int g = 0; g < kGroups; ++g) {
-        if (NM == 1 && (g & 1) != ws) continue;
+        if (kGroups > 1 && nm == 1 && (g & 1) != ws) continue;
         uint32_t v[kHalves][32];
 #pragma unroll
         for (int h = 0; h < kHalves; ++h)
@@ -789,7 +790,11 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
       uint32_t pa = 0, pb = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      const bool fast = S == 1 && nm == natural_nm(BLOCK_N) && !(p.dbg & (64 | 1024));  // 1024: force the generic loop
+      // the unrolled issue path exists for the natural tile and, for the 64-column / 128-byte layers (conv2d_4: with
+      // two M blocks instead of four its weights stay resident), for half of it
+      constexpr bool kHalfNm = BLOCK_N == 64 && SWZ == 128;
+      const bool fast = S == 1 && (nm == natural_nm(BLOCK_N) || (kHalfNm && nm == natural_nm(BLOCK_N) / 2)) &&
+                        !(p.dbg & (64 | 1024));  // 1024: force the generic loop
       const bool nowait = (p.dbg & 128) != 0;   // timing experiment: the issuing thread never waits on a barrier
       if (p.b_resident && !nowait) {
         sm100::mbar_wait(&b_full[0], 0);
@@ -808,7 +813,10 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
           uint32_t a_row_lo = sm100::smem_desc_lo(sm100::smem_u32(smem_a + sa * p.a_stage_bytes));
           if (fast) {
             constexpr int kNM = natural_nm(BLOCK_N);
-            if (p.taps == 9)
+            if (kHalfNm && nm != kNM)
+              issue_kb<kTF32, (kHalfNm ? kNM / 2 : kNM), Cfg::kKSteps, SWZ, BLOCK_N, true>(
+                  tmem_d, a_row_lo, a_hi, b_hi, idesc, kb != 0, p.b_resident != 0, b_res_lo, b_lo0, b_full, b_empty, sb, pb, n_b);
+            else if (p.taps == 9)
               issue_kb<kTF32, kNM, Cfg::kKSteps, SWZ, BLOCK_N, true>(tmem_d, a_row_lo, a_hi, b_hi, idesc, kb != 0, p.b_resident != 0,
                                                                      b_res_lo, b_lo0, b_full, b_empty, sb, pb, n_b);
             else

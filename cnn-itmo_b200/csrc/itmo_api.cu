@@ -470,6 +470,17 @@ int run_conv(const ConvArgs& a, cudaStream_t stream) {
   if (force_nm > 0) nm = std::min(force_nm, nm);
   while (nm > 1 && a.w % (itmo::kBlkW * nm)) nm >>= 1;
   const int bk = int(swz / es);
+  // conv2d_4 (64 -> 64 channels, 128-byte rows): with four M blocks the 78 KB halo stages leave no room for the 72 KB
+  // of weights, which then stream through a two-stage ring whose refill latency is exposed on every tap. Two M blocks
+  // keep the weights resident (ITMO_HALF_NM=0: A/B).
+  static const int allow_half_nm = env_int("ITMO_HALF_NM", 1);
+  if (allow_half_nm && conv && taps == 9 && prec_is16(a.precision) && block_n == 64 && swz == 128 && nm == 4 && rows == block_n &&
+      acc_split == 1 && force_nm == 0) {
+    const int ks = k_mult(a.precision) * cin / bk * taps * block_n * swz;          // all weight tiles
+    const int a4 = (swz * (itmo::kBlkW * 4 + 2) * (itmo::kBlkH + 2) + 1023) / 1024 * 1024;
+    const int room = itmo::kSmemLimit - 1024 - itmo::kAuxBytes - itmo::kNumEpiWarps * 40 * 128 - (a.stats ? itmo::kNumEpiWarps * 2 * a.cout * 4 : 0);
+    if (ks + 2 * a4 > room) nm = 2;
+  }
   const int halo_w = itmo::kBlkW * nm + 2 * pad, halo_h = itmo::kBlkH + 2 * pad;
   const int a_stage = (swz * halo_w * halo_h + 1023) / 1024 * 1024;
   const int b_stage = block_n * swz;
@@ -490,7 +501,7 @@ int run_conv(const ConvArgs& a, cudaStream_t stream) {
   static const int allow_const_env = env_int("ITMO_CONST_AFFINE", 1);
   int epi = itmo::kEpiGeneric;
   const int natural_nm = block_n >= 256 ? 1 : block_n == 128 ? 2 : 4;
-  if (allow_fast && prec_is16(a.precision) && acc_split == 1 && nm == natural_nm && !a.stats && !a.no_relu && !a.one_tap &&
+  if (allow_fast && prec_is16(a.precision) && acc_split == 1 && (nm == natural_nm || (block_n == 64 && swz == 128 && nm == 2)) && !a.stats && !a.no_relu && !a.one_tap &&
       (dbg_env & ~32) == 0) {
     const bool can_const = a.h_bias && a.h_scale && a.h_shift && allow_const_env;
     if (conv && a.head_dtype != itmo::kHeadNone) {

@@ -26,8 +26,35 @@ constexpr int kRgbHaloH = kRgbTileH + 2, kRgbHaloW = kRgbTileW + 2;
 // the epilogue's FFMAs take them as immediate-indexed constant operands — no shared-memory reads at all (the 24
 // broadcast reads per pixel row were ~40 % of this kernel's L1 data-pipe wavefronts, its bottleneck).
 struct RgbAffine {
-  float bias[32], scale[32], shift[32];
+  alignas(16) float bias[32];
+  alignas(16) float scale[32];
+  alignas(16) float shift[32];
 };
+
+// K slot s of the im2col row (0..31, twice: against w_hi and w_lo): kernel row dy = s / 10, j = s % 10 = 3 * dx + ch; the
+// tenth slot of a kernel row and slots 30, 31 are padding (zero weights). Ten slots per kernel row keep the 16-bit pairs
+// inside one kernel row, so a pair is two adjacent input bytes.
+__device__ __forceinline__ int rgb_k_tap(int s) {
+  const int dy = s / 10, j = s - dy * 10;
+  return (dy < 3 && j < 9) ? dy * 9 + j : -1;
+}
+
+// Two raw bytes -> two exact 16-bit floats. fp16 without an integer conversion: 0x6400 | b is the fp16 number 1024 + b
+// (exact for b < 256) and one packed subtraction removes the offset. `sel` picks the two bytes of q (PRMT selector):
+// 0x4140 = bytes 0, 1; 0x4342 = bytes 2, 3.
+template <typename Elem>
+__device__ __forceinline__ uint32_t bytes_to_pair(uint32_t q, uint32_t sel) {
+  if constexpr (ElemTraits<Elem>::kFmt == sm100::kFmtF16) {
+    const uint32_t w = __byte_perm(q, 0x64646464u, sel);
+    const uint32_t off = 0x64006400u;
+    const __half2 r = __hsub2(*reinterpret_cast<const __half2*>(&w), *reinterpret_cast<const __half2*>(&off));
+    return *reinterpret_cast<const uint32_t*>(&r);
+  } else {
+    // bf16 has 8 significand bits: no offset leaves 256 consecutive integers exact, so convert (bf16 is the opt-in mode)
+    const uint32_t lo = (sel & 0xFu) * 8u, hi = ((sel >> 8) & 0xFu) * 8u;
+    return pack2<Elem>(float((q >> lo) & 0xFFu), float((q >> hi) & 0xFFu));
+  }
+}
 
 template <typename Elem, typename InT, bool kConstAffine = false>
 __global__ void __launch_bounds__(128, 8) rgb_conv_tc_kernel(const InT* __restrict__ in, Elem* __restrict__ out,
@@ -57,8 +84,9 @@ __global__ void __launch_bounds__(128, 8) rgb_conv_tc_kernel(const InT* __restri
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
         const int k0 = (c8 & 3) * 8 + 2 * i;
-        float a = k0 < 27 ? w_hwio[k0 * 32 + tid] : 0.f;
-        float b = k0 + 1 < 27 ? w_hwio[(k0 + 1) * 32 + tid] : 0.f;
+        const int t0 = rgb_k_tap(k0), t1 = rgb_k_tap(k0 + 1);
+        float a = t0 >= 0 ? w_hwio[t0 * 32 + tid] : 0.f;
+        float b = t1 >= 0 ? w_hwio[t1 * 32 + tid] : 0.f;
         if (c8 >= 4) {  // remainder after the 16-bit rounding
           a -= float(Elem(a));
           b -= float(Elem(b));
@@ -96,34 +124,54 @@ __global__ void __launch_bounds__(128, 8) rgb_conv_tc_kernel(const InT* __restri
   // epilogue of the current tile. Needs a 4-byte aligned input pointer (W is a multiple of 32, so every row is).
   constexpr int kWordsPerRow = 26, kWords = kRgbHaloH * kWordsPerRow;   // 156
   const bool fast_u8 = sizeof(InT) == 1 && (reinterpret_cast<uintptr_t>(in) & 3) == 0;
-  auto fetch_word = [&](int tile, int idx) -> uint32_t {
-    if (idx >= kWords || tile >= total) return 0u;
-    const int tx = tile % tiles_x;
-    const int ty = (tile / tiles_x) % tiles_y;
-    const int img = tile / (tiles_x * tiles_y);
-    const int hy = idx / kWordsPerRow, k = idx - hy * kWordsPerRow;
-    const int yy = ty * kRgbTileH + hy - 1;
-    const int off = tx * kRgbTileW * 3 - 4 + 4 * k;             // byte offset inside the image row
+  // Tile coordinates advance by gridDim.x tiles per iteration: the stride is decomposed ONCE into (images, tile rows,
+  // tile columns) and the coordinates move by adds with carries — the per-tile divisions by run-time values (seven of
+  // them, ~250 integer instructions per warp and tile) were 40 % of this kernel's issue slots, its bottleneck.
+  const int per_img = tiles_x * tiles_y;
+  const int st_img = int(gridDim.x) / per_img, st_rem = int(gridDim.x) - st_img * per_img;
+  const int st_ty = st_rem / tiles_x, st_tx = st_rem - st_ty * tiles_x;
+  int img = int(blockIdx.x) / per_img;
+  int ty = (int(blockIdx.x) - img * per_img) / tiles_x;
+  int tx = int(blockIdx.x) - img * per_img - ty * tiles_x;
+  auto advance = [&](int& ax, int& ay, int& ai) {
+    ax += st_tx;
+    if (ax >= tiles_x) {
+      ax -= tiles_x;
+      ++ay;
+    }
+    ay += st_ty;
+    if (ay >= tiles_y) {
+      ay -= tiles_y;
+      ++ai;
+    }
+    ai += st_img;
+  };
+  // this thread's two halo words: (halo row, word) are loop-invariant
+  const int hy0 = tid / kWordsPerRow, k0 = tid - hy0 * kWordsPerRow;
+  const int hy1 = (tid + 128) / kWordsPerRow, k1 = (tid + 128) - hy1 * kWordsPerRow;
+  const bool has1 = tid + 128 < kWords;
+  auto fetch_word = [&](int ax, int ay, int ai, int hy, int k) -> uint32_t {
+    const int yy = ay * kRgbTileH + hy - 1;
+    const int off = ax * (kRgbTileW * 3) - 4 + 4 * k;           // byte offset inside the image row
     if (yy < 0 || yy >= H || off < 0 || off >= 3 * W) return 0u;  // 'same' padding (whole words: 3*W % 4 == 0)
     return __ldg(reinterpret_cast<const uint32_t*>(reinterpret_cast<const uint8_t*>(in) +
-                                                   (size_t(img) * H + yy) * W * 3 + off));
+                                                   (size_t(ai) * H + yy) * W * 3 + off));
   };
   uint32_t nw0 = 0, nw1 = 0;
-  if (fast_u8) {
-    nw0 = fetch_word(blockIdx.x, tid);
-    nw1 = fetch_word(blockIdx.x, tid + 128);
+  if (fast_u8 && int(blockIdx.x) < total) {
+    nw0 = fetch_word(tx, ty, img, hy0, k0);
+    if (has1) nw1 = fetch_word(tx, ty, img, hy1, k1);
   }
+  int ntx = tx, nty = ty, nimg = img;
+  advance(ntx, nty, nimg);
 
   for (int tile = blockIdx.x; tile < total; tile += gridDim.x) {
-    const int tx = tile % tiles_x;
-    const int ty = (tile / tiles_x) % tiles_y;
-    const int img = tile / (tiles_x * tiles_y);
     const int x0 = tx * kRgbTileW, y0 = ty * kRgbTileH;
 
     // ---- halo tile -> shared memory as floats (zero outside the image = 'same' padding)
     if (fast_u8) {
-      if (tid < kWords) s_raw[tid / kWordsPerRow][tid % kWordsPerRow] = nw0;
-      if (tid + 128 < kWords) s_raw[(tid + 128) / kWordsPerRow][(tid + 128) % kWordsPerRow] = nw1;
+      s_raw[hy0][k0] = nw0;
+      if (has1) s_raw[hy1][k1] = nw1;
     } else {
       for (int i = tid; i < kRgbHaloH * kRgbHaloW * 3; i += 128) {
         const int hy = i / (kRgbHaloW * 3), rem = i - hy * (kRgbHaloW * 3);
@@ -139,42 +187,43 @@ __global__ void __launch_bounds__(128, 8) rgb_conv_tc_kernel(const InT* __restri
       }
     }
     __syncthreads();
-    if (fast_u8) {   // next tile's words: in flight during the im2col, the MMA and the epilogue
-      nw0 = fetch_word(tile + gridDim.x, tid);
-      nw1 = fetch_word(tile + gridDim.x, tid + 128);
+    if (fast_u8 && tile + int(gridDim.x) < total) {   // next tile's words: in flight during the im2col, the MMA and the epilogue
+      nw0 = fetch_word(ntx, nty, nimg, hy0, k0);
+      if (has1) nw1 = fetch_word(ntx, nty, nimg, hy1, k1);
     }
 
-    // ---- im2col: k = dy*9 + dx*3 + ch = dy*9 + (9 consecutive halo values starting at pixel c)
+    // ---- im2col: slot s = dy*10 + j, j = 9 consecutive halo bytes starting at pixel c (see rgb_k_tap)
     {
-      float a[32];
+      uint32_t pr[16];   // the row's 16 pairs of 16-bit operands
       if constexpr (sizeof(InT) == 1) {
-        // 9 consecutive bytes from raw byte 3c + 1: three word reads + funnel shifts instead of 9 scalar reads
+        // 9 consecutive bytes from raw byte 3c + 1: three word reads + funnel shifts, then five PRMT + five packed
+        // subtractions per kernel row (bytes_to_pair) instead of 9 x (extract, I2F) + 5 packs
         const int sb = 3 * c + 1, w0 = sb >> 2;
         const uint32_t sh = uint32_t(sb & 3) * 8u;
 #pragma unroll
         for (int dy = 0; dy < 3; ++dy) {
           const uint32_t W0 = s_raw[r + dy][w0], W1 = s_raw[r + dy][w0 + 1], W2 = s_raw[r + dy][w0 + 2];
           const uint32_t q0 = __funnelshift_r(W0, W1, sh), q1 = __funnelshift_r(W1, W2, sh), q2 = W2 >> sh;
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            a[dy * 9 + j] = float((q0 >> (8 * j)) & 0xFFu);
-            a[dy * 9 + 4 + j] = float((q1 >> (8 * j)) & 0xFFu);
-          }
-          a[dy * 9 + 8] = float(q2 & 0xFFu);
+          pr[dy * 5 + 0] = bytes_to_pair<Elem>(q0, 0x4140u);
+          pr[dy * 5 + 1] = bytes_to_pair<Elem>(q0, 0x4342u);
+          pr[dy * 5 + 2] = bytes_to_pair<Elem>(q1, 0x4140u);
+          pr[dy * 5 + 3] = bytes_to_pair<Elem>(q1, 0x4342u);
+          pr[dy * 5 + 4] = bytes_to_pair<Elem>(q2, 0x4140u);   // (j = 8, padding slot: any finite value, its weight is 0)
         }
       } else {
 #pragma unroll
-        for (int dy = 0; dy < 3; ++dy)
+        for (int dy = 0; dy < 3; ++dy) {
 #pragma unroll
-          for (int j = 0; j < 9; ++j) a[dy * 9 + j] = s_halo[r + dy][c * 3 + j];
+          for (int jj = 0; jj < 4; ++jj)
+            pr[dy * 5 + jj] = pack2<Elem>(s_halo[r + dy][c * 3 + 2 * jj], s_halo[r + dy][c * 3 + 2 * jj + 1]);
+          pr[dy * 5 + 4] = pack2<Elem>(s_halo[r + dy][c * 3 + 8], 0.f);
+        }
       }
-#pragma unroll
-      for (int j = 27; j < 32; ++j) a[j] = 0.f;
+      pr[15] = 0u;
       const int sw = tid & 7;
 #pragma unroll
       for (int c4 = 0; c4 < 4; ++c4) {
-        const uint4 v = make_uint4(pack2<Elem>(a[c4 * 8 + 0], a[c4 * 8 + 1]), pack2<Elem>(a[c4 * 8 + 2], a[c4 * 8 + 3]),
-                                   pack2<Elem>(a[c4 * 8 + 4], a[c4 * 8 + 5]), pack2<Elem>(a[c4 * 8 + 6], a[c4 * 8 + 7]));
+        const uint4 v = make_uint4(pr[4 * c4], pr[4 * c4 + 1], pr[4 * c4 + 2], pr[4 * c4 + 3]);
         *reinterpret_cast<uint4*>(s_a + tid * 128 + ((c4 ^ sw) * 16)) = v;        // pairs with w_hi
         *reinterpret_cast<uint4*>(s_a + tid * 128 + (((c4 + 4) ^ sw) * 16)) = v;  // pairs with w_lo
       }
@@ -201,24 +250,23 @@ __global__ void __launch_bounds__(128, 8) rgb_conv_tc_kernel(const InT* __restri
     sm100::tmem_ld_32x32b_x32(tmem + (uint32_t(32 * warp) << 16), v);
     sm100::tmem_ld_wait();
     uint32_t pk[16];
+    const uint64_t in2 = f2_pack(in_scale, in_scale);
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {   // 128-bit broadcast reads: a quarter of the shared-memory wavefronts of scalar ones
-      float4 b4, sc4, sh4;
+    for (int i = 0; i < 16; ++i) {   // packed fp32 pairs: FFMA2, 2 x FMNMX, FFMA2 per channel pair
+      uint64_t b2, sc2, sh2;
       if constexpr (kConstAffine) {
-        b4 = make_float4(aff.bias[4 * i], aff.bias[4 * i + 1], aff.bias[4 * i + 2], aff.bias[4 * i + 3]);
-        sc4 = make_float4(aff.scale[4 * i], aff.scale[4 * i + 1], aff.scale[4 * i + 2], aff.scale[4 * i + 3]);
-        sh4 = make_float4(aff.shift[4 * i], aff.shift[4 * i + 1], aff.shift[4 * i + 2], aff.shift[4 * i + 3]);
+        b2 = cpair(aff.bias, 2 * i);
+        sc2 = cpair(aff.scale, 2 * i);
+        sh2 = cpair(aff.shift, 2 * i);
       } else {
-        b4 = reinterpret_cast<const float4*>(s_bias)[i];
-        sc4 = reinterpret_cast<const float4*>(s_scale)[i];
-        sh4 = reinterpret_cast<const float4*>(s_shift)[i];
+        b2 = *reinterpret_cast<const uint64_t*>(s_bias + 2 * i);
+        sc2 = *reinterpret_cast<const uint64_t*>(s_scale + 2 * i);
+        sh2 = *reinterpret_cast<const uint64_t*>(s_shift + 2 * i);
       }
-      const float f0 = fmaf(fmaxf(fmaf(__uint_as_float(v[4 * i]), in_scale, b4.x), 0.f), sc4.x, sh4.x);
-      const float f1 = fmaf(fmaxf(fmaf(__uint_as_float(v[4 * i + 1]), in_scale, b4.y), 0.f), sc4.y, sh4.y);
-      const float f2 = fmaf(fmaxf(fmaf(__uint_as_float(v[4 * i + 2]), in_scale, b4.z), 0.f), sc4.z, sh4.z);
-      const float f3 = fmaf(fmaxf(fmaf(__uint_as_float(v[4 * i + 3]), in_scale, b4.w), 0.f), sc4.w, sh4.w);
-      pk[2 * i] = pack2<Elem>(f0, f1);
-      pk[2 * i + 1] = pack2<Elem>(f2, f3);
+      float u0, u1, f0, f1;
+      f2_unpack(f2_fma(f2_pack(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1])), in2, b2), u0, u1);
+      f2_unpack(f2_fma(f2_pack(fmaxf(u0, 0.f), fmaxf(u1, 0.f)), sc2, sh2), f0, f1);
+      pk[i] = pack2<Elem>(f0, f1);
     }
     // The 32 pixels of a warp are 2 KB of contiguous output. Stage them in the (now idle) im2col tile with a
     // 16-byte-piece swizzle, then store 512 contiguous bytes per instruction instead of 32 pieces 64 B apart.
@@ -235,6 +283,10 @@ __global__ void __launch_bounds__(128, 8) rgb_conv_tc_kernel(const InT* __restri
       const int u = k * 32 + lane, px = u >> 2;
       dst[u] = *reinterpret_cast<const uint4*>(stage + px * 64 + (((u & 3) ^ ((px >> 1) & 3)) * 16));
     }
+    tx = ntx;
+    ty = nty;
+    img = nimg;
+    advance(ntx, nty, nimg);
   }
 
   sm100::tc_fence_before_sync();
