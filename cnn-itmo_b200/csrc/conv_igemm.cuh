@@ -56,7 +56,12 @@ enum StoreMode : int { kStorePlain = 0, kStoreTf32Rna = 1, kStoreSplit = 2 };
 // counted ~480 warp instructions per 32-column chunk in the generic loop, ~46 of them branches, against ~150 the
 // arithmetic needs, and the HBM-bound layers were bound by exactly that issue stream (two epilogue warps per
 // scheduler). | kEpiConstAffine: bias / scale / shift as constant-bank operands (cout <= 64).
-enum EpiKind : int { kEpiGeneric = 0, kEpiConv = 1, kEpiConvPool = 2, kEpiConvT = 3, kEpiHead = 4, kEpiConstAffine = 16 };
+// | kEpiPair: the kernel runs as CTA PAIRS (cluster of two CTAs on one TPC, tcgen05.mma.cta_group::2): the two CTAs
+// work on two horizontally adjacent tiles as one M = 256 MMA. Each CTA loads its own halo tile but only HALF of every
+// weight tile (the tensor core reads the other half from the peer's shared memory), so weight traffic L2 -> SMEM and
+// the weight-operand shared-memory reads per MMA halve: N = 64 MMAs go from 6 KB to 5 KB of operand reads each
+// (conv2d_14 is bound by exactly that), the N = 256 layers stream 4 KB instead of 8 KB of weights per MMA.
+enum EpiKind : int { kEpiGeneric = 0, kEpiConv = 1, kEpiConvPool = 2, kEpiConvT = 3, kEpiHead = 4, kEpiConstAffine = 16, kEpiPair = 32 };
 
 struct ConvParams {
   CUtensorMap tmA[4];  // activation sources: dims (C, W, H, N), box (BK, 8*NM+2*pad, 16+2*pad, 1)
@@ -324,7 +329,7 @@ struct ConvCfg {
 // only by compile-time constants in the start-address field (units of 16 bytes), so each MMA costs the issuing
 // thread two integer adds: at N <= 64 the tensor pipe retires an MMA every 40-48 clocks (tools/ubench/umma_rate.cu)
 // and a longer issue sequence per MMA becomes the bottleneck of the whole kernel. K step outer, M block inner.
-template <bool TF32, int NM, int KSTEPS, int SWZ, int BLOCK_N>
+template <bool TF32, int NM, int KSTEPS, int SWZ, int BLOCK_N, bool PAIR = false>
 __device__ __forceinline__ void issue_tap(uint32_t tmem_d, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo, uint32_t b_hi,
                                           uint32_t idesc, uint32_t have) {
 #pragma unroll
@@ -333,7 +338,8 @@ __device__ __forceinline__ void issue_tap(uint32_t tmem_d, uint32_t a_lo, uint32
 #pragma unroll
     for (int j = 0; j < NM; ++j) {
       const uint64_t da = (uint64_t(a_hi) << 32) | uint64_t(a_lo + uint32_t((j * kBlkW * SWZ + k * 32) >> 4));
-      sm100::umma_ss<TF32>(tmem_d + uint32_t(j * BLOCK_N), da, db, idesc, k == 0 ? have : 1u);
+      if constexpr (PAIR) sm100::umma_ss_pair(tmem_d + uint32_t(j * BLOCK_N), da, db, idesc, k == 0 ? have : 1u);
+      else sm100::umma_ss<TF32>(tmem_d + uint32_t(j * BLOCK_N), da, db, idesc, k == 0 ? have : 1u);
     }
   }
 }
@@ -342,13 +348,13 @@ __device__ __forceinline__ void issue_tap(uint32_t tmem_d, uint32_t a_lo, uint32
 // (NM M blocks, 3x3 or single tap): every descriptor is "stage base + compile-time constant". The issuing thread's
 // instructions between two MMAs are NOT hidden behind the tensor pipe beyond a few queued MMAs (measured: a 25-instruction
 // tap prologue cost ~40 clocks per MMA at N = 64), so the stream has to be this dense.
-template <bool TF32, int NM, int KSTEPS, int SWZ, int BLOCK_N, bool CONV>
+template <bool TF32, int NM, int KSTEPS, int SWZ, int BLOCK_N, bool CONV, bool PAIR = false>
 __device__ __forceinline__ void issue_kb(uint32_t tmem_d, uint32_t a_lo, uint32_t a_hi, uint32_t b_hi, uint32_t idesc,
                                          uint32_t have_first, bool resident, uint32_t b_res_lo, uint32_t b_lo0,
                                          uint64_t* b_full, uint64_t* b_empty, int& sb, uint32_t& pb, int n_b) {
   constexpr int kT = CONV ? 3 : 1;
   constexpr int kHaloW = kBlkW * NM + (CONV ? 2 : 0);
-  constexpr uint32_t kB16 = uint32_t(BLOCK_N * SWZ) >> 4;
+  constexpr uint32_t kB16 = uint32_t(BLOCK_N * SWZ / (PAIR ? 2 : 1)) >> 4;   // a CTA of a pair holds half of the rows
 #pragma unroll
   for (int ty = 0; ty < kT; ++ty) {
 #pragma unroll
@@ -362,10 +368,11 @@ __device__ __forceinline__ void issue_kb(uint32_t tmem_d, uint32_t a_lo, uint32_
         sm100::tc_fence_after_sync();
         b_lo = b_lo0 + uint32_t(sb) * kB16;
       }
-      issue_tap<TF32, NM, KSTEPS, SWZ, BLOCK_N>(tmem_d, a_lo + (uint32_t((ty * kHaloW + tx) * SWZ) >> 4), a_hi, b_lo, b_hi,
-                                                 idesc, tap == 0 ? have_first : 1u);
+      issue_tap<TF32, NM, KSTEPS, SWZ, BLOCK_N, PAIR>(tmem_d, a_lo + (uint32_t((ty * kHaloW + tx) * SWZ) >> 4), a_hi, b_lo, b_hi,
+                                                       idesc, tap == 0 ? have_first : 1u);
       if (!resident) {
-        sm100::umma_commit(&b_empty[sb]);  // frees this weight stage once the MMAs retire
+        if constexpr (PAIR) sm100::umma_commit_pair(&b_empty[sb]);
+        else sm100::umma_commit(&b_empty[sb]);  // frees this weight stage once the MMAs retire
         if (++sb == n_b) {
           sb = 0;
           pb ^= 1;
@@ -420,9 +427,17 @@ __device__ __forceinline__ void epilogue_fast(const ConvParams& p, uint32_t tmem
   const int ws = ew >> 2;                 // warp set 0 / 1
   const int r = 4 * q + (lane >> 3);      // pixel row inside the 16x8 M block
   const int c = lane & 7;                 // pixel column inside the M block
+  constexpr bool kPair = (EPI & kEpiPair) != 0;
+  const uint32_t cta_rank = kPair ? sm100::cluster_ctarank() : 0u;
   const int tiles_x = p.W / kTileW;
   const int tiles_y = p.H / kBlkH;
-  const int total_tiles = p.NB * tiles_y * tiles_x * p.n_tiles;
+  const int m_tiles = p.NB * tiles_y * tiles_x;
+  const int total_tiles = kPair ? (m_tiles >> 1) * p.n_tiles : m_tiles * p.n_tiles;
+  const int unit0 = kPair ? int(blockIdx.x >> 1) : int(blockIdx.x);
+  const int unit_stride = kPair ? int(gridDim.x >> 1) : int(gridDim.x);
+  // pair: the accumulators of both CTAs are handed back through the leader's barrier
+  const uint32_t empty_remote[2] = {kPair ? sm100::mapa_u32(&tmem_empty_bar[0], 0) : 0u,
+                                    kPair ? sm100::mapa_u32(&tmem_empty_bar[1], 0) : 0u};
   const uint32_t buf_cols = uint32_t(nm * BLOCK_N);
   uint8_t* const stage0 = epi_stage + ew * p.epi_bufs * kStageB;
   const int sw_out = kRowB == 128 ? (lane & 7) : ((lane >> 1) & 3);
@@ -430,9 +445,10 @@ __device__ __forceinline__ void epilogue_fast(const ConvParams& p, uint32_t tmem
   int buf = 0;
   int acc = 0;
   uint32_t acc_phase = 0;
-  for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-    const int n_tile = tile % p.n_tiles;
-    int m = tile / p.n_tiles;
+  for (int unit = unit0; unit < total_tiles; unit += unit_stride) {
+    const int n_tile = unit % p.n_tiles;
+    int m = unit / p.n_tiles;
+    if constexpr (kPair) m = 2 * m + int(cta_rank);
     const int tx = m % tiles_x;
     m /= tiles_x;
     const int ty = m % tiles_y;
@@ -602,7 +618,10 @@ __device__ __forceinline__ void epilogue_fast(const ConvParams& p, uint32_t tmem
     // accumulators drained: hand the TMEM buffer back to the MMA warp
     sm100::tc_fence_before_sync();
     __syncwarp();
-    if (lane == 0) sm100::mbar_arrive(&tmem_empty_bar[acc]);
+    if (lane == 0) {
+      if constexpr (kPair) sm100::mbar_arrive_cluster(empty_remote[acc]);
+      else sm100::mbar_arrive(&tmem_empty_bar[acc]);
+    }
     acc ^= 1;
     if (acc == 0) acc_phase ^= 1;
   }
@@ -616,6 +635,10 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
   using Cfg = ConvCfg<Elem, BLOCK_N, SWZ>;
   constexpr bool kTF32 = ElemTraits<Elem>::kTF32;
   static_assert(BLOCK_N % 32 == 0 && BLOCK_N <= 256, "BLOCK_N: multiple of 32 up to 256");
+  constexpr bool kPair = (EPI & kEpiPair) != 0;                 // CTA pairs, see EpiKind
+  static_assert(!kPair || (EPI & 15) != kEpiGeneric, "CTA pairs: specialised epilogues only");
+  constexpr int kBStage = Cfg::kBBytes / (kPair ? 2 : 1);      // weight tile bytes in THIS CTA's shared memory
+  const uint32_t cta_rank = kPair ? sm100::cluster_ctarank() : 0u;
 
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_addr = sm100::smem_u32(smem_raw);
@@ -625,7 +648,7 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
   const int n_a = p.n_a_stages, n_b = p.n_b_stages;
   uint8_t* smem_a = smem;                                   // n_a x halo tile
   uint8_t* smem_b = smem + n_a * p.a_stage_bytes;           // n_b x [BLOCK_N rows x SWZ bytes]
-  uint8_t* epi_stage = smem_b + n_b * Cfg::kBBytes;         // TMA-store staging: [kNumEpiWarps][40 rows][kEpiRowB], 1 KB aligned
+  uint8_t* epi_stage = smem_b + n_b * kBStage;              // TMA-store staging: [kNumEpiWarps][40 rows][kEpiRowB], 1 KB aligned
   uint8_t* aux = epi_stage + p.epi_bytes;
   uint64_t* a_full = reinterpret_cast<uint64_t*>(aux);      // [kMaxAStages]
   uint64_t* a_empty = a_full + kMaxAStages;
@@ -649,7 +672,10 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
   const int tiles_x = p.W / tile_w;
   const int tiles_y = p.H / kBlkH;
   const int m_tiles = p.NB * tiles_y * tiles_x;
-  const int total_tiles = m_tiles * p.n_tiles;
+  // work units: one tile per CTA, or two horizontally adjacent tiles (same N tile) per CTA pair
+  const int total_tiles = kPair ? (m_tiles >> 1) * p.n_tiles : m_tiles * p.n_tiles;
+  const int unit0 = kPair ? int(blockIdx.x >> 1) : int(blockIdx.x);
+  const int unit_stride = kPair ? int(gridDim.x >> 1) : int(gridDim.x);
   int kb_total = 0;
   for (int s = 0; s < p.n_seg; ++s) kb_total += p.seg_kb[s];
   const int halo_w = tile_w + 2 * p.pad;                    // halo pitch in pixels
@@ -671,6 +697,11 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
     }
   }
   if (warp_idx == 1 && lane == 0) {
+    // CTA pair: the "full" barriers that count are the leader's — ONE arrival (the leader's producer, which also
+    // announces the bytes of both CTAs' loads; the peer's loads only complete bytes on it: a remote arrive per weight
+    // tile cost the peer's producer ~600 clocks each and halved the streamed layers' speed); the leader's "TMEM
+    // empty" barriers collect the epilogue warps of both CTAs
+    constexpr uint32_t kCtas = kPair ? 2 : 1;
     for (int i = 0; i < kMaxAStages; ++i) {
       sm100::mbar_init(&a_full[i], 1);
       sm100::mbar_init(&a_empty[i], 1);
@@ -681,12 +712,13 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
     }
     for (int i = 0; i < 2; ++i) {
       sm100::mbar_init(&tmem_full_bar[i], 1);
-      sm100::mbar_init(&tmem_empty_bar[i], kNumEpiWarps);  // one arrive per epilogue warp
+      sm100::mbar_init(&tmem_empty_bar[i], kNumEpiWarps * kCtas);  // one arrive per epilogue warp
     }
     sm100::fence_barrier_init();
   }
   if (warp_idx == 2) {
-    sm100::tmem_alloc(tmem_ptr_smem, tmem_cols);
+    if constexpr (kPair) sm100::tmem_alloc_pair(tmem_ptr_smem, tmem_cols);
+    else sm100::tmem_alloc(tmem_ptr_smem, tmem_cols);
   }
   const bool with_stats = p.stats != nullptr;
   for (int i = threadIdx.x; i < p.cout; i += blockDim.x) {
@@ -716,7 +748,8 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
     }
   }
   sm100::tc_fence_before_sync();
-  __syncthreads();
+  if constexpr (kPair) sm100::cluster_sync();   // the peer's barriers must be initialised before anything signals them
+  else __syncthreads();
   sm100::tc_fence_after_sync();
   const uint32_t tmem_base = *tmem_ptr_smem;
 
@@ -725,19 +758,33 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
     // ===== TMA producer (one elected thread) =====
     if (sm100::elect_one() && !(p.dbg & 512)) {  // 512: timing experiment without the producer
       const uint32_t a_bytes = uint32_t(SWZ) * halo_w * halo_h;
+      constexpr uint32_t kCtas = kPair ? 2 : 1;
+      // pair: only the leader arms its barrier, with the bytes of both CTAs' loads. The peer's bytes may land before
+      // that (the transaction count goes negative meanwhile); the phase cannot complete before the leader's arrival,
+      // and the peer cannot be a whole ring ahead because its "empty" barriers are signalled by the leader's MMAs.
+      auto arm = [&](uint64_t* bar, uint32_t bytes_all) {
+        if (!kPair || cta_rank == 0) sm100::mbar_arrive_expect_tx(bar, bytes_all);
+      };
+      auto load_b = [&](uint8_t* dst, uint64_t* bar, int k0, int row0, int tap) {
+        if constexpr (kPair)
+          sm100::tma_load_3d_pair(dst, &p.tmB, sm100::mapa_u32(bar, 0), k0, row0 + int(cta_rank) * (BLOCK_N / 2), tap,
+                                  sm100::kEvictLast);
+        else
+          sm100::tma_load_3d(dst, &p.tmB, bar, k0, row0, tap, sm100::kEvictLast);
+      };
       if (p.b_resident) {
         // all weight tiles of the layer, once (n_tiles == 1 in this mode)
-        sm100::mbar_arrive_expect_tx(&b_full[0], uint32_t(kb_total * p.taps) * Cfg::kBBytes);
+        arm(&b_full[0], uint32_t(kb_total * p.taps) * Cfg::kBBytes);
         for (int kb = 0; kb < kb_total; ++kb)
           for (int tap = 0; tap < p.taps; ++tap)
-            sm100::tma_load_3d(smem_b + (kb * p.taps + tap) * Cfg::kBBytes, &p.tmB, &b_full[0], kb * Cfg::kBK, 0, tap,
-                               sm100::kEvictLast);
+            load_b(smem_b + (kb * p.taps + tap) * kBStage, &b_full[0], kb * Cfg::kBK, 0, tap);
       }
       int sa = 0, sb = 0, a_loads = 0;
       uint32_t pa = 0, pb = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        const int n_tile = tile % p.n_tiles;
-        int m = tile / p.n_tiles;
+      for (int unit = unit0; unit < total_tiles; unit += unit_stride) {
+        const int n_tile = unit % p.n_tiles;
+        int m = unit / p.n_tiles;
+        if constexpr (kPair) m = 2 * m + int(cta_rank);
         const int tx = m % tiles_x;
         m /= tiles_x;
         const int ty = m % tiles_y;
@@ -749,11 +796,15 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
           for (int kb = 0; kb < p.seg_kb[s]; ++kb, ++kb_glob) {
             sm100::mbar_wait(&a_empty[sa], pa ^ 1);
             if ((p.dbg & 16) && a_loads >= n_a) {   // timing experiment: no activation traffic after the ring filled
-              sm100::mbar_arrive(&a_full[sa]);
+              if (!kPair || cta_rank == 0) sm100::mbar_arrive(&a_full[sa]);
             } else {
-              sm100::mbar_arrive_expect_tx(&a_full[sa], a_bytes);
-              sm100::tma_load_4d(smem_a + sa * p.a_stage_bytes, tmA, &a_full[sa], kb * Cfg::kBK, x0, y0, img,
-                                 sm100::kEvictNormal);
+              arm(&a_full[sa], a_bytes * kCtas);
+              if constexpr (kPair)
+                sm100::tma_load_4d_pair(smem_a + sa * p.a_stage_bytes, tmA, sm100::mapa_u32(&a_full[sa], 0), kb * Cfg::kBK, x0,
+                                        y0, img, sm100::kEvictNormal);
+              else
+                sm100::tma_load_4d(smem_a + sa * p.a_stage_bytes, tmA, &a_full[sa], kb * Cfg::kBK, x0, y0, img,
+                                   sm100::kEvictNormal);
             }
             ++a_loads;
             if (++sa == n_a) {
@@ -763,9 +814,8 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
             if (!p.b_resident) {
               for (int tap = 0; tap < p.taps; ++tap) {
                 sm100::mbar_wait(&b_empty[sb], pb ^ 1);
-                sm100::mbar_arrive_expect_tx(&b_full[sb], Cfg::kBBytes);
-                sm100::tma_load_3d(smem_b + sb * Cfg::kBBytes, &p.tmB, &b_full[sb], kb_glob * Cfg::kBK,
-                                   n_tile * BLOCK_N, tap, sm100::kEvictLast);
+                arm(&b_full[sb], Cfg::kBBytes);
+                load_b(smem_b + sb * kBStage, &b_full[sb], kb_glob * Cfg::kBK, n_tile * BLOCK_N, tap);
                 if (++sb == n_b) {
                   sb = 0;
                   pb ^= 1;
@@ -778,8 +828,13 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
     }
   } else if (warp_idx == 1) {
     // ===== MMA issuer (one elected thread) =====
-    if (sm100::elect_one()) {
-      constexpr uint32_t idesc = sm100::make_idesc(ElemTraits<Elem>::kFmt, kTileM, BLOCK_N);
+    // (CTA pair: the leader issues the M = 256 MMAs for both CTAs; the peer's tensor core executes its half)
+    if (sm100::elect_one() && cta_rank == 0) {
+      constexpr uint32_t idesc = sm100::make_idesc(ElemTraits<Elem>::kFmt, kPair ? 2 * kTileM : kTileM, BLOCK_N);
+      auto commit = [&](uint64_t* bar) {
+        if constexpr (kPair) sm100::umma_commit_pair(bar);   // arrives on this barrier in both CTAs
+        else sm100::umma_commit(bar);
+      };
       // descriptor high words are constant; the low words (start address >> 4) advance by whole pixels / rows
       const uint32_t a_hi = sm100::smem_desc_hi<SWZ>(uint32_t(halo_w) * SWZ);  // 8-pixel groups one halo row apart
       const uint32_t b_hi = sm100::smem_desc_hi<SWZ>(8u * SWZ);
@@ -800,7 +855,7 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
         sm100::mbar_wait(&b_full[0], 0);
         sm100::tc_fence_after_sync();
       }
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      for (int unit = unit0; unit < total_tiles; unit += unit_stride) {
         if (!nowait) sm100::mbar_wait(&tmem_empty_bar[acc], acc_phase ^ 1);
         sm100::tc_fence_after_sync();
         const uint32_t tmem_d = tmem_base + uint32_t(acc) * buf_cols;
@@ -814,15 +869,15 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
           if (fast) {
             constexpr int kNM = natural_nm(BLOCK_N);
             if (kHalfNm && nm != kNM)
-              issue_kb<kTF32, (kHalfNm ? kNM / 2 : kNM), Cfg::kKSteps, SWZ, BLOCK_N, true>(
+              issue_kb<kTF32, (kHalfNm ? kNM / 2 : kNM), Cfg::kKSteps, SWZ, BLOCK_N, true, kPair>(
                   tmem_d, a_row_lo, a_hi, b_hi, idesc, kb != 0, p.b_resident != 0, b_res_lo, b_lo0, b_full, b_empty, sb, pb, n_b);
             else if (p.taps == 9)
-              issue_kb<kTF32, kNM, Cfg::kKSteps, SWZ, BLOCK_N, true>(tmem_d, a_row_lo, a_hi, b_hi, idesc, kb != 0, p.b_resident != 0,
+              issue_kb<kTF32, kNM, Cfg::kKSteps, SWZ, BLOCK_N, true, kPair>(tmem_d, a_row_lo, a_hi, b_hi, idesc, kb != 0, p.b_resident != 0,
                                                                      b_res_lo, b_lo0, b_full, b_empty, sb, pb, n_b);
             else
-              issue_kb<kTF32, kNM, Cfg::kKSteps, SWZ, BLOCK_N, false>(tmem_d, a_row_lo, a_hi, b_hi, idesc, kb != 0, p.b_resident != 0,
+              issue_kb<kTF32, kNM, Cfg::kKSteps, SWZ, BLOCK_N, false, kPair>(tmem_d, a_row_lo, a_hi, b_hi, idesc, kb != 0, p.b_resident != 0,
                                                                       b_res_lo, b_lo0, b_full, b_empty, sb, pb, n_b);
-            b_res_lo += uint32_t(p.taps) * (Cfg::kBBytes >> 4);
+            b_res_lo += uint32_t(p.taps) * (kBStage >> 4);
           } else
           for (int ty_ = 0; ty_ < taps_y; ++ty_, a_row_lo += row16) {
             uint32_t a_tap_lo = a_row_lo;   // halo row / column of the tap's first pixel
@@ -830,11 +885,11 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
               uint32_t b_lo;
               if (p.b_resident) {
                 b_lo = b_res_lo;
-                b_res_lo += Cfg::kBBytes >> 4;
+                b_res_lo += kBStage >> 4;
               } else {
                 sm100::mbar_wait(&b_full[sb], pb);
                 sm100::tc_fence_after_sync();
-                b_lo = b_lo0 + uint32_t(sb) * (Cfg::kBBytes >> 4);
+                b_lo = b_lo0 + uint32_t(sb) * (kBStage >> 4);
               }
               // accumulator of this tap: always 0 unless the fp32 mode splits the sum (round-robin, no division:
               // everything in this loop is on the single issuing thread's critical path)
@@ -851,12 +906,12 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
               used |= 1u << sacc;
               const uint32_t d0 = tmem_d + uint32_t(sacc * nm) * BLOCK_N;
               if (!(p.dbg & 64)) {  // 64: timing experiment without the MMAs (TMA + epilogue only)
-                if (nm == 4) issue_tap<kTF32, 4, Cfg::kKSteps, SWZ, BLOCK_N>(d0, a_tap_lo, a_hi, b_lo, b_hi, idesc, have);
-                else if (nm == 2) issue_tap<kTF32, 2, Cfg::kKSteps, SWZ, BLOCK_N>(d0, a_tap_lo, a_hi, b_lo, b_hi, idesc, have);
-                else issue_tap<kTF32, 1, Cfg::kKSteps, SWZ, BLOCK_N>(d0, a_tap_lo, a_hi, b_lo, b_hi, idesc, have);
+                if (nm == 4) issue_tap<kTF32, 4, Cfg::kKSteps, SWZ, BLOCK_N, kPair>(d0, a_tap_lo, a_hi, b_lo, b_hi, idesc, have);
+                else if (nm == 2) issue_tap<kTF32, 2, Cfg::kKSteps, SWZ, BLOCK_N, kPair>(d0, a_tap_lo, a_hi, b_lo, b_hi, idesc, have);
+                else issue_tap<kTF32, 1, Cfg::kKSteps, SWZ, BLOCK_N, kPair>(d0, a_tap_lo, a_hi, b_lo, b_hi, idesc, have);
               }
               if (!p.b_resident) {
-                sm100::umma_commit(&b_empty[sb]);  // frees this weight stage once the MMAs retire
+                commit(&b_empty[sb]);  // frees this weight stage once the MMAs retire
                 if (++sb == n_b) {
                   sb = 0;
                   pb ^= 1;
@@ -864,13 +919,13 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
               }
             }
           }
-          sm100::umma_commit(&a_empty[sa]);      // halo tile consumed by all taps
+          commit(&a_empty[sa]);      // halo tile consumed by all taps
           if (++sa == n_a) {
             sa = 0;
             pa ^= 1;
           }
         }
-        sm100::umma_commit(&tmem_full_bar[acc]);  // accumulators complete -> epilogue
+        commit(&tmem_full_bar[acc]);  // accumulators complete -> epilogue
         acc ^= 1;
         if (acc == 0) acc_phase ^= 1;
       }
@@ -890,7 +945,7 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
     constexpr int kChunksPerBlk = BLOCK_N / kChunk;
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+    for (int tile = unit0; tile < total_tiles; tile += unit_stride) {
       const int n_tile = tile % p.n_tiles;
       int m = tile / p.n_tiles;
       const int tx = m % tiles_x;
@@ -1171,7 +1226,8 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
 
   // ---------------------------------------------------------------- teardown
   sm100::tc_fence_before_sync();
-  __syncthreads();
+  if constexpr (kPair) sm100::cluster_sync();   // neither CTA may leave while the peer can still signal or read it
+  else __syncthreads();
   if (with_stats) {
     float* dst = p.stats + size_t(blockIdx.x) * 2 * p.cout;
     for (int i = threadIdx.x; i < 2 * p.cout; i += blockDim.x) {
@@ -1183,7 +1239,8 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
   }
   if (warp_idx == 2) {
     sm100::tc_fence_after_sync();
-    sm100::tmem_dealloc(tmem_base, tmem_cols);
+    if constexpr (kPair) sm100::tmem_dealloc_pair(tmem_base, tmem_cols);
+    else sm100::tmem_dealloc(tmem_base, tmem_cols);
   }
 }
 

@@ -343,6 +343,37 @@ int launch_conv_epi(const itmo::ConvParams& p, int total_tiles, int smem_bytes, 
     ITMO_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, itmo::kSmemLimit));
     configured = true;
   }
+  if constexpr ((EPI & itmo::kEpiPair) != 0) {
+    // CTA pairs: clusters of two CTAs (one TPC), one pair per two tiles; total_tiles counts single tiles and is even
+    cudaLaunchConfig_t cfg = {};
+    cfg.blockDim = dim3(itmo::kNumThreads);
+    cfg.dynamicSmemBytes = size_t(smem_bytes);
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    // persistent grid = the pairs the device can hold at once (a TPC with one SM fused off hosts no pair)
+    static int max_pairs = 0;
+    if (max_pairs == 0) {
+      cfg.gridDim = dim3(2 * (num_sms() / 2));
+      cfg.dynamicSmemBytes = size_t(itmo::kSmemLimit);
+      int n = 0;
+      if (cudaOccupancyMaxActiveClusters(&n, kern, &cfg) != cudaSuccess || n <= 0) {
+        cudaGetLastError();
+        n = num_sms() / 2;
+      }
+      max_pairs = std::min(n, num_sms() / 2);
+      cfg.dynamicSmemBytes = size_t(smem_bytes);
+    }
+    const int pairs = std::min(total_tiles / 2, max_pairs);
+    cfg.gridDim = dim3(2 * pairs);
+    ITMO_CUDA(cudaLaunchKernelEx(&cfg, kern, p));
+    return ITMO_OK;
+  }
   const int grid = std::min(total_tiles, num_sms());
   kern<<<grid, itmo::kNumThreads, smem_bytes, stream>>>(p);
   ITMO_CUDA(cudaGetLastError());
@@ -366,6 +397,14 @@ int launch_conv_fast(int block_n, int swz, int epi, const itmo::ConvParams& p, i
   ITMO_FAST(256, 128, kEpiConvT);         // conv2d_transpose_1 ... 3
   ITMO_FAST(256, 128, kEpiConvT | C);     // conv2d_transpose_4 (cout 64)
   ITMO_FAST(64, 64, kEpiHead | C);        // conv2d_14 + head
+  constexpr int P = kEpiPair;              // the same as CTA pairs (tcgen05.mma.cta_group::2, M = 256)
+  ITMO_FAST(64, 64, kEpiConv | C | P);
+  ITMO_FAST(64, 128, kEpiConvPool | C | P);
+  ITMO_FAST(128, 128, kEpiConv | P);
+  ITMO_FAST(128, 128, kEpiConvPool | P);
+  ITMO_FAST(256, 128, kEpiConv | P);
+  ITMO_FAST(256, 128, kEpiConvPool | P);
+  ITMO_FAST(64, 64, kEpiHead | C | P);
 #undef ITMO_FAST
   return -1;
 }
@@ -483,7 +522,7 @@ int run_conv(const ConvArgs& a, cudaStream_t stream) {
   }
   const int halo_w = itmo::kBlkW * nm + 2 * pad, halo_h = itmo::kBlkH + 2 * pad;
   const int a_stage = (swz * halo_w * halo_h + 1023) / 1024 * 1024;
-  const int b_stage = block_n * swz;
+  int b_stage = block_n * swz;
   const int kmult = k_mult(a.precision);
   const int kb_total = kmult * cin / bk;
   const int stats_bytes = a.stats ? itmo::kNumEpiWarps * 2 * a.cout * 4 : 0;   // per-warp statistic rows (ConvParams::stats)
@@ -515,6 +554,27 @@ int run_conv(const ConvArgs& a, cudaStream_t stream) {
         epi = itmo::kEpiConvT;
         if (can_const && a.cout == 64 && block_n == 256) epi |= itmo::kEpiConstAffine;
       }
+    }
+  }
+  // ---- CTA pairs (itmo::kEpiPair): the 3x3 layers with at least 64 weight rows per tile, two horizontally adjacent
+  // tiles per pair (ITMO_PAIR=0: A/B). Each CTA then holds half of every weight tile.
+  static const int allow_pair = env_int("ITMO_PAIR", 1);
+  {
+    const int tiles_x = a.w / (itmo::kBlkW * nm);
+    const int kind = epi & 15;
+    const int C = itmo::kEpiConstAffine;
+    // the pair instantiations of launch_conv_fast
+    const bool compiled = (block_n == 64 && swz == 64 && (epi == (itmo::kEpiConv | C) || epi == (itmo::kEpiHead | C))) ||
+                          (block_n == 64 && swz == 128 && epi == (itmo::kEpiConvPool | C)) ||
+                          ((block_n == 128 || block_n == 256) && swz == 128 && (epi == itmo::kEpiConv || epi == itmo::kEpiConvPool));
+    // measured per layer on one box (ITMO_PAIR=0/1, equal clocks): conv2d_14 -19 %, conv2d_6 ... 13 -2 ... -7 %; the
+    // 32 / 64-input-channel layers whose whole weight set is resident anyway (conv2d_3 / 4 / 5) are 6 - 30 % SLOWER as
+    // pairs (two CTAs in lock-step have less slack against HBM latency), so they stay single (ITMO_PAIR=2 forces all)
+    const bool worth = kind == itmo::kEpiHead || cin >= 128 || allow_pair == 2;
+    if (allow_pair && worth && dbg_env == 0 && conv && compiled && tiles_x % 2 == 0 && num_sms() >= 2 &&
+        (kind == itmo::kEpiConv || kind == itmo::kEpiConvPool || kind == itmo::kEpiHead)) {
+      epi |= itmo::kEpiPair;
+      b_stage /= 2;
     }
   }
   static const int fast_bufs = std::max(1, std::min(2, env_int("ITMO_EPI_BUFS", 1)));
@@ -550,7 +610,8 @@ int run_conv(const ConvArgs& a, cudaStream_t stream) {
                           a.row_stride[i & 1], a.img_stride[i & 1]);
     if (rc) return rc;
   }
-  int rc = make_weight_map(&p.tmB, a.wpacked, a.precision, kmult * cin, rows, taps, block_n, swz, a.w_tap_stride_rows);
+  int rc = make_weight_map(&p.tmB, a.wpacked, a.precision, kmult * cin, rows, taps,
+                           (epi & itmo::kEpiPair) ? block_n / 2 : block_n, swz, a.w_tap_stride_rows);
   if (rc) return rc;
   if (tma_store) {
     p.tma_store = 1;
@@ -638,6 +699,7 @@ int run_conv(const ConvArgs& a, cudaStream_t stream) {
                         ? launch_conv_fast<__nv_bfloat16>(block_n, swz, epi, p, total_tiles, smem_bytes, stream)
                         : launch_conv_fast<__half>(block_n, swz, epi, p, total_tiles, smem_bytes, stream);
     if (rcf != -1) return rcf;
+    if (epi & itmo::kEpiPair) return fail(ITMO_ERR_INVALID, "CTA-pair kernel not compiled for BLOCK_N %d / %d-byte rows", block_n, swz);
     // not compiled for this shape: the generic kernel reads the same parameters (one staging tile per warp is a
     // prefix of two)
   }
