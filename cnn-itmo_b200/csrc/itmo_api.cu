@@ -405,6 +405,7 @@ int launch_conv_fast(int block_n, int swz, int epi, const itmo::ConvParams& p, i
   ITMO_FAST(256, 128, kEpiConv | P);
   ITMO_FAST(256, 128, kEpiConvPool | P);
   ITMO_FAST(64, 64, kEpiHead | C | P);
+  ITMO_FAST(256, 128, kEpiConvT | P);
 #undef ITMO_FAST
   return -1;
 }
@@ -562,17 +563,23 @@ int run_conv(const ConvArgs& a, cudaStream_t stream) {
   {
     const int tiles_x = a.w / (itmo::kBlkW * nm);
     const int kind = epi & 15;
+    const int n_tiles_early = rows / block_n;
     const int C = itmo::kEpiConstAffine;
     // the pair instantiations of launch_conv_fast
     const bool compiled = (block_n == 64 && swz == 64 && (epi == (itmo::kEpiConv | C) || epi == (itmo::kEpiHead | C))) ||
                           (block_n == 64 && swz == 128 && epi == (itmo::kEpiConvPool | C)) ||
-                          ((block_n == 128 || block_n == 256) && swz == 128 && (epi == itmo::kEpiConv || epi == itmo::kEpiConvPool));
+                          ((block_n == 128 || block_n == 256) && swz == 128 && (epi == itmo::kEpiConv || epi == itmo::kEpiConvPool)) ||
+                          (block_n == 256 && swz == 128 && epi == itmo::kEpiConvT);
     // measured per layer on one box (ITMO_PAIR=0/1, equal clocks): conv2d_14 -19 %, conv2d_6 ... 13 -2 ... -7 %; the
     // 32 / 64-input-channel layers whose whole weight set is resident anyway (conv2d_3 / 4 / 5) are 6 - 30 % SLOWER as
     // pairs (two CTAs in lock-step have less slack against HBM latency), so they stay single (ITMO_PAIR=2 forces all)
     const bool worth = kind == itmo::kEpiHead || cin >= 128 || allow_pair == 2;
-    if (allow_pair && worth && dbg_env == 0 && conv && compiled && tiles_x % 2 == 0 && num_sms() >= 2 &&
-        (kind == itmo::kEpiConv || kind == itmo::kEpiConvPool || kind == itmo::kEpiHead)) {
+    static const int pair_convt = env_int("ITMO_PAIR_CONVT", 1);
+    // transposed convolutions with several N tiles re-stream a 32 KB weight tile per 4 MMAs (94 B / clock / SM from L2
+    // with the activations): as pairs each CTA streams half of it
+    const bool convt_ok = kind == itmo::kEpiConvT && pair_convt && n_tiles_early >= 4;
+    if (allow_pair && (worth || convt_ok) && dbg_env == 0 && (conv || convt_ok) && compiled && tiles_x % 2 == 0 && num_sms() >= 2 &&
+        (kind == itmo::kEpiConv || kind == itmo::kEpiConvPool || kind == itmo::kEpiHead || convt_ok)) {
       epi |= itmo::kEpiPair;
       b_stage /= 2;
     }
@@ -597,6 +604,13 @@ int run_conv(const ConvArgs& a, cudaStream_t stream) {
     if (n_b < 2) return fail(ITMO_ERR_INVALID, "tile does not fit in shared memory");
     const int left = budget - n_a * a_stage - n_b * b_stage;
     if (left >= a_stage) n_a = 3;
+    static const int deep_1tap = env_int("ITMO_DEEP_1TAP", 1);
+    if (deep_1tap && taps == 1) {
+      // one tap: a channel block is one halo stage + one weight stage and only four MMAs long, so both rings get the
+      // same depth — as many (stage, stage) pairs as fit — instead of a deep weight ring behind a three-stage halo ring
+      const int both = std::min(itmo::kMaxAStages, budget / (a_stage + b_stage));
+      if (both >= 3) n_a = n_b = both;
+    }
   }
   const int smem_bytes = 1024 + n_a * a_stage + n_b * b_stage + epi_bytes + itmo::kAuxBytes + stats_bytes;
 
