@@ -515,8 +515,8 @@ def run_batch_leg(a, hz, precision=None, batch=None, steps=None, with_e2e=True, 
 # --------------------------------------------------------------------------------------------------
 def run_frames_leg(a, hz, weights=None, steps=None, warm_s=1.0):
     """3840x2160 uint8 frames, tiled 512x512 with a 96-pixel halo (84 tiles per frame), frames sharded over the ranks
-    (no collective), fused inverse-Reinhard output (float32 HDR; `--hdr-half` is not offered: the reference's
-    inverse_Reinhard.m writes doubles). Reported in Mpix/s of UNIQUE output pixels (8.29 Mpix per frame); executed
+    (no collective), fused inverse-Reinhard output (float32 HDR, like the floats inverse_Reinhard.m
+    writes; the half-float output kind is timed beside it under e2e.half_float_output). Reported in Mpix/s of UNIQUE output pixels (8.29 Mpix per frame); executed
     FLOPs are 84 x 165.37 GFLOP per frame. Input frames are virtual-camera renders of seeded HDR fields when the
     synthesis kernels are available (datagen), else uniform noise."""
     import numpy as np
@@ -575,6 +575,26 @@ def run_frames_leg(a, hz, weights=None, steps=None, warm_s=1.0):
     torch.cuda.synchronize()
     dt = hz.max_over_ranks(time.perf_counter() - t0)
     e2e = hz.world * F * e2e_steps * (H * W / 1e6) / dt
+    # the same with the half-float output kind (OpenEXR's HALF pixel type): half the device -> host bytes, which is what
+    # bounds this path when eight ranks share one host's PCIe / pinned-memory path
+    yh = torch.empty((F, H, W, 3), dtype=torch.float16, device=hz.dev)
+    hyh = pinned_empty((F, H, W, 3), np.float16)
+    hyht = torch.from_numpy(hyh)
+
+    def step_half():
+        frames.predict_frames_device(model, x.data_ptr(), F, H, W, yh.data_ptr(), 'hdr_f16', 0.18, hz.stream.cuda_stream)
+
+    step_half()
+    torch.cuda.synchronize()
+    hz.barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        x.copy_(hxt, non_blocking=True)
+        step_half()
+        hyht.copy_(yh, non_blocking=True)
+    torch.cuda.synchronize()
+    dth = hz.max_over_ranks(time.perf_counter() - t0)
+    e2e_half = hz.world * F * e2e_steps * (H * W / 1e6) / dth
     line = None
     if hz.rank == 0:
         line = {'metric': '4K SDR->HDR frames, unique output pixels', 'value': round(mpix, 2), 'unit': 'Mpix/s',
@@ -591,10 +611,12 @@ def run_frames_leg(a, hz, weights=None, steps=None, warm_s=1.0):
                 'clocks': clocks,
                 'e2e': {'value': round(e2e, 2), 'unit': 'Mpix/s', 'h2d_bytes_per_step': int(hx.nbytes),
                         'd2h_bytes_per_step': int(hy.nbytes), 'steps': e2e_steps,
-                        'api': 'frames.predict_frames_device with pinned host copies'},
+                        'api': 'frames.predict_frames_device with pinned host copies',
+                        'half_float_output': {'value': round(e2e_half, 2), 'unit': 'Mpix/s',
+                                              'd2h_bytes_per_step': int(hyh.nbytes), 'out_kind': 'hdr_f16'}},
                 'gpu_launches': int(launches), 'roofline': roofline, 'cpu_baseline': None}
     model.close()
-    del x, y, hx, hy, hxt, hyt
+    del x, y, hx, hy, hxt, hyt, yh, hyh, hyht
     torch.cuda.empty_cache()
     return line
 

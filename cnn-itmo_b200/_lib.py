@@ -14,7 +14,7 @@ LIB_PATH = os.path.join(_HERE, 'libitmo_b200.so')
 
 PREC_TF32, PREC_BF16, PREC_FP32, PREC_FP16 = 0, 1, 2, 3
 DT_U8, DT_F32 = 0, 1
-OUT_U8, OUT_F32, OUT_HDR_INTENDED, OUT_HDR_AS_WRITTEN = 0, 1, 2, 3
+OUT_U8, OUT_F32, OUT_HDR_INTENDED, OUT_HDR_AS_WRITTEN, OUT_HDR_INTENDED_F16 = 0, 1, 2, 3, 4
 NUM_LAYERS = 19
 TRAIN_NO_DROPOUT, TRAIN_FREEZE_MOVING, TRAIN_KEEP_GRADS = 1, 2, 4
 OPT_RMSPROP, OPT_ADAM = 0, 1

@@ -170,7 +170,9 @@ __global__ void __launch_bounds__(256) frame_stats_kernel(const uint8_t* __restr
 // as_written = 0 is the repaired form: X = I'/(1-I') with I' = min(I, 1 - 0.5/255), E = key * X / G_X (geometric mean
 // of the recovered luminance over the non-black pixels normalised to `key`, mirroring Reinhard.m:19-21), zero-luminance
 // pixels stay black.
-__global__ void __launch_bounds__(256) inverse_reinhard_kernel(const uint8_t* __restrict__ frame, float* __restrict__ hdr,
+// OutT = float, or __half (ITMO_OUT_HDR_INTENDED_F16: values above fp16's range clamp to 65504).
+template <typename OutT>
+__global__ void __launch_bounds__(256) inverse_reinhard_kernel(const uint8_t* __restrict__ frame, OutT* __restrict__ hdr,
                                                                size_t n_pix, const FrameStats* __restrict__ stats,
                                                                int as_written, double key) {
   const double P = double(n_pix);
@@ -194,9 +196,15 @@ __global__ void __launch_bounds__(256) inverse_reinhard_kernel(const uint8_t* __
     if (E >= 4294967296.0) E = 4294967296.0;  // :19
     double q = E / I;                         // :22
     if (!as_written && I == 0.0) q = 0.0;
-    hdr[3 * p] = float(r * q);
-    hdr[3 * p + 1] = float(g * q);
-    hdr[3 * p + 2] = float(b * q);
+    if constexpr (sizeof(OutT) == 2) {
+      hdr[3 * p] = __float2half_rn(fminf(float(r * q), 65504.f));
+      hdr[3 * p + 1] = __float2half_rn(fminf(float(g * q), 65504.f));
+      hdr[3 * p + 2] = __float2half_rn(fminf(float(b * q), 65504.f));
+    } else {
+      hdr[3 * p] = float(r * q);
+      hdr[3 * p + 1] = float(g * q);
+      hdr[3 * p + 2] = float(b * q);
+    }
   }
 }
 

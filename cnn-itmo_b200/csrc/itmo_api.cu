@@ -1376,7 +1376,7 @@ int itmo_inverse_reinhard(const void* frames_u8_dev, void* hdr_f32_dev, int n_fr
   for (int f = 0; f < n_frames; ++f) {
     const uint8_t* src = (const uint8_t*)frames_u8_dev + size_t(f) * n_pix * 3;
     itmo::frame_stats_kernel<<<grid, 256, 0, s>>>(src, n_pix, st + f, as_written);
-    itmo::inverse_reinhard_kernel<<<grid, 256, 0, s>>>(src, (float*)hdr_f32_dev + size_t(f) * n_pix * 3, n_pix, st + f,
+    itmo::inverse_reinhard_kernel<float><<<grid, 256, 0, s>>>(src, (float*)hdr_f32_dev + size_t(f) * n_pix * 3, n_pix, st + f,
                                                        as_written, key);
   }
   ITMO_CUDA(cudaGetLastError());
@@ -1387,7 +1387,7 @@ int itmo_predict_frames(itmo_ctx* ctx, const void* frames_dev, int n_frames, int
                         double key, void* stream) {
   if (!ctx || !frames_dev || !out_dev) return fail(ITMO_ERR_INVALID, "null argument");
   if (!ctx->weights_loaded) return fail(ITMO_ERR_STATE, "itmo_predict_frames before itmo_load_weights");
-  if (out_kind < ITMO_OUT_U8 || out_kind > ITMO_OUT_HDR_AS_WRITTEN) return fail(ITMO_ERR_INVALID, "bad out_kind");
+  if (out_kind < ITMO_OUT_U8 || out_kind > ITMO_OUT_HDR_INTENDED_F16) return fail(ITMO_ERR_INVALID, "bad out_kind");
   if (n_frames < 0) return fail(ITMO_ERR_INVALID, "negative frame count");
   int oy[64], ylo[64], yhi[64], ox[64], xlo[64], xhi[64];
   const int ny = itmo::plan_axis(h, oy, ylo, yhi, 64), nx = itmo::plan_axis(w, ox, xlo, xhi, 64);
@@ -1463,9 +1463,14 @@ int itmo_predict_frames(itmo_ctx* ctx, const void* frames_dev, int n_frames, int
     }
     if (hdr) {
       const int grid = int(std::min<size_t>((frame_px + 255) / 256, size_t(num_sms()) * 8));
-      itmo::inverse_reinhard_kernel<<<grid, 256, 0, s>>>((const uint8_t*)ctx->frm_u8,
-                                                         (float*)out_dev + size_t(f) * frame_px * 3, frame_px,
-                                                         ctx->frm_stats, as_written ? 1 : 0, key);
+      if (out_kind == ITMO_OUT_HDR_INTENDED_F16)
+        itmo::inverse_reinhard_kernel<__half><<<grid, 256, 0, s>>>((const uint8_t*)ctx->frm_u8,
+                                                                    (__half*)out_dev + size_t(f) * frame_px * 3, frame_px,
+                                                                    ctx->frm_stats, 0, key);
+      else
+        itmo::inverse_reinhard_kernel<float><<<grid, 256, 0, s>>>((const uint8_t*)ctx->frm_u8,
+                                                                   (float*)out_dev + size_t(f) * frame_px * 3, frame_px,
+                                                                   ctx->frm_stats, as_written ? 1 : 0, key);
       ITMO_CUDA(cudaGetLastError());
       ctx->launches++;
     }

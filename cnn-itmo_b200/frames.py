@@ -18,7 +18,8 @@ from . import _lib
 TILE = 512
 HALO = 96          # >= 92, the receptive-field reach of the graph, on the 16-pixel pool grid
 OUT_KINDS = {'u8': _lib.OUT_U8, 'f32': _lib.OUT_F32, 'hdr': _lib.OUT_HDR_INTENDED,
-             'hdr_as_written': _lib.OUT_HDR_AS_WRITTEN}
+             'hdr_as_written': _lib.OUT_HDR_AS_WRITTEN, 'hdr_f16': _lib.OUT_HDR_INTENDED_F16}
+OUT_DTYPES = {'u8': 'uint8', 'f32': 'float32', 'hdr': 'float32', 'hdr_as_written': 'float32', 'hdr_f16': 'float16'}
 
 
 def plan_axis(extent: int) -> List[Tuple[int, int, int]]:
@@ -110,13 +111,14 @@ def predict_frames_device(model, frames_ptr: int, n: int, h: int, w: int, out_pt
 
 def predict_frames(model, frames_u8, out: str = 'u8', key: float = 0.18) -> np.ndarray:
     """uint8 frames [n,h,w,3] -> 'u8': what predict.py:64 would write for the whole frame; 'f32': the sigmoid
-    output; 'hdr' / 'hdr_as_written': float32 linear HDR through the inverse-Reinhard stage."""
+    output; 'hdr' / 'hdr_as_written': float32 linear HDR through the inverse-Reinhard stage; 'hdr_f16': the repaired
+    inverse as half floats (OpenEXR's HALF pixel type, clamped to 65504): half the bytes to copy back."""
     import torch
     x = _check_frames(frames_u8)
     n, h, w, _ = x.shape
     dev = torch.device('cuda', model.device)
     xd = torch.from_numpy(x).to(dev)
-    yd = torch.empty((n, h, w, 3), dtype=torch.uint8 if out == 'u8' else torch.float32, device=dev)
+    yd = torch.empty((n, h, w, 3), dtype=getattr(torch, OUT_DTYPES[out]), device=dev)
     with torch.cuda.device(dev):
         s = torch.cuda.current_stream()
         predict_frames_device(model, xd.data_ptr(), n, h, w, yd.data_ptr(), out, key, s.cuda_stream)

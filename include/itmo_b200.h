@@ -167,11 +167,13 @@ enum itmo_out_kind {
   ITMO_OUT_U8 = 0,            /* trunc(p*255) uint8, what predict.py:64 writes */
   ITMO_OUT_F32 = 1,           /* sigmoid output float32 */
   ITMO_OUT_HDR_INTENDED = 2,  /* float32 linear HDR: m-files/inverse_Reinhard.m with its sign error repaired */
-  ITMO_OUT_HDR_AS_WRITTEN = 3 /* float32: m-files/inverse_Reinhard.m:2-23 literally (degenerate) */
+  ITMO_OUT_HDR_AS_WRITTEN = 3, /* float32: m-files/inverse_Reinhard.m:2-23 literally (degenerate) */
+  ITMO_OUT_HDR_INTENDED_F16 = 4 /* the repaired inverse as IEEE half floats (OpenEXR's HALF pixel type), clamped to 65504:
+                                   half the bytes to bring back to the host; the arithmetic is the float64 one of kind 2 */
 };
 /* Tile plan along one axis: returns the tile count, fills origin / valid range [lo,hi) per tile (up to cap). */
 int itmo_tile_axis_plan(int extent, int* origin, int* valid_lo, int* valid_hi, int cap);
-/* frames_dev: [n_frames,h,w,3] uint8 on the device; out_dev: same shape, uint8 or float32 by out_kind.
+/* frames_dev: [n_frames,h,w,3] uint8 on the device; out_dev: same shape, uint8, float32 or half by out_kind.
  * `key` is the geometric-mean luminance the repaired inverse normalises to (Reinhard.m:20 uses 0.18). */
 int itmo_predict_frames(itmo_ctx* ctx, const void* frames_dev, int n_frames, int h, int w, void* out_dev, int out_kind,
                         double key, void* stream);

@@ -97,6 +97,15 @@ def test_fused_hdr_output_equals_u8_then_inverse(model, frame):
     assert np.allclose(bad[~np.isnan(bad)], wantb[~np.isnan(wantb)], rtol=2e-5, atol=1e-30)
 
 
+def test_half_float_hdr_output_is_the_float_output_rounded(model, frame):
+    """out='hdr_f16' (ITMO_OUT_HDR_INTENDED_F16): the float32 result of out='hdr', clamped to 65504 and rounded to half."""
+    from cnn_itmo_b200 import frames
+    hdr = frames.predict_frames(model, frame, out='hdr', key=0.18)
+    half = frames.predict_frames(model, frame, out='hdr_f16', key=0.18)
+    assert half.dtype == np.float16 and half.shape == hdr.shape
+    assert np.array_equal(half, np.minimum(hdr, 65504.0).astype(np.float16))
+
+
 def test_4k_frame_properties(calibrated_weights):
     """BASELINE config 4 at full size: one 3840x2160 frame = 84 tiles. Properties instead of an oracle run:
     finite, equal to the 512x512 model on a tile that touches no seam, and flip-consistent tile plan."""

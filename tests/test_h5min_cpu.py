@@ -106,3 +106,40 @@ def test_empty_and_fixed_string_arrays(tmp_path):
     assert list(f['g'].attrs['names']) == [b'a', b'bcd', b'ef']
     np.testing.assert_array_equal(f['g/u8'].read(), np.arange(12, dtype=np.uint8).reshape(3, 4))
     np.testing.assert_array_equal(f['g/f64'].read(), np.linspace(0, 1, 7))
+
+
+# ---- files h5min did NOT write: hand-assembled from the HDF5 specification (tests/golden/make_h5py_style.py) -------------
+@pytest.mark.parametrize('leaf_k,internal_k,chunked_every,cont', [(1, 2, 3, True), (4, 16, 0, True), (2, 1, 1, False)])
+def test_h5py_style_checkpoint_is_read_by_load_model_reader(tmp_path, leaf_k, internal_k, chunked_every, cont):
+    """A Keras-2.2.4 / h5py-2.x style file of the whole U-Net built by an independent assembler: multi-level group
+    B-trees in strcmp (not layer) order, attributes in object-header continuation blocks, fixed-length string scalars
+    and arrays, a vlen string through the global heap, a zero-length float64 weight_names, contiguous and chunked
+    (overhanging edge chunks) float32 datasets, messages to skip. Read back through the reader load_model uses."""
+    import importlib.util
+    import os
+    spec = importlib.util.spec_from_file_location(
+        'make_h5py_style', os.path.join(os.path.dirname(__file__), 'golden', 'make_h5py_style.py'))
+    mk = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mk)
+    from cnn_itmo_b200 import checkpoint, graph
+    from oracle import unet_ref as R
+    ws = R.synthetic_weights(31)
+    data = mk.build_keras_file(ws, graph.keras_layers(), checkpoint.model_config(), checkpoint.training_config(),
+                               leaf_k=leaf_k, internal_k=internal_k, chunked_every=chunked_every,
+                               attrs_in_continuation=cont)
+    p = tmp_path / 'h5py_style.hdf5'
+    p.write_bytes(data)
+    got, meta = checkpoint.read_checkpoint(str(p))
+    assert len(got) == graph.NUM_LAYERS
+    for l, a, b in zip(graph.LAYERS, got, ws):
+        for key in b:
+            assert np.array_equal(a[key], np.asarray(b[key], np.float32)), (l.name, key)
+    assert meta['keras_version'] == '2.2.4' and meta['backend'] == 'tensorflow'
+    assert meta['model_config']['config']['name'] == graph.MODEL_NAME
+    assert meta['training_config']['loss'] == 'mse'
+    assert abs(meta['bn_epsilon'] - graph.BN_EPS) < 1e-12
+    # the raw group order is strcmp order, which differs from the model order the reader must follow
+    f = h5min.File(str(p))
+    raw_order = f['model_weights'].keys()
+    assert raw_order == sorted(raw_order) and raw_order != [k.name for k in graph.keras_layers()]
+    f.close()
