@@ -671,8 +671,23 @@ def run_train_leg(a, hz, steps=None, warmup=None):
         raise SystemExit(f'bench.py: global batch {a.train_batch} is not divisible by {world} ranks')
     per_rank = a.train_batch // world
     mb = min(a.micro_batch, per_rank)
-    tr = train.Trainer(M.initial_weights(seed=218), micro_batch=mb, image_hw=(IMG, IMG), device=hz.local_rank,
-                       optimizer='rmsprop', seed=0)
+    # gradient exchange: the fused peer-memory kernel (reduce-scatter -> RMSprop on the local shard -> all-gather, one
+    # launch, no NCCL on the data path) when the ranks can map each other's windows, else NCCL all-reduce + optimizer
+    tr = None
+    exchange = a.exchange
+    if exchange in ('auto', 'fused'):
+        try:
+            tr = train.Trainer(M.initial_weights(seed=218), micro_batch=mb, image_hw=(IMG, IMG), device=hz.local_rank,
+                               optimizer='rmsprop', seed=0, exchange='fused')
+            exchange = 'fused'
+        except Exception as e:  # noqa: BLE001  (raised on every rank together, see Trainer.__init__)
+            if a.exchange == 'fused':
+                raise
+            log(f'fused exchange unavailable ({e!r}); using NCCL all-reduce')
+            exchange = 'nccl'
+    if tr is None:
+        tr = train.Trainer(M.initial_weights(seed=218), micro_batch=mb, image_hw=(IMG, IMG), device=hz.local_rank,
+                           optimizer='rmsprop', seed=0)
     x, y, data = synth_pairs(hz, per_rank, seed=7 + hz.rank)
     loss_count = float(a.train_batch) * IMG * IMG * 3
     comm_events = []
@@ -686,10 +701,14 @@ def run_train_leg(a, hz, steps=None, warmup=None):
                         freeze_moving=(k + 1 < len(starts)))
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(hz.stream)
-        tr.allreduce_grads()
-        e1.record(hz.stream)
+        if exchange == 'fused':
+            tr.exchange_and_update()       # ONE kernel: reduce-scatter + RMSprop + all-gather (+ the operand repack)
+            e1.record(hz.stream)
+        else:
+            tr.allreduce_grads()
+            e1.record(hz.stream)
+            tr.update()
         comm_events.append((e0, e1))
-        tr.update()
 
     for _ in range(warmup):
         step()
@@ -755,11 +774,18 @@ def run_train_leg(a, hz, steps=None, warmup=None):
                 'tflops_per_gpu': round(whole, 1),
                 'whole_step_frac_of_peak': round(whole / peaks['tflops_sustained'], 4),
                 'allreduce_ms': round(allreduce_ms, 3), 'h2d_ms': round(h2d_ms, 3),
+                'exchange': {'mode': exchange,
+                             'what_allreduce_ms_times': ('itmo_exchange_step: reduce-scatter + optimizer + all-gather over '
+                                                         'NVLink peer memory + operand repack (includes waiting for the '
+                                                         'slowest rank)') if exchange == 'fused' else
+                             'the NCCL all-reduce alone (includes waiting for the slowest rank)'},
                 'config': {'workload': f'data-parallel training step, global batch {a.train_batch} ({per_rank} per GPU in '
                                        f'micro-batches of {mb}), 512x512x3 uint8 SDR in, float32 target, random-init '
                                        'weights, Dropout on, RMSprop (BASELINE configs[4])',
                            'global_batch': a.train_batch, 'micro_batch': mb,
-                           'parallelism': f'dp{world} (one NCCL all-reduce of the 44.6 MB flat fp32 gradient per step)',
+                           'parallelism': f'dp{world} (' + ('fused reduce-scatter / RMSprop / all-gather kernel over NVLink peer '
+                                                             'memory' if exchange == 'fused' else
+                                                             'one NCCL all-reduce of the 44.6 MB flat fp32 gradient per step') + ')',
                            'l2': 'every micro-batch streams > 10 GB of activations; no explicit flush'},
                 'clocks': clocks,
                 'e2e': {'value': round(e2e, 2), 'unit': 'images/s', 'h2d_bytes_per_step': int(hx.nbytes + hy.nbytes),
@@ -781,7 +807,7 @@ def run_train_leg(a, hz, steps=None, warmup=None):
 
 
 def compact(line, keys=('value', 'unit', 'ms_per_step', 'steps', 'scaling', 'dtype', 'data', 'e2e', 'roofline',
-                        'allreduce_ms', 'h2d_ms', 'tflops_per_gpu', 'whole_step_frac_of_peak', 'frames_per_s',
+                        'allreduce_ms', 'exchange', 'h2d_ms', 'tflops_per_gpu', 'whole_step_frac_of_peak', 'frames_per_s',
                         'executed_tflops_per_gpu', 'gpu_launches', 'train_loss', 'parity', 'config')):
     if line is None:
         return None
@@ -810,6 +836,9 @@ def main(argv=None) -> int:
     ap.add_argument('--no-cpu', action='store_true', help='skip the cpu_baseline leg')
     ap.add_argument('--parity-images', type=int, default=8, help='images of the parity leg against the oracle')
     ap.add_argument('--train-batch', type=int, default=512, help='GLOBAL batch of the training leg (configs[4]: 512)')
+    ap.add_argument('--exchange', default='auto', choices=['auto', 'fused', 'nccl'],
+                    help='gradient exchange of the training leg: fused peer-memory kernel, NCCL all-reduce, or fused with '
+                         'NCCL as the fallback when CUDA IPC is unavailable (auto)')
     ap.add_argument('--micro-batch', type=int, default=32, help='images per forward/backward pass of the training leg')
     ap.add_argument('--workload', default='batch', choices=['batch', '4k', 'train'],
                     help="'batch' = BASELINE configs[2] (default, the headline, followed by the secondary legs); "

@@ -18,6 +18,7 @@ OUT_U8, OUT_F32, OUT_HDR_INTENDED, OUT_HDR_AS_WRITTEN, OUT_HDR_INTENDED_F16 = 0,
 NUM_LAYERS = 19
 TRAIN_NO_DROPOUT, TRAIN_FREEZE_MOVING, TRAIN_KEEP_GRADS = 1, 2, 4
 OPT_RMSPROP, OPT_ADAM = 0, 1
+IPC_HANDLE_BYTES = 64
 
 
 class LayerWeights(ctypes.Structure):
@@ -93,6 +94,13 @@ SIGNATURES = {
     'itmo_virtual_camera': (c_int, [c_void_p, c_int, c_int, c_int, POINTER(CameraParams), c_void_p, c_int, c_void_p]),
     'itmo_reinhard_target': (c_int, [c_void_p, c_int, c_int, c_int, c_double, c_void_p, c_int, c_void_p]),
     'itmo_augment': (c_int, [c_void_p, c_int, c_int, c_int, c_int, POINTER(AffineParams), c_void_p, c_float, c_void_p]),
+    # fused gradient exchange over NVLink peer memory (SURVEY §8 e, K8)
+    'itmo_exchange_create': (c_int, [POINTER(c_void_p), c_int, c_void_p]),
+    'itmo_exchange_grads': (c_void_p, [c_void_p]),
+    'itmo_exchange_params': (c_void_p, [c_void_p]),
+    'itmo_exchange_open': (c_int, [c_void_p, c_int, c_int, c_void_p]),
+    'itmo_exchange_step': (c_int, [c_void_p, c_void_p, c_int, c_float, c_float, c_float, c_float, c_float, c_void_p]),
+    'itmo_exchange_destroy': (None, [c_void_p]),
     'itmo_wgrad3x3': (c_int, [c_void_p, c_int, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
     'itmo_dgrad3x3': (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_int, c_void_p, c_void_p]),
 }

@@ -91,6 +91,10 @@ struct ConvParams {
   int a_stage_bytes;   // halo tile bytes rounded up to 1024
   int n_a_stages, n_b_stages;
   int b_resident;      // 1: all (channel block, tap) weight tiles are loaded once and kept in shared memory
+  int n_stationary;    // 1 (with b_resident, several N tiles): a CTA (pair) keeps ONE N tile — (block index) mod n_tiles —
+                       // for all its M tiles, so that N tile's weights stay resident instead of being re-streamed from L2
+                       // for every 128 pixels (the transposed convolutions were bound by exactly that: convT_3 moved
+                       // 192 KB L2 -> SMEM per tile of which 128 KB weights). The grid is a multiple of n_tiles.
   int store_mode;      // StoreMode (Elem = float only)
   int acc_split;       // S >= 1 TMEM accumulators per M block, summed in fp32 registers by the epilogue. The
                        // tensor core adds into its fp32 accumulator with truncation, a bias that grows with the
@@ -112,9 +116,9 @@ struct ConvParams {
   // as immediate-indexed constant operands: no shared-memory broadcast reads on the L1 data pipe these layers are
   // bound by (it is shared with the tensor core's operand reads).
   int const_affine;
-  alignas(16) float c_bias[64];
-  alignas(16) float c_scale[64];
-  alignas(16) float c_shift[64];
+  alignas(16) float c_bias[128];    // transposed conv with 64 output channels: the vectors twice (indexed by column & 127)
+  alignas(16) float c_scale[128];
+  alignas(16) float c_shift[128];
   // fp16 storage only: incremented once per (thread, 32-channel chunk) in which a value was clamped to +-65504 by the
   // saturating pack, so a checkpoint whose activations leave fp16's range cannot clip silently (itmo_saturation_count)
   unsigned long long* sat_count;
@@ -432,9 +436,15 @@ __device__ __forceinline__ void epilogue_fast(const ConvParams& p, uint32_t tmem
   const int tiles_x = p.W / kTileW;
   const int tiles_y = p.H / kBlkH;
   const int m_tiles = p.NB * tiles_y * tiles_x;
-  const int total_tiles = kPair ? (m_tiles >> 1) * p.n_tiles : m_tiles * p.n_tiles;
-  const int unit0 = kPair ? int(blockIdx.x >> 1) : int(blockIdx.x);
-  const int unit_stride = kPair ? int(gridDim.x >> 1) : int(gridDim.x);
+  const int m_units = kPair ? (m_tiles >> 1) : m_tiles;
+  const int cta_unit = kPair ? int(blockIdx.x >> 1) : int(blockIdx.x);
+  const int cta_units = kPair ? int(gridDim.x >> 1) : int(gridDim.x);
+  // work units of this CTA (pair): (N tile, M unit) interleaved, or — n_stationary — M units of one fixed N tile
+  const bool stat = p.n_stationary != 0;
+  const int total_tiles = stat ? m_units : m_units * p.n_tiles;
+  const int unit0 = stat ? cta_unit / p.n_tiles : cta_unit;
+  const int unit_stride = stat ? cta_units / p.n_tiles : cta_units;
+  const int n_fixed = cta_unit % p.n_tiles;
   // pair: the accumulators of both CTAs are handed back through the leader's barrier
   const uint32_t empty_remote[2] = {kPair ? sm100::mapa_u32(&tmem_empty_bar[0], 0) : 0u,
                                     kPair ? sm100::mapa_u32(&tmem_empty_bar[1], 0) : 0u};
@@ -446,8 +456,8 @@ __device__ __forceinline__ void epilogue_fast(const ConvParams& p, uint32_t tmem
   int acc = 0;
   uint32_t acc_phase = 0;
   for (int unit = unit0; unit < total_tiles; unit += unit_stride) {
-    const int n_tile = unit % p.n_tiles;
-    int m = unit / p.n_tiles;
+    const int n_tile = stat ? n_fixed : unit % p.n_tiles;
+    int m = stat ? unit : unit / p.n_tiles;
     if constexpr (kPair) m = 2 * m + int(cta_rank);
     const int tx = m % tiles_x;
     m /= tiles_x;
@@ -491,7 +501,7 @@ __device__ __forceinline__ void epilogue_fast(const ConvParams& p, uint32_t tmem
 #pragma unroll
             for (int i = 0; i < 32; i += 2) relu_bias2(v[h][i], v[h][i + 1], cpair(p.c_bias, col + i), f[i], f[i + 1]);
           } else if constexpr (kConst) {
-            const int cc = kConvT ? (col & 63) : col;                 // transposed conv: cout == 64
+            const int cc = kConvT ? (col & 127) : col;                // transposed conv: cout == 128, or 64 stored twice
 #pragma unroll
             for (int i = 0; i < 32; i += 2) {
               float r0, r1;
@@ -673,9 +683,14 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
   const int tiles_y = p.H / kBlkH;
   const int m_tiles = p.NB * tiles_y * tiles_x;
   // work units: one tile per CTA, or two horizontally adjacent tiles (same N tile) per CTA pair
-  const int total_tiles = kPair ? (m_tiles >> 1) * p.n_tiles : m_tiles * p.n_tiles;
-  const int unit0 = kPair ? int(blockIdx.x >> 1) : int(blockIdx.x);
-  const int unit_stride = kPair ? int(gridDim.x >> 1) : int(gridDim.x);
+  const int m_units = kPair ? (m_tiles >> 1) : m_tiles;
+  const int cta_unit = kPair ? int(blockIdx.x >> 1) : int(blockIdx.x);
+  const int cta_units = kPair ? int(gridDim.x >> 1) : int(gridDim.x);
+  const bool stat = p.n_stationary != 0;        // see ConvParams::n_stationary
+  const int total_tiles = stat ? m_units : m_units * p.n_tiles;
+  const int unit0 = stat ? cta_unit / p.n_tiles : cta_unit;
+  const int unit_stride = stat ? cta_units / p.n_tiles : cta_units;
+  const int n_fixed = cta_unit % p.n_tiles;
   int kb_total = 0;
   for (int s = 0; s < p.n_seg; ++s) kb_total += p.seg_kb[s];
   const int halo_w = tile_w + 2 * p.pad;                    // halo pitch in pixels
@@ -773,17 +788,17 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
           sm100::tma_load_3d(dst, &p.tmB, bar, k0, row0, tap, sm100::kEvictLast);
       };
       if (p.b_resident) {
-        // all weight tiles of the layer, once (n_tiles == 1 in this mode)
+        // all weight tiles of the layer — of this CTA's N tile when there are several (n_stationary) — once
         arm(&b_full[0], uint32_t(kb_total * p.taps) * Cfg::kBBytes);
         for (int kb = 0; kb < kb_total; ++kb)
           for (int tap = 0; tap < p.taps; ++tap)
-            load_b(smem_b + (kb * p.taps + tap) * kBStage, &b_full[0], kb * Cfg::kBK, 0, tap);
+            load_b(smem_b + (kb * p.taps + tap) * kBStage, &b_full[0], kb * Cfg::kBK, (stat ? n_fixed : 0) * BLOCK_N, tap);
       }
       int sa = 0, sb = 0, a_loads = 0;
       uint32_t pa = 0, pb = 0;
       for (int unit = unit0; unit < total_tiles; unit += unit_stride) {
-        const int n_tile = unit % p.n_tiles;
-        int m = unit / p.n_tiles;
+        const int n_tile = stat ? n_fixed : unit % p.n_tiles;
+        int m = stat ? unit : unit / p.n_tiles;
         if constexpr (kPair) m = 2 * m + int(cta_rank);
         const int tx = m % tiles_x;
         m /= tiles_x;
@@ -946,8 +961,8 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int tile = unit0; tile < total_tiles; tile += unit_stride) {
-      const int n_tile = tile % p.n_tiles;
-      int m = tile / p.n_tiles;
+      const int n_tile = stat ? n_fixed : tile % p.n_tiles;
+      int m = stat ? tile : tile / p.n_tiles;
       const int tx = m % tiles_x;
       m /= tiles_x;
       const int ty = m % tiles_y;

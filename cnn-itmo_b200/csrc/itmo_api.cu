@@ -369,12 +369,14 @@ int launch_conv_epi(const itmo::ConvParams& p, int total_tiles, int smem_bytes, 
       max_pairs = std::min(n, num_sms() / 2);
       cfg.dynamicSmemBytes = size_t(smem_bytes);
     }
-    const int pairs = std::min(total_tiles / 2, max_pairs);
+    int pairs = std::min(total_tiles / 2, max_pairs);
+    if (p.n_stationary) pairs = pairs / p.n_tiles * p.n_tiles;   // every N tile gets the same number of pairs
     cfg.gridDim = dim3(2 * pairs);
     ITMO_CUDA(cudaLaunchKernelEx(&cfg, kern, p));
     return ITMO_OK;
   }
-  const int grid = std::min(total_tiles, num_sms());
+  int grid = std::min(total_tiles, num_sms());
+  if (p.n_stationary) grid = grid / p.n_tiles * p.n_tiles;
   kern<<<grid, itmo::kNumThreads, smem_bytes, stream>>>(p);
   ITMO_CUDA(cudaGetLastError());
   return ITMO_OK;
@@ -553,7 +555,8 @@ int run_conv(const ConvArgs& a, cudaStream_t stream) {
         if (can_const && rows == block_n && block_n <= 64) epi |= itmo::kEpiConstAffine;
       } else {
         epi = itmo::kEpiConvT;
-        if (can_const && a.cout == 64 && block_n == 256) epi |= itmo::kEpiConstAffine;
+        static const int const128 = env_int("ITMO_CONVT_CONST128", 1);
+        if (can_const && (a.cout == 64 || (a.cout == 128 && const128)) && block_n == 256) epi |= itmo::kEpiConstAffine;
       }
     }
   }
@@ -593,8 +596,20 @@ int run_conv(const ConvArgs& a, cudaStream_t stream) {
   const int epi_bytes = tma_store ? epi_one * epi_bufs : 0;
   const int budget = itmo::kSmemLimit - 1024 - itmo::kAuxBytes - stats_bytes - epi_bytes;
   const int n_tiles = rows / block_n;
-  int n_a, n_b, resident = 0;
-  if (!no_resident && n_tiles == 1 && kb_total * taps * b_stage + 2 * a_stage <= budget) {
+  int n_a, n_b, resident = 0, stationary = 0;
+  // several N tiles, one tap (transposed convolutions), specialised epilogue: every CTA (pair) keeps ONE N tile so its
+  // weights stay resident (ConvParams::n_stationary; ITMO_N_STATIONARY=0: A/B)
+  static const int allow_stationary = env_int("ITMO_N_STATIONARY", 1);
+  const int cta_units_max = (epi & itmo::kEpiPair) ? num_sms() / 2 : num_sms();
+  if (allow_stationary && !no_resident && n_tiles > 1 && taps == 1 && (epi & 15) == itmo::kEpiConvT && block_n == 256 &&
+      swz == 128 && cta_units_max >= n_tiles &&
+      a.n * (a.h / itmo::kBlkH) * (a.w / (itmo::kBlkW * nm)) / ((epi & itmo::kEpiPair) ? 2 : 1) >= 3 * (cta_units_max / n_tiles) &&
+      kb_total * b_stage + 3 * a_stage <= budget) {
+    resident = 1;
+    stationary = 1;
+    n_b = kb_total;
+    n_a = std::min(itmo::kMaxAStages, (budget - n_b * b_stage) / a_stage);
+  } else if (!no_resident && n_tiles == 1 && kb_total * taps * b_stage + 2 * a_stage <= budget) {
     resident = 1;
     n_b = kb_total * taps;
     n_a = std::min(std::min(itmo::kMaxAStages, max_a), (budget - n_b * b_stage) / a_stage);
@@ -675,6 +690,7 @@ int run_conv(const ConvArgs& a, cudaStream_t stream) {
   p.n_a_stages = n_a;
   p.n_b_stages = n_b;
   p.b_resident = resident;
+  p.n_stationary = stationary;
   static const int dbg = env_int("ITMO_DBG", 0);
   p.dbg = dbg;
   p.acc_split = acc_split;
@@ -690,9 +706,12 @@ int run_conv(const ConvArgs& a, cudaStream_t stream) {
       (allow_const && a.h_bias && a.h_scale && a.h_shift && conv && !a.one_tap && n_tiles == 1 && a.cout == block_n &&
        block_n <= 64 && !a.no_relu && !a.stats)) {
     p.const_affine = 1;
-    memcpy(p.c_bias, a.h_bias, a.cout * sizeof(float));
-    memcpy(p.c_scale, a.h_scale, a.cout * sizeof(float));
-    memcpy(p.c_shift, a.h_shift, a.cout * sizeof(float));
+    for (int rep = 0; rep * a.cout < 128; ++rep) {   // 64 channels: stored twice (see ConvParams::c_bias)
+      const int n = std::min(a.cout, 128);
+      memcpy(p.c_bias + rep * n, a.h_bias, n * sizeof(float));
+      memcpy(p.c_scale + rep * n, a.h_scale, n * sizeof(float));
+      memcpy(p.c_shift + rep * n, a.h_shift, n * sizeof(float));
+    }
   }
   p.sat_count = a.precision == ITMO_PREC_FP16 ? a.sat_count : nullptr;
   p.bias = a.bias;
@@ -1670,4 +1689,5 @@ int itmo_conv3x3_bn_rgb(int precision, const void* in, int in_dtype, int n, int 
 }  // extern "C"
 
 #include "train_api.cuh"
+#include "exchange_api.cuh"
 #include "datagen_api.cuh"

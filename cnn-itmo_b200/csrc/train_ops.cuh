@@ -613,27 +613,37 @@ __global__ void __launch_bounds__(256) rgb_to_c32_kernel(const InT* __restrict__
 }
 
 // ---- optimizer over the flat parameter buffer -----------------------------------------------------------------------
+// One element of the optimizer step, shared by the plain kernels below and by the fused exchange kernel (exchange.cuh);
+// explicit round-to-nearest intrinsics so that every caller rounds identically whatever the compiler would contract.
 // Keras RMSprop (model.py:281 'rmsprop': lr 1e-3, rho 0.9, eps 1e-7):  a = rho a + (1-rho) g^2;  p -= lr g / (sqrt(a) + eps)
+// Keras Adam (model.py:280,282 comments: lr 1e-3 / 2e-3, beta_1 0.5):  lr_t = lr sqrt(1-b2^t)/(1-b1^t);
+// m = b1 m + (1-b1) g; v = b2 v + (1-b2) g^2; p -= lr_t m / (sqrt(v) + eps)       (lr = lr_t for Adam; b1 = rho for RMSprop)
+__device__ __forceinline__ float opt_element(bool adam, float lr, float b1, float b2, float eps, float gscale, float p,
+                                             float g, float& s0, float& s1) {
+  g = __fmul_rn(g, gscale);
+  if (adam) {
+    s0 = __fmaf_rn(b1, s0, __fmul_rn(1.f - b1, g));
+    s1 = __fmaf_rn(b2, s1, __fmul_rn(__fmul_rn(1.f - b2, g), g));
+    return __fsub_rn(p, __fdiv_rn(__fmul_rn(lr, s0), __fadd_rn(__fsqrt_rn(s1), eps)));
+  }
+  s0 = __fmaf_rn(b1, s0, __fmul_rn(__fmul_rn(1.f - b1, g), g));
+  return __fsub_rn(p, __fdiv_rn(__fmul_rn(lr, g), __fadd_rn(__fsqrt_rn(s0), eps)));
+}
 __global__ void rmsprop_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ a, size_t n,
                                float lr, float rho, float eps, float gscale) {
   for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n; i += size_t(gridDim.x) * blockDim.x) {
-    const float gi = g[i] * gscale;
-    const float ai = rho * a[i] + (1.f - rho) * gi * gi;
-    a[i] = ai;
-    p[i] -= lr * gi / (sqrtf(ai) + eps);
+    float s0 = a[i], s1 = 0.f;
+    p[i] = opt_element(false, lr, rho, 0.f, eps, gscale, p[i], g[i], s0, s1);
+    a[i] = s0;
   }
 }
-// Keras Adam (model.py:280,282 comments: lr 1e-3 / 2e-3, beta_1 0.5):  lr_t = lr sqrt(1-b2^t)/(1-b1^t);
-// m = b1 m + (1-b1) g; v = b2 v + (1-b2) g^2; p -= lr_t m / (sqrt(v) + eps)
 __global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
                             float* __restrict__ v, size_t n, float lr_t, float b1, float b2, float eps, float gscale) {
   for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n; i += size_t(gridDim.x) * blockDim.x) {
-    const float gi = g[i] * gscale;
-    const float mi = b1 * m[i] + (1.f - b1) * gi;
-    const float vi = b2 * v[i] + (1.f - b2) * gi * gi;
-    m[i] = mi;
-    v[i] = vi;
-    p[i] -= lr_t * mi / (sqrtf(vi) + eps);
+    float s0 = m[i], s1 = v[i];
+    p[i] = opt_element(true, lr_t, b1, b2, eps, gscale, p[i], g[i], s0, s1);
+    m[i] = s0;
+    v[i] = s1;
   }
 }
 

@@ -141,8 +141,30 @@ def optimizer_weights_to_flat(weights: Sequence[np.ndarray], layout, optimizer: 
     return state, it
 
 
+class _DeviceArray:
+    """A float32 device buffer owned by libitmo_b200.so, viewed by torch through __cuda_array_interface__ (no copy)."""
+
+    def __init__(self, ptr: int, n: int):
+        self.__cuda_array_interface__ = {'shape': (int(n),), 'typestr': '<f4', 'data': (int(ptr), False), 'version': 3,
+                                         'strides': None}
+
+
+def shard_bounds(n: int, world: int, rank: int) -> Tuple[int, int]:
+    """[begin, end) of the flat parameter buffer that `rank` owns in the fused exchange (itmo_exchange_step computes the
+    same): ceil(n / world) rounded up to 4 floats per rank, the last rank takes what is left."""
+    per = ((n + world - 1) // world + 3) // 4 * 4
+    b = min(n, per * rank)
+    return b, min(n, b + per)
+
+
 class Trainer:
-    """Batch statistics note: BatchNormalization's batch mean / variance (and its backward) are taken over ONE
+    """Gradient exchange (`exchange`): 'nccl' = ONE all-reduce of the flat gradient buffer, then the optimizer on every
+    rank; 'fused' = itmo_exchange_step: reduce-scatter -> optimizer on the local 1/N shard -> all-gather as ONE kernel
+    over NVLink peer memory (the flat buffers live in an IPC-shared window; torch.distributed only carries the 64-byte
+    handles at start-up). With 'fused' only the owner keeps a shard's optimizer state current: get_optimizer_weights
+    gathers the shards first.
+
+    Batch statistics note: BatchNormalization's batch mean / variance (and its backward) are taken over ONE
     micro-batch of this rank, not over the whole global batch — Keras on one device normalises over the whole batch it
     is fed (main.py:87 feeds 2 images). With N <= micro_batch on one rank the two agree exactly; larger batches are a
     gradient-accumulation approximation, like per-replica statistics in Keras' own multi-GPU data parallelism. The
@@ -154,7 +176,7 @@ class Trainer:
 
     def __init__(self, weights: Sequence[Dict[str, np.ndarray]], micro_batch: int = 8, image_hw=(512, 512),
                  device: int = 0, optimizer: str = 'rmsprop', lr: Optional[float] = None, seed: Optional[int] = 0,
-                 **opt_kwargs):
+                 exchange: str = 'nccl', **opt_kwargs):
         import torch
         if not torch.cuda.is_available():
             raise _lib.ItmoError('the training step needs an sm_100a GPU: there is no CPU fallback')
@@ -176,8 +198,39 @@ class Trainer:
         dev = torch.device('cuda', self.device)
         self._torch = torch
         self._dev = dev
-        self.params = torch.zeros(self.n_params, dtype=torch.float32, device=dev)
-        self.grads = torch.zeros(self.n_params, dtype=torch.float32, device=dev)
+        if exchange not in ('nccl', 'fused'):
+            raise ValueError("exchange must be 'nccl' or 'fused'")
+        self.exchange = exchange
+        self._x = ctypes.c_void_p()
+        if exchange == 'fused':
+            # the flat gradient / parameter buffers live in the library's IPC-shared window
+            handle = ctypes.create_string_buffer(_lib.IPC_HANDLE_BYTES)
+            with torch.cuda.device(dev):
+                _lib.check(lib.itmo_exchange_create(ctypes.byref(self._x), self.device, handle))
+                self.params = torch.as_tensor(_DeviceArray(lib.itmo_exchange_params(self._x), self.n_params), device=dev)
+                self.grads = torch.as_tensor(_DeviceArray(lib.itmo_exchange_grads(self._x), self.n_params), device=dev)
+            world, rank = world_info()
+            if world > 1:
+                import torch.distributed as dist
+                handles = [None] * world
+                dist.all_gather_object(handles, handle.raw)
+                err = None
+                try:
+                    _lib.check(lib.itmo_exchange_open(self._x, rank, world, b''.join(handles)))
+                except _lib.ItmoError as ex:     # every rank must learn about it: the others are about to wait for this one
+                    err = ex
+                ok = torch.tensor([0 if err else 1], dtype=torch.int32, device=dev)
+                dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+                if int(ok[0]) == 0:
+                    self.params = self.grads = None
+                    lib.itmo_exchange_destroy(self._x)
+                    self._x = ctypes.c_void_p()
+                    raise err or _lib.ItmoError('fused exchange: a peer rank could not map the windows (CUDA IPC)')
+            else:
+                _lib.check(lib.itmo_exchange_open(self._x, 0, 1, None))
+        else:
+            self.params = torch.zeros(self.n_params, dtype=torch.float32, device=dev)
+            self.grads = torch.zeros(self.n_params, dtype=torch.float32, device=dev)
         self.opt_state = torch.zeros(2 * self.n_params, dtype=torch.float32, device=dev)
         self.bn_moving = torch.zeros(2 * self.n_bn, dtype=torch.float32, device=dev)
         self._h = ctypes.c_void_p()
@@ -212,6 +265,10 @@ class Trainer:
         if getattr(self, '_h', None):
             _lib.load().itmo_trainer_destroy(self._h)
             self._h = ctypes.c_void_p()
+        if getattr(self, '_x', None):
+            self.params = self.grads = None          # views of the window
+            _lib.load().itmo_exchange_destroy(self._x)
+            self._x = ctypes.c_void_p()
 
     def __del__(self):
         try:
@@ -263,7 +320,22 @@ class Trainer:
         """The optimizer state as Keras lists it in ``model.optimizer.weights`` (what model.save writes under
         /optimizer_weights, main.py:123-124)."""
         self._torch.cuda.synchronize(self._dev)
+        self._gather_optimizer_shards()
         return optimizer_weights_from_flat(self.opt_state.cpu().numpy(), self.layout, self.optimizer, self.step_index)
+
+    def _gather_optimizer_shards(self):
+        """Fused exchange: every rank's optimizer state is current only on the shard it owns; make it whole everywhere
+        (one all-reduce of the state with the foreign shards zeroed — checkpoint time only)."""
+        world, rank = world_info()
+        if self.exchange != 'fused' or world == 1:
+            return
+        import torch.distributed as dist
+        b, e = shard_bounds(self.n_params, world, rank)
+        for h in range(2):
+            half = self.opt_state[h * self.n_params:(h + 1) * self.n_params]
+            half[:b].zero_()
+            half[e:].zero_()
+        dist.all_reduce(self.opt_state)
 
     def set_optimizer_weights(self, weights: Sequence[np.ndarray]):
         """Resume: load the state a checkpoint's /optimizer_weights group holds."""
@@ -307,6 +379,17 @@ class Trainer:
         o = self.opt
         _lib.check(_lib.load().itmo_train_update(self._h, _OPTIMIZERS[self.optimizer], o['lr'], o['beta1'], o['beta2'],
                                                  o['eps'], float(grad_scale), self._stream()))
+
+    def exchange_and_update(self, grad_scale: float = 1.0):
+        """The exchange step + optimizer of one data-parallel step: all-reduce then update ('nccl'), or the one fused
+        kernel over peer memory ('fused')."""
+        if self.exchange == 'fused':
+            o = self.opt
+            _lib.check(_lib.load().itmo_exchange_step(self._x, self._h, _OPTIMIZERS[self.optimizer], o['lr'], o['beta1'],
+                                                      o['beta2'], o['eps'], float(grad_scale), self._stream()))
+        else:
+            self.allreduce_grads()
+            self.update(grad_scale)
 
     def metrics(self, reset: bool = True) -> Tuple[float, float]:
         sq, hits = ctypes.c_double(), ctypes.c_double()
@@ -354,8 +437,7 @@ class Trainer:
                           freeze_moving=(k + 1 < len(starts)))
             xs.record_stream(main)
             ys.record_stream(main)
-        self.allreduce_grads()
-        self.update()
+        self.exchange_and_update()
         sq, hits = self.metrics()
         if world > 1:
             t = torch.tensor([sq, hits], dtype=torch.float64, device=self._dev)

@@ -278,6 +278,30 @@ typedef struct itmo_affine_params {
 int itmo_augment(const void* in_dev, int in_dtype, int n, int h, int w, const itmo_affine_params* params_host,
                  float* out_dev, float scale, void* stream);
 
+/* ---- fused gradient exchange over NVLink peer memory (replaces the ncclAllReduce + itmo_train_update pair
+ * of a data-parallel step, main.py:126-132 run on N GPUs of one box) -------------------------------------------------------
+ * ONE kernel per step and rank: reduce-scatter (peer loads of every rank's gradient shard, summed IN RANK ORDER) ->
+ * optimizer on the local 1/N shard -> all-gather (peer stores of the updated parameters into every rank's buffer), between
+ * two flag barriers in the peers' windows. One process per GPU; the windows are shared through CUDA IPC:
+ *   1. every rank: itmo_exchange_create (allocates the window holding ITS flat gradient + parameter buffers, returns the
+ *      IPC handle), then itmo_trainer_create with params_dev = itmo_exchange_params(), grads_dev = itmo_exchange_grads();
+ *   2. the caller gathers all ranks' handles (any host channel; 64 bytes each) and calls itmo_exchange_open;
+ *   3. per step, after the last itmo_train_backward: itmo_exchange_step on every rank (same arguments as
+ *      itmo_train_update; also rebuilds the tensor-core operand copies). All ranks must call it the same number of times.
+ * Every parameter is computed by exactly one rank and broadcast, so all ranks hold bit-identical parameters, and an
+ * N-rank step equals one rank accumulating the N shards in rank order bit for bit. The owner alone keeps a shard's
+ * optimizer state current (gather the shards before saving a checkpoint). world == 1 needs no open and equals
+ * itmo_train_update. */
+#define ITMO_IPC_HANDLE_BYTES 64
+typedef struct itmo_exchange itmo_exchange;
+int itmo_exchange_create(itmo_exchange** out, int device, void* ipc_handle_out /* ITMO_IPC_HANDLE_BYTES or NULL */);
+float* itmo_exchange_grads(itmo_exchange* x);
+float* itmo_exchange_params(itmo_exchange* x);
+int itmo_exchange_open(itmo_exchange* x, int rank, int world, const void* all_handles /* [world][ITMO_IPC_HANDLE_BYTES] */);
+int itmo_exchange_step(itmo_exchange* x, itmo_trainer* t, int optimizer, float lr, float beta1_or_rho, float beta2,
+                       float eps, float grad_scale, void* stream);
+void itmo_exchange_destroy(itmo_exchange* x);
+
 #ifdef __cplusplus
 }
 #endif

@@ -435,3 +435,29 @@ def test_checkpoint_resumes_optimizer_state(dev, tmp_path):
     loss = r.train_on_batch(x, y)[0]
     assert np.isfinite(loss)
     r.close()
+
+
+def test_fused_exchange_step_equals_plain_update_on_one_rank(dev):
+    """itmo_exchange_step (reduce-scatter -> optimizer -> all-gather over peer memory, ONE kernel) with a single rank is
+    the plain optimizer step: same parameters and optimizer state bit for bit, RMSprop and Adam, over two steps (the
+    window-backed flat buffers, the cooperative launch and the flag barriers are all exercised; tools/dp_check.py
+    asserts the N-rank property on real peers)."""
+    from cnn_itmo_b200 import train
+    x, y = T.synthetic_pair(2, 256, 128, seed=5)
+    ws = R.synthetic_weights(4)
+    xd, yd = torch.from_numpy(x).to(dev), torch.from_numpy(y).to(dev)
+    for opt in ('rmsprop', 'adam'):
+        a = train.Trainer(ws, micro_batch=2, image_hw=(256, 128), device=0, optimizer=opt, exchange='fused')
+        b = train.Trainer(ws, micro_batch=2, image_hw=(256, 128), device=0, optimizer=opt)
+        for step in range(2):
+            for tr in (a, b):
+                tr.zero_grad()
+                tr.backward(xd, yd, float(y.size), seed=step, dropout=True)
+                tr.exchange_and_update()
+        torch.cuda.synchronize()
+        assert torch.equal(a.params, b.params), opt
+        assert torch.equal(a.opt_state, b.opt_state), opt
+        assert a.step_index == b.step_index == 2
+        assert float((a.params - torch.from_numpy(train.flatten_layers(ws)).to(dev)).abs().max()) > 0
+        a.close()
+        b.close()

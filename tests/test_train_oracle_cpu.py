@@ -201,3 +201,17 @@ def test_data_parallel_exchange_over_two_gloo_ranks():
     with pytest.raises(ValueError):
         train.shard_range(5, 2, 0)
     assert train.shard_range(512, 8, 3) == (192, 256)
+
+
+def test_fused_exchange_shards_partition_the_flat_buffer():
+    """train.shard_bounds (what itmo_exchange_step computes on the device): the ranks' shards tile [0, n) exactly, start
+    on 4-float boundaries (128-bit peer loads) and differ by at most one vector."""
+    from cnn_itmo_b200 import train
+    n = 11159011
+    for world in range(1, 9):
+        cuts = [train.shard_bounds(n, world, r) for r in range(world)]
+        assert cuts[0][0] == 0 and cuts[-1][1] == n
+        for (b0, e0), (b1, e1) in zip(cuts, cuts[1:]):
+            assert e0 == b1 and b1 % 4 == 0
+        sizes = [e - b for b, e in cuts]
+        assert max(sizes) - min(sizes) <= 4 * world

@@ -54,7 +54,36 @@ for r in range(world):
     tr2.backward(torch.from_numpy(x[bb:ee]).to(dev), torch.from_numpy(y[bb:ee]).to(dev), count, seed=0, dropout=False)
 torch.cuda.synchronize()
 noise = float((tr2.grads - g_ref).norm() / g_ref.norm())
-out = {'world': world, 'rank': rank, 'grad_rel_vs_single_rank': rel, 'grad_bit_identical_to_single_rank': exact,
+# ---- fused exchange (itmo_exchange_step: reduce-scatter -> optimizer -> all-gather in ONE kernel over peer memory):
+# two optimizer steps on every rank's shard; all ranks must hold bit-identical parameters, equal — bit for bit, at any N,
+# because the kernel sums the shards in rank order — to ONE rank accumulating the same shards and taking plain steps.
+fused = {}
+for opt in ('rmsprop', 'adam'):
+    trf = train.Trainer(ws, micro_batch=per, device=local, optimizer=opt, exchange='fused')
+    trs = train.Trainer(ws, micro_batch=per, device=local, optimizer=opt)
+    for step in range(2):
+        trf.zero_grad()
+        trf.backward(torch.from_numpy(x[b:e]).to(dev), torch.from_numpy(y[b:e]).to(dev), count, seed=step, dropout=False)
+        trf.exchange_and_update()
+        trs.zero_grad()
+        for r in range(world):
+            bb, ee = train.shard_range(per * world, world, r)
+            trs.backward(torch.from_numpy(x[bb:ee]).to(dev), torch.from_numpy(y[bb:ee]).to(dev), count, seed=step, dropout=False)
+        trs.update()
+    torch.cuda.synchronize()
+    pf = trf.params.clone()
+    pf0 = pf.clone()
+    if world > 1:
+        dist.broadcast(pf0, 0)
+    st_f = trf.get_optimizer_weights()      # gathers the owners' shards
+    st_s = trs.get_optimizer_weights()
+    fused[opt] = {'params_bit_identical_across_ranks': bool(torch.equal(pf, pf0)),
+                  'params_bit_identical_to_single_rank_steps': bool(torch.equal(pf, trs.params)),
+                  'optimizer_state_bit_identical_to_single_rank': all(np.array_equal(a_, b_) for a_, b_ in zip(st_f, st_s)),
+                  'moved': float((pf - torch.from_numpy(train.flatten_layers(ws)).to(dev)).abs().max())}
+    trf.close()
+    trs.close()
+out = {'world': world, 'rank': rank, 'fused_exchange': fused, 'grad_rel_vs_single_rank': rel, 'grad_bit_identical_to_single_rank': exact,
        'single_rank_run_to_run_rel': noise,
        'grad_max_abs_diff_vs_rank0': same,
        'param_max_abs_diff_vs_rank0': same_p, 'grad_norm': float(g_dp.norm())}
@@ -67,7 +96,10 @@ if rank == 0:
     ok = all((o['grad_bit_identical_to_single_rank'] if world <= 2 else o['grad_rel_vs_single_rank'] <= 1e-6) and
              o['single_rank_run_to_run_rel'] == 0.0 and
              o['grad_max_abs_diff_vs_rank0'] == 0.0 and
-             o['param_max_abs_diff_vs_rank0'] == 0.0 for o in (out if isinstance(out, list) else [out]))
+             o['param_max_abs_diff_vs_rank0'] == 0.0 and
+             all(f['params_bit_identical_across_ranks'] and f['params_bit_identical_to_single_rank_steps'] and
+                 f['optimizer_state_bit_identical_to_single_rank'] and f['moved'] > 0 for f in o['fused_exchange'].values())
+             for o in (out if isinstance(out, list) else [out]))
     print('dp_check', 'OK' if ok else 'FAILED')
 if world > 1:
     dist.barrier()
