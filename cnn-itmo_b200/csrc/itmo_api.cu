@@ -601,7 +601,10 @@ int run_conv(const ConvArgs& a, cudaStream_t stream) {
   // weights stay resident (ConvParams::n_stationary; ITMO_N_STATIONARY=0: A/B)
   static const int allow_stationary = env_int("ITMO_N_STATIONARY", 1);
   const int cta_units_max = (epi & itmo::kEpiPair) ? num_sms() / 2 : num_sms();
-  if (allow_stationary && !no_resident && n_tiles > 1 && taps == 1 && (epi & 15) == itmo::kEpiConvT && block_n == 256 &&
+  // (measured: convT_3, two N tiles, -6 %; convT_1 / convT_2 with 8 / 4 N tiles as pairs are 8 % slower stationary — fewer
+  // pairs per N tile, a three-stage halo ring beside 128 KB of weights — and keep streaming; ITMO_N_STATIONARY=2 forces all)
+  if (allow_stationary && !no_resident && (n_tiles == 2 || (n_tiles > 2 && allow_stationary == 2)) && taps == 1 &&
+      (epi & 15) == itmo::kEpiConvT && block_n == 256 &&
       swz == 128 && cta_units_max >= n_tiles &&
       a.n * (a.h / itmo::kBlkH) * (a.w / (itmo::kBlkW * nm)) / ((epi & itmo::kEpiPair) ? 2 : 1) >= 3 * (cta_units_max / n_tiles) &&
       kb_total * b_stage + 3 * a_stage <= budget) {
