@@ -199,7 +199,15 @@ struct itmo_trainer {
   __nv_bfloat16* dbg_dpre[ITMO_NUM_LAYERS] = {};
   __nv_bfloat16* x32 = nullptr;
   __nv_bfloat16* g[2] = {};     // ping-pong activation gradients
-  __nv_bfloat16* gp = nullptr;  // dpre
+  __nv_bfloat16* gp = nullptr;  // dpre of the layer in flight (= gpb[k])
+  // The weight-gradient GEMMs run on a side stream: they depend only on dpre and on forward activations, nothing on the
+  // main stream's backward chain depends on them, and they are tensor / shared-memory bound while the BN-backward and
+  // pooling kernels the main stream runs next are HBM bound — two kinds of kernel that share an SM well. dpre is double
+  // buffered so the next layer's BN backward can write while this layer's wgrad still reads.
+  __nv_bfloat16* gpb[2] = {};
+  cudaStream_t s2 = nullptr;
+  cudaEvent_t ev_gp[2] = {}, ev_wg[2] = {};
+  bool wg_pending[2] = {false, false};
   __nv_bfloat16* gq = nullptr;  // pooled gradient
   float* bn_vec = nullptr;      // per layer: mean, invstd, scale, shift (4 x 512 each)
   double* stats = nullptr;      // per layer 2 x 512: totals of the BN-backward reductions
@@ -359,6 +367,15 @@ int train_backward(itmo_trainer* t, const void* x, int x_dtype, const float* y, 
       }
       ITMO_CUDA(cudaMemcpyAsync(t->dbg_dA[li], dA, npix * L.cout * 2, cudaMemcpyDeviceToDevice, s));
     }
+    // dpre buffer of this layer; the wgrad that last read it (two layers ago, on the side stream) must be done
+    static const bool side_wgrad = env_int("ITMO_TRAIN_WGRAD_STREAM", 1) != 0;
+    const int gb = side_wgrad ? ((17 - li) & 1) : 0;
+    t->gp = t->gpb[gb];
+    if (t->wg_pending[gb]) {
+      ITMO_CUDA(cudaStreamWaitEvent(s, t->ev_wg[gb], 0));
+      t->wg_pending[gb] = false;
+    }
+    cudaStream_t sw = side_wgrad ? t->s2 : s;   // stream of this layer's weight-gradient GEMMs
     {
       PhaseStamp ps(t, kPhOther, s, __LINE__);
       static const int g_red = full_wave_grid(itmo::bn_bwd_reduce_kernel, kPartialRows);
@@ -378,15 +395,19 @@ int train_backward(itmo_trainer* t, const void* x, int x_dtype, const float* y, 
     }
     if (flags & ITMO_TRAIN_KEEP_GRADS)
       ITMO_CUDA(cudaMemcpyAsync(t->dbg_dpre[li], t->gp, npix * L.cout * 2, cudaMemcpyDeviceToDevice, s));
-    // ---- weight gradient
+    // ---- weight gradient (side stream: after dpre is complete)
+    if (side_wgrad) {
+      ITMO_CUDA(cudaEventRecord(t->ev_gp[gb], s));
+      ITMO_CUDA(cudaStreamWaitEvent(sw, t->ev_gp[gb], 0));
+    }
     if (L.kind == kRgbConv) {
       {
-        PhaseStamp ps(t, kPhOther, s, __LINE__);
+        PhaseStamp ps(t, kPhOther, sw, __LINE__);
         const size_t np = size_t(nb) * hi * wi;
         if (x_dtype == ITMO_DT_U8)
-          itmo::rgb_to_c32_kernel<uint8_t><<<ew_grid(np * 4), 256, 0, s>>>((const uint8_t*)x, t->x32, np, 1.f);
+          itmo::rgb_to_c32_kernel<uint8_t><<<ew_grid(np * 4), 256, 0, sw>>>((const uint8_t*)x, t->x32, np, 1.f);
         else
-          itmo::rgb_to_c32_kernel<float><<<ew_grid(np * 4), 256, 0, s>>>((const float*)x, t->x32, np, 1.f);
+          itmo::rgb_to_c32_kernel<float><<<ew_grid(np * 4), 256, 0, sw>>>((const float*)x, t->x32, np, 1.f);
         ITMO_CUDA(cudaGetLastError());
       }
       WgradArgs w;
@@ -405,8 +426,8 @@ int train_backward(itmo_trainer* t, const void* x, int x_dtype, const float* y, 
       w.ld_n = L.cout;
       w.ws = t->wg_ws;
       w.ws_bytes = wgrad_ws_bytes();
-      PhaseStamp ps(t, kPhWgrad, s, __LINE__);
-      int rc = run_wgrad(w, s);
+      PhaseStamp ps(t, kPhWgrad, sw, __LINE__);
+      int rc = run_wgrad(w, sw);
       if (rc) return rc;
     } else if (L.kind == kConv) {
       for (int src = 0; src < (L.cin1 > 0 ? 2 : 1); ++src) {
@@ -426,8 +447,8 @@ int train_backward(itmo_trainer* t, const void* x, int x_dtype, const float* y, 
         w.m_off = src == 0 ? 0 : L.cin0;
         w.ws = t->wg_ws;
         w.ws_bytes = wgrad_ws_bytes();
-        PhaseStamp ps(t, kPhWgrad, s, __LINE__);
-        int rc = run_wgrad(w, s);
+        PhaseStamp ps(t, kPhWgrad, sw, __LINE__);
+        int rc = run_wgrad(w, sw);
         if (rc) return rc;
       }
     } else {  // kConvT: dW[a][b][co][ci] = sum G[n, 2i+a, 2j+b, co] X[n, i, j, ci]
@@ -449,10 +470,14 @@ int train_backward(itmo_trainer* t, const void* x, int x_dtype, const float* y, 
         w.ld_n = L.cin0;
         w.ws = t->wg_ws;
         w.ws_bytes = wgrad_ws_bytes();
-        PhaseStamp ps(t, kPhWgrad, s, __LINE__);
-        int rc = run_wgrad(w, s);
+        PhaseStamp ps(t, kPhWgrad, sw, __LINE__);
+        int rc = run_wgrad(w, sw);
         if (rc) return rc;
       }
+    }
+    if (side_wgrad) {
+      ITMO_CUDA(cudaEventRecord(t->ev_wg[gb], sw));
+      t->wg_pending[gb] = true;
     }
     if (li == 0) break;
     // ---- data gradient
@@ -525,6 +550,13 @@ int train_backward(itmo_trainer* t, const void* x, int x_dtype, const float* y, 
       if (rc) return rc;
     }
   }
+  // join: everything the caller launches next on `s` (the next micro-batch's forward overwrites the activations the
+  // weight-gradient GEMMs read; update / exchange / zero_grad touch the gradient buffer) follows the side stream's work
+  for (int gb = 0; gb < 2; ++gb)
+    if (t->wg_pending[gb]) {
+      ITMO_CUDA(cudaStreamWaitEvent(s, t->ev_wg[gb], 0));
+      t->wg_pending[gb] = false;
+    }
   return ITMO_OK;
 }
 
@@ -558,6 +590,11 @@ void itmo_trainer_destroy(itmo_trainer* t) {
   cudaSetDevice(t->device);
   cudaDeviceSynchronize();
   for (void* p : t->allocs) cudaFree(p);
+  if (t->s2) cudaStreamDestroy(t->s2);
+  for (int i = 0; i < 2; ++i) {
+    if (t->ev_gp[i]) cudaEventDestroy(t->ev_gp[i]);
+    if (t->ev_wg[i]) cudaEventDestroy(t->ev_wg[i]);
+  }
   for (auto& st : t->stamps) {
     cudaEventDestroy(st.beg);
     cudaEventDestroy(st.end);
@@ -611,7 +648,17 @@ int itmo_trainer_create(itmo_trainer** out, int device, int micro_batch, int h, 
   if (rc == ITMO_OK) rc = tr_alloc(t, &t->x32, size_t(micro_batch) * h * w * 32);
   if (rc == ITMO_OK) rc = tr_alloc(t, &t->g[0], gmax);
   if (rc == ITMO_OK) rc = tr_alloc(t, &t->g[1], gmax);
-  if (rc == ITMO_OK) rc = tr_alloc(t, &t->gp, gmax);
+  if (rc == ITMO_OK) rc = tr_alloc(t, &t->gpb[0], gmax);
+  if (rc == ITMO_OK) rc = tr_alloc(t, &t->gpb[1], gmax);
+  t->gp = t->gpb[0];
+  if (rc == ITMO_OK) {
+    cudaError_t es = cudaStreamCreateWithFlags(&t->s2, cudaStreamNonBlocking);
+    for (int i = 0; i < 2 && es == cudaSuccess; ++i) {
+      es = cudaEventCreateWithFlags(&t->ev_gp[i], cudaEventDisableTiming);
+      if (es == cudaSuccess) es = cudaEventCreateWithFlags(&t->ev_wg[i], cudaEventDisableTiming);
+    }
+    if (es != cudaSuccess) rc = fail(ITMO_ERR_CUDA, "side stream setup failed: %s", cudaGetErrorString(es));
+  }
   if (rc == ITMO_OK) rc = tr_alloc(t, &t->gq, qmax);
   if (rc == ITMO_OK) rc = tr_alloc(t, &t->bn_vec, size_t(ITMO_NUM_LAYERS) * 4 * 512);
   if (rc == ITMO_OK) rc = tr_alloc(t, &t->stats, size_t(ITMO_NUM_LAYERS) * 1024);
