@@ -62,7 +62,11 @@ def launches(src: str, dst: str) -> None:
 
 
 def full(src: str, dst: str, names: list[str]) -> None:
-    raw = subprocess.run(['ncu', '-i', src, '--page', 'raw', '--csv'], capture_output=True, text=True, check=True).stdout
+    # src: the .ncu-rep, or the raw page already exported on the GPU box (`ncu -i rep --page raw --csv > x.csv`)
+    if src.endswith('.csv'):
+        raw = open(src).read()
+    else:
+        raw = subprocess.run(['ncu', '-i', src, '--page', 'raw', '--csv'], capture_output=True, text=True, check=True).stdout
     rows = list(csv.reader(io.StringIO(raw)))
     hdr, units, body = rows[0], rows[1], rows[2:]
     col = {h: i for i, h in enumerate(hdr)}
