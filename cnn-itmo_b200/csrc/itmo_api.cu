@@ -22,6 +22,7 @@
 #include "conv_igemm.cuh"
 #include "frame_ops.cuh"
 #include "rgb_conv_tc.cuh"
+#include "stem_fused.cuh"
 
 namespace {
 
@@ -460,6 +461,8 @@ struct ConvArgs {
   const float* h_scale;
   const float* h_shift;
   unsigned long long* sat_count;   // fp16: device counter of clamped store groups (ConvParams::sat_count) or null
+  itmo::ConvParams* capture;       // non-null: fill *capture with the launch parameters (and *capture_epi with the
+  int* capture_epi;                // epilogue variant) instead of launching — the fused stem kernel embeds conv2d_2's
 };
 
 // Debug / tuning overrides (environment, read once): ITMO_FORCE_NM = 1|2|4, ITMO_NO_RESIDENT = 1
@@ -730,6 +733,11 @@ int run_conv(const ConvArgs& a, cudaStream_t stream) {
   p.head_dtype = a.head_dtype;
   const int total_tiles = a.n * (a.h / itmo::kBlkH) * (a.w / (itmo::kBlkW * nm)) * n_tiles;
   if (a.stats_blocks) *a.stats_blocks = std::min(total_tiles, num_sms());   // = launch_conv_t's grid
+  if (a.capture) {
+    *a.capture = p;
+    if (a.capture_epi) *a.capture_epi = epi;
+    return ITMO_OK;
+  }
   if (epi != itmo::kEpiGeneric) {
     const int rcf = a.precision == ITMO_PREC_BF16
                         ? launch_conv_fast<__nv_bfloat16>(block_n, swz, epi, p, total_tiles, smem_bytes, stream)
@@ -842,6 +850,51 @@ int run_rgb_conv(int precision, const void* in, int in_dtype, int n, int h, int 
   return run_rgb_conv_t<float>(in, in_dtype, n, h, w, w_hwio, bias, scale, shift, out, out_lo, sm, grid, stream);
 }
 
+// conv2d_1 + conv2d_2 as one kernel (stem_fused.cuh). `c2` = conv2d_2's arguments as forward_chunk builds them (its
+// source pointer is not read). Returns 1 when the shape / mode is not the one the kernel is written for (the caller then
+// launches the two layers separately), 0 after a launch, < 0 on errors.
+int run_stem(const ConvArgs& c2, const void* in_u8, const float* w1_hwio, const itmo::RgbAffine& a1, cudaStream_t stream) {
+  if (!prec_is16(c2.precision) || (reinterpret_cast<uintptr_t>(in_u8) & 3) || c2.h % itmo::kBlkH || c2.w % 32 ||
+      c2.c0 != 32 || c2.c1 != 0 || c2.cout != 32 || !c2.pooled || !c2.out)
+    return 1;
+  static thread_local itmo::StemParams sp;   // ~3 KB of tensor maps and vectors: not on the stack of every call
+  int epi = 0;
+  ConvArgs a = c2;
+  a.capture = &sp.c2;
+  a.capture_epi = &epi;
+  int rc = run_conv(a, stream);
+  if (rc) return rc;
+  const itmo::ConvParams& p = sp.c2;
+  if (epi != (itmo::kEpiConvPool | itmo::kEpiConstAffine) || p.nm != 4 || !p.b_resident || !p.tma_store || p.epi_bufs != 1 ||
+      p.n_tiles != 1 || p.taps != 9 || p.dbg != 0)
+    return 1;
+  sp.in = (const uint8_t*)in_u8;
+  sp.w1_hwio = w1_hwio;
+  sp.a1 = a1;
+  sp.in_scale = 1.0f / 255.0f;
+  const int total_tiles = c2.n * (c2.h / itmo::kBlkH) * (c2.w / 32);
+  const int grid = std::min(total_tiles, num_sms());
+  if (c2.precision == ITMO_PREC_BF16) {
+    auto kern = itmo::stem_fused_kernel<__nv_bfloat16>;
+    static bool configured = false;
+    if (!configured) {
+      ITMO_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, itmo::kStemSmemBytes));
+      configured = true;
+    }
+    kern<<<grid, itmo::kStemThreads, itmo::kStemSmemBytes, stream>>>(sp);
+  } else {
+    auto kern = itmo::stem_fused_kernel<__half>;
+    static bool configured = false;
+    if (!configured) {
+      ITMO_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, itmo::kStemSmemBytes));
+      configured = true;
+    }
+    kern<<<grid, itmo::kStemThreads, itmo::kStemSmemBytes, stream>>>(sp);
+  }
+  ITMO_CUDA(cudaGetLastError());
+  return ITMO_OK;
+}
+
 // Keras head kernel [64][3] -> [3][64] (tiny, host side)
 void transpose_head(const float* k64x3, float* out3x64) {
   for (int c = 0; c < 64; ++c)
@@ -866,6 +919,7 @@ struct itmo_ctx {
   // host copy of layer 0's bias / folded BN scale / shift: passed to rgb_conv_tc_kernel by value (constant bank)
   itmo::RgbAffine l0_affine = {};
   bool l0_affine_valid = false;
+  bool act0_valid = true;   // false after a forward through the fused stem kernel (conv2d_1's output is not materialised)
   // host copies of every layer's bias / folded scale / shift (ConvArgs::h_*)
   float h_bias[ITMO_NUM_LAYERS][itmo::kMaxCout] = {};
   float h_scale[ITMO_NUM_LAYERS][itmo::kMaxCout] = {};
@@ -914,6 +968,7 @@ struct itmo_ctx {
   // (images, in dtype, out dtype, staging slot): itmo_predict_host replays them instead of re-launching
   bool use_graph = false;
   std::map<std::tuple<int, int, int, int>, cudaGraphExec_t> graphs;
+  std::map<std::tuple<int, int, int, int>, int> graph_kernels;   // kernel nodes of each graph (17 with the fused stem, else 18)
   // per-layer device timing (itmo_set_profiling): event pairs recorded around every layer launch
   bool profiling = false;
   struct Stamp { int layer; cudaEvent_t beg, end; };
@@ -950,15 +1005,86 @@ struct LayerStamp {
     cudaEventRecord(beg, stream);
     ctx->stamps.push_back({layer, beg, end});
   }
+  // the launch this stamp was opened for did not happen: drop the pair
+  void cancel() {
+    if (!end) return;
+    auto st = ctx->stamps.back();
+    ctx->stamps.pop_back();
+    ctx->event_pool.push_back(st.beg);
+    ctx->event_pool.push_back(st.end);
+    end = nullptr;
+  }
   ~LayerStamp() {
     if (end) cudaEventRecord(end, stream);
   }
 };
 
+// conv_igemm arguments of tensor-core layer li of a context's forward pass
+ConvArgs forward_layer_args(itmo_ctx* ctx, int li, int nb, void* out_dev, int out_dtype) {
+  const LayerDef& L = kLayers[li];
+  ConvArgs a;
+  memset(&a, 0, sizeof(a));
+  a.precision = ctx->precision;
+  a.mode = L.kind == kConvT ? itmo::kModeConvT2x2 : itmo::kModeConv3x3;
+  a.src0 = L.src0_pooled ? ctx->pooled[L.src0] : ctx->act[L.src0];
+  a.c0 = L.cin0;
+  a.src1 = L.src1 >= 0 ? ctx->act[L.src1] : nullptr;
+  a.c1 = L.cin1;
+  a.src0_lo = L.src0_pooled ? ctx->pooled_lo[L.src0] : ctx->act_lo[L.src0];
+  a.src1_lo = L.src1 >= 0 ? ctx->act_lo[L.src1] : nullptr;
+  a.n = nb;
+  a.h = L.hin;
+  a.w = L.hin;
+  a.wpacked = ctx->wpacked[li];
+  a.bias = ctx->bias[li];
+  a.scale = ctx->scale[li];
+  a.shift = ctx->shift[li];
+  a.cout = L.cout;
+  a.out = ctx->act[li];
+  a.out_lo = ctx->act_lo[li];
+  a.pooled = L.pool ? ctx->pooled[li] : nullptr;
+  a.pooled_lo = L.pool ? ctx->pooled_lo[li] : nullptr;
+  a.head_dtype = itmo::kHeadNone;
+  a.sat_count = ctx->sat_dev;
+  if (ctx->h_affine_valid) {
+    a.h_bias = ctx->h_bias[li];
+    a.h_scale = ctx->h_scale[li];
+    a.h_shift = ctx->h_shift[li];
+  }
+  if (li == 17) {
+    a.out = nullptr;  // conv2d_14's activation only feeds the head: never written to HBM
+    a.out_lo = nullptr;
+    a.head_w = (const float*)ctx->wpacked[18];
+    a.head_b = ctx->bias[18];
+    a.head_out = out_dev;
+    a.head_dtype = out_dtype == ITMO_DT_U8 ? itmo::kHeadU8 : itmo::kHeadF32;
+  }
+  return a;
+}
+
 int forward_chunk(itmo_ctx* ctx, const void* in_dev, int in_dtype, void* out_dev, int out_dtype, int nb,
                   cudaStream_t stream) {
   const int prec = ctx->precision;
-  for (int li = 0; li < ITMO_NUM_LAYERS; ++li) {
+  // 16-bit modes, raw uint8 input, a loaded context: conv2d_1 + conv2d_2 as ONE kernel (stem_fused.cuh; the first
+  // layer's activation is then not materialised — ITMO_STEM_FUSED=0 launches the two layers separately)
+  static const int allow_stem = env_int("ITMO_STEM_FUSED", 1);
+  int first = 0;
+  ctx->act0_valid = true;
+  if (allow_stem && prec_is16(prec) && in_dtype == ITMO_DT_U8 && ctx->l0_affine_valid && ctx->h_affine_valid &&
+      kLayers[0].kind == kRgbConv && kLayers[1].kind == kConv && kLayers[1].src0 == 0) {
+    LayerStamp stamp(ctx, 1, stream);   // booked under conv2d_2
+    const int rc = run_stem(forward_layer_args(ctx, 1, nb, out_dev, out_dtype), in_dev, (const float*)ctx->wpacked[0],
+                            ctx->l0_affine, stream);
+    if (rc < 0) return rc;
+    if (rc == 0) {
+      ctx->launches++;
+      ctx->act0_valid = false;
+      first = 2;
+    } else {
+      stamp.cancel();
+    }
+  }
+  for (int li = first; li < ITMO_NUM_LAYERS; ++li) {
     const LayerDef& L = kLayers[li];
     if (L.kind == kHead) continue;  // fused into layer 17's epilogue
     LayerStamp stamp(ctx, li, stream);
@@ -970,44 +1096,7 @@ int forward_chunk(itmo_ctx* ctx, const void* in_dev, int in_dtype, void* out_dev
       ctx->launches++;
       continue;
     }
-    ConvArgs a;
-    memset(&a, 0, sizeof(a));
-    a.precision = prec;
-    a.mode = L.kind == kConvT ? itmo::kModeConvT2x2 : itmo::kModeConv3x3;
-    a.src0 = L.src0_pooled ? ctx->pooled[L.src0] : ctx->act[L.src0];
-    a.c0 = L.cin0;
-    a.src1 = L.src1 >= 0 ? ctx->act[L.src1] : nullptr;
-    a.c1 = L.cin1;
-    a.src0_lo = L.src0_pooled ? ctx->pooled_lo[L.src0] : ctx->act_lo[L.src0];
-    a.src1_lo = L.src1 >= 0 ? ctx->act_lo[L.src1] : nullptr;
-    a.n = nb;
-    a.h = L.hin;
-    a.w = L.hin;
-    a.wpacked = ctx->wpacked[li];
-    a.bias = ctx->bias[li];
-    a.scale = ctx->scale[li];
-    a.shift = ctx->shift[li];
-    a.cout = L.cout;
-    a.out = ctx->act[li];
-    a.out_lo = ctx->act_lo[li];
-    a.pooled = L.pool ? ctx->pooled[li] : nullptr;
-    a.pooled_lo = L.pool ? ctx->pooled_lo[li] : nullptr;
-    a.head_dtype = itmo::kHeadNone;
-    a.sat_count = ctx->sat_dev;
-    if (ctx->h_affine_valid) {
-      a.h_bias = ctx->h_bias[li];
-      a.h_scale = ctx->h_scale[li];
-      a.h_shift = ctx->h_shift[li];
-    }
-    if (li == 17) {
-      a.out = nullptr;  // conv2d_14's activation only feeds the head: never written to HBM
-      a.out_lo = nullptr;
-      a.head_w = (const float*)ctx->wpacked[18];
-      a.head_b = ctx->bias[18];
-      a.head_out = out_dev;
-      a.head_dtype = out_dtype == ITMO_DT_U8 ? itmo::kHeadU8 : itmo::kHeadF32;
-    }
-    int rc = run_conv(a, stream);
+    int rc = run_conv(forward_layer_args(ctx, li, nb, out_dev, out_dtype), stream);
     if (rc) return rc;
     ctx->launches++;
   }
@@ -1018,6 +1107,7 @@ int forward_chunk(itmo_ctx* ctx, const void* in_dev, int in_dtype, void* out_dev
 void drop_graphs(itmo_ctx* ctx) {
   for (auto& kv : ctx->graphs) cudaGraphExecDestroy(kv.second);
   ctx->graphs.clear();
+  ctx->graph_kernels.clear();
 }
 
 // One arena chunk of itmo_predict_host through a captured CUDA graph: the 18 launches (tensor maps and the by-value
@@ -1037,6 +1127,7 @@ int forward_chunk_graph(itmo_ctx* ctx, int slot, int in_dtype, int out_dtype, in
     rc = forward_chunk(ctx, ctx->dev_in[slot], in_dtype, ctx->dev_out[slot], out_dtype, nb, ctx->own_stream);
     cudaGraph_t graph = nullptr;
     cudaError_t e = cudaStreamEndCapture(ctx->own_stream, &graph);
+    ctx->graph_kernels[key] = int(ctx->launches - launches0);
     ctx->launches = launches0;   // recorded, not launched
     if (rc) {
       if (graph) cudaGraphDestroy(graph);
@@ -1050,7 +1141,7 @@ int forward_chunk_graph(itmo_ctx* ctx, int slot, int in_dtype, int out_dtype, in
     it = ctx->graphs.emplace(key, exec).first;
   }
   ITMO_CUDA(cudaGraphLaunch(it->second, ctx->own_stream));
-  ctx->launches += ITMO_NUM_LAYERS - 1;   // kernels the replay launches
+  ctx->launches += ctx->graph_kernels[key];   // kernels the replay launches
   ctx->last_chunk = nb;
   return ITMO_OK;
 }
@@ -1566,6 +1657,8 @@ int itmo_read_activation(itmo_ctx* ctx, int layer, int which, float* dst_host, s
   const void* src = which ? ctx->pooled[layer] : ctx->act[layer];
   const size_t per_img = which ? ctx->pooled_elems_per_img[layer] : ctx->act_elems_per_img[layer];
   if (!src || ctx->last_chunk == 0) return fail(ITMO_ERR_STATE, "activation %d/%d is not materialised", layer, which);
+  if (layer == 0 && !ctx->act0_valid)
+    return fail(ITMO_ERR_STATE, "conv2d_1's activation is not materialised by the fused stem kernel (set ITMO_STEM_FUSED=0)");
   const size_t n = per_img * ctx->last_chunk;
   *n_elems = n;
   if (n > cap_elems) return fail(ITMO_ERR_INVALID, "destination too small: need %zu elements", n);

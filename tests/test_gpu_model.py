@@ -275,3 +275,33 @@ def test_pipelined_predict_loop_equals_reference_loop(pkg, calibrated_weights, g
         np.testing.assert_array_equal(P.load_png(pa), P.load_png(pb))
     assert stats['files'] == 12 and stats['gpu_seconds'] > 0
     m.close()
+
+
+def test_fused_stem_kernel_is_bit_identical_to_the_two_layers(pkg, calibrated_weights, images, tmp_path):
+    """conv2d_1 + conv2d_2 as one kernel (csrc/stem_fused.cuh, the default for uint8 input in the 16-bit modes) against the
+    two layers launched separately (ITMO_STEM_FUSED=0, read once per process -> a second interpreter): same operand split,
+    same affine sequence, same packing, so every output byte and every later activation is identical."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = (
+        "import sys, numpy as np; sys.path.insert(0, %r)\n"
+        "import cnn_itmo_b200 as M\n"
+        "from oracle import unet_ref as R\n"
+        "ws = R.calibrated_weights(218); imgs = R.synthetic_images_u8(3, seed=5)\n"
+        "out = {}\n"
+        "for prec in ('fp16', 'bf16'):\n"
+        "    m = M.Model(ws, precision=prec, max_batch=2)\n"
+        "    out[prec] = m.predict_u8(imgs); out[prec + '_act1'] = m.read_activation(1); out[prec + '_pool1'] = m.read_activation(1, pooled=True); m.close()\n"
+        "np.savez(sys.argv[1], **out)\n" % root)
+    outs = {}
+    for flag in ('1', '0'):
+        path = str(tmp_path / f'stem{flag}.npz')
+        env = dict(os.environ, ITMO_STEM_FUSED=flag)
+        r = subprocess.run([sys.executable, '-c', code, path], env=env, capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0, r.stderr[-2000:]
+        outs[flag] = np.load(path)
+    for key in outs['1'].files:
+        assert np.array_equal(outs['1'][key], outs['0'][key]), key
+    assert outs['1']['fp16'].std() > 5       # not a constant image
