@@ -61,7 +61,9 @@ enum StoreMode : int { kStorePlain = 0, kStoreTf32Rna = 1, kStoreSplit = 2 };
 // weight tile (the tensor core reads the other half from the peer's shared memory), so weight traffic L2 -> SMEM and
 // the weight-operand shared-memory reads per MMA halve: N = 64 MMAs go from 6 KB to 5 KB of operand reads each
 // (conv2d_14 is bound by exactly that), the N = 256 layers stream 4 KB instead of 8 KB of weights per MMA.
-enum EpiKind : int { kEpiGeneric = 0, kEpiConv = 1, kEpiConvPool = 2, kEpiConvT = 3, kEpiHead = 4, kEpiConstAffine = 16, kEpiPair = 32 };
+// | kEpiHeadConst (with kEpiHead): the head's folded weights as 64-bit constant-bank operands too (ConvParams::c_head) — no
+// shared-memory reads left in conv2d_14's epilogue, whose MMAs already use ~90 % of the shared-memory pipe.
+enum EpiKind : int { kEpiGeneric = 0, kEpiConv = 1, kEpiConvPool = 2, kEpiConvT = 3, kEpiHead = 4, kEpiConstAffine = 16, kEpiPair = 32, kEpiHeadConst = 64 };
 
 struct ConvParams {
   CUtensorMap tmA[4];  // activation sources: dims (C, W, H, N), box (BK, 8*NM+2*pad, 16+2*pad, 1)
@@ -119,6 +121,7 @@ struct ConvParams {
   alignas(16) float c_bias[128];    // transposed conv with 64 output channels: the vectors twice (indexed by column & 127)
   alignas(16) float c_scale[128];
   alignas(16) float c_shift[128];
+  alignas(16) float c_head[196];    // kEpiHeadConst: head weights [3][64] with conv2d_14's BN scale folded in, then the 3 folded biases
   // fp16 storage only: incremented once per (thread, 32-channel chunk) in which a value was clamped to +-65504 by the
   // saturating pack, so a checkpoint whose activations leave fp16's range cannot clip silently (itmo_saturation_count)
   unsigned long long* sat_count;
@@ -527,6 +530,13 @@ __device__ __forceinline__ void epilogue_fast(const ConvParams& p, uint32_t tmem
             // even / odd channels accumulate in the two halves of a packed pair: 3 FFMA2 per channel pair
 #pragma unroll
             for (int i = 0; i < 32; i += 4) {
+              if constexpr ((EPI & kEpiHeadConst) != 0) {
+                const uint64_t fa = f2_pack(f[i], f[i + 1]), fb = f2_pack(f[i + 2], f[i + 3]);
+                hh0 = f2_fma(fb, cpair(p.c_head, 0 * 64 + col + i + 2), f2_fma(fa, cpair(p.c_head, 0 * 64 + col + i), hh0));
+                hh1 = f2_fma(fb, cpair(p.c_head, 1 * 64 + col + i + 2), f2_fma(fa, cpair(p.c_head, 1 * 64 + col + i), hh1));
+                hh2 = f2_fma(fb, cpair(p.c_head, 2 * 64 + col + i + 2), f2_fma(fa, cpair(p.c_head, 2 * 64 + col + i), hh2));
+                continue;
+              }
               const ulonglong2 w0 = *reinterpret_cast<const ulonglong2*>(s_head + 0 * 64 + col + i);
               const ulonglong2 w1 = *reinterpret_cast<const ulonglong2*>(s_head + 1 * 64 + col + i);
               const ulonglong2 w2 = *reinterpret_cast<const ulonglong2*>(s_head + 2 * 64 + col + i);
@@ -607,7 +617,9 @@ __device__ __forceinline__ void epilogue_fast(const ConvParams& p, uint32_t tmem
         f2_unpack(hh0, e0, o0);
         f2_unpack(hh1, e1, o1);
         f2_unpack(hh2, e2, o2);
-        const float z0 = (e0 + o0) + s_head[192], z1 = (e1 + o1) + s_head[193], z2 = (e2 + o2) + s_head[194];
+        constexpr bool kHC = (EPI & kEpiHeadConst) != 0;
+        const float z0 = (e0 + o0) + (kHC ? p.c_head[192] : s_head[192]), z1 = (e1 + o1) + (kHC ? p.c_head[193] : s_head[193]),
+                    z2 = (e2 + o2) + (kHC ? p.c_head[194] : s_head[194]);
         const float q0 = 1.f / (1.f + expf(-z0)), q1 = 1.f / (1.f + expf(-z1)), q2 = 1.f / (1.f + expf(-z2));
         const size_t pix = (size_t(img) * p.H + y) * p.W + x;
         if (p.head_dtype == kHeadF32) {

@@ -408,6 +408,7 @@ int launch_conv_fast(int block_n, int swz, int epi, const itmo::ConvParams& p, i
   ITMO_FAST(256, 128, kEpiConv | P);
   ITMO_FAST(256, 128, kEpiConvPool | P);
   ITMO_FAST(64, 64, kEpiHead | C | P);
+  ITMO_FAST(64, 64, kEpiHead | C | P | kEpiHeadConst);
   ITMO_FAST(256, 128, kEpiConvT | P);
 #undef ITMO_FAST
   return -1;
@@ -461,6 +462,8 @@ struct ConvArgs {
   const float* h_scale;
   const float* h_shift;
   unsigned long long* sat_count;   // fp16: device counter of clamped store groups (ConvParams::sat_count) or null
+  const float* h_head_w;           // host copies of the head's [3][64] weights and [3] biases (kEpiHeadConst) or null
+  const float* h_head_b;
   itmo::ConvParams* capture;       // non-null: fill *capture with the launch parameters (and *capture_epi with the
   int* capture_epi;                // epilogue variant) instead of launching — the fused stem kernel embeds conv2d_2's
 };
@@ -733,6 +736,19 @@ int run_conv(const ConvArgs& a, cudaStream_t stream) {
   p.head_dtype = a.head_dtype;
   const int total_tiles = a.n * (a.h / itmo::kBlkH) * (a.w / (itmo::kBlkW * nm)) * n_tiles;
   if (a.stats_blocks) *a.stats_blocks = std::min(total_tiles, num_sms());   // = launch_conv_t's grid
+  static const int head_const = env_int("ITMO_HEAD_CONST", 0);   // A/B on one box: no difference (conv2d_14 is bound by the MMAs' operand reads, not by its epilogue's 9 % of LSU wavefronts)
+  if (head_const && epi == (itmo::kEpiHead | itmo::kEpiConstAffine | itmo::kEpiPair) && a.h_head_w && a.h_head_b) {
+    // fold conv2d_14's BN affine into the head (the arithmetic of the kernel's own setup, on the host)
+    for (int k = 0; k < 3; ++k) {
+      float acc = a.h_head_b[k];
+      for (int ch = 0; ch < 64; ++ch) {
+        p.c_head[k * 64 + ch] = a.h_head_w[k * 64 + ch] * a.h_scale[ch];
+        acc = fmaf(a.h_head_w[k * 64 + ch], a.h_shift[ch], acc);
+      }
+      p.c_head[192 + k] = acc;
+    }
+    epi |= itmo::kEpiHeadConst;
+  }
   if (a.capture) {
     *a.capture = p;
     if (a.capture_epi) *a.capture_epi = epi;
@@ -919,6 +935,8 @@ struct itmo_ctx {
   // host copy of layer 0's bias / folded BN scale / shift: passed to rgb_conv_tc_kernel by value (constant bank)
   itmo::RgbAffine l0_affine = {};
   bool l0_affine_valid = false;
+  float h_head_w[192] = {}, h_head_b[3] = {};   // host copy of the head's [3][64] weights / biases (ConvArgs::h_head_w)
+  bool h_head_valid = false;
   bool act0_valid = true;   // false after a forward through the fused stem kernel (conv2d_1's output is not materialised)
   // host copies of every layer's bias / folded scale / shift (ConvArgs::h_*)
   float h_bias[ITMO_NUM_LAYERS][itmo::kMaxCout] = {};
@@ -1055,6 +1073,10 @@ ConvArgs forward_layer_args(itmo_ctx* ctx, int li, int nb, void* out_dev, int ou
     a.out = nullptr;  // conv2d_14's activation only feeds the head: never written to HBM
     a.out_lo = nullptr;
     a.head_w = (const float*)ctx->wpacked[18];
+    if (ctx->h_head_valid) {
+      a.h_head_w = ctx->h_head_w;
+      a.h_head_b = ctx->h_head_b;
+    }
     a.head_b = ctx->bias[18];
     a.head_out = out_dev;
     a.head_dtype = out_dtype == ITMO_DT_U8 ? itmo::kHeadU8 : itmo::kHeadF32;
@@ -1377,8 +1399,11 @@ int itmo_load_weights(itmo_ctx* ctx, const itmo_layer_weights* layers, int n_lay
         if (e == cudaSuccess) e = cudaMemcpy(ctx->h_shift[li], ctx->shift[li], L.cout * 4, cudaMemcpyDeviceToHost);
       }
     }
+    ctx->h_head_valid = false;
+    if (e == cudaSuccess) e = cudaMemcpy(ctx->h_head_w, ctx->wpacked[18], 192 * 4, cudaMemcpyDeviceToHost);   // [3][64]
+    if (e == cudaSuccess) e = cudaMemcpy(ctx->h_head_b, ctx->bias[18], 3 * 4, cudaMemcpyDeviceToHost);
     if (e != cudaSuccess) rc = fail(ITMO_ERR_CUDA, "affine read-back failed: %s", cudaGetErrorString(e));
-    else ctx->h_affine_valid = true;
+    else ctx->h_affine_valid = ctx->h_head_valid = true;
   }
   if (rc == ITMO_OK) ctx->weights_loaded = true;
   return rc;
