@@ -351,6 +351,9 @@ def layer_table(graph, layer_times, steps, B, precision, peaks):
     """Every layer against ITS bound from the CUDA events of the timed region."""
     per_layer = []
     igemm_flops = igemm_ms = 0.0
+    # conv2d_1 + conv2d_2 run as ONE kernel (csrc/stem_fused.cuh) for uint8 input in the 16-bit modes: no launch is
+    # booked under conv2d_1 then, and conv2d_2's row carries both layers' FLOPs and the pair's HBM bytes
+    stem_fused = layer_times[0][1] == 0 and layer_times[1][1] > 0
     for l in graph.LAYERS:
         ms, calls = layer_times[l.index]
         ks = graph.kernel_shape(l)
@@ -362,13 +365,18 @@ def layer_table(graph, layer_times, steps, B, precision, peaks):
             fl += 2.0 * IMG * IMG * 64 * 3  # fused 1x1 head
         if l.kind == 'head':
             continue
+        if stem_fused and l.index == 0:
+            per_layer.append({'layer': l.name, 'ms_per_step': 0.0, 'fused_into': 'conv2d_2 (stem_fused_kernel)'})
+            continue
+        if stem_fused and l.index == 1:
+            fl += 2.0 * IMG * IMG * 27 * 32
         ms_per_step = ms / steps
         tf = fl * B / (ms_per_step * 1e-3) / 1e12 if ms_per_step > 0 else 0.0
         # algorithmic HBM bytes per image: every source read once, the output written once (+ the
         # pooled copy), the weights once per launch; uint8 pixels in front of conv2d_1, uint8 RGB behind conv2d_14
         es = 2 if precision in ('bf16', 'fp16') else 4
         hout = 2 * l.hin if l.kind == 'convT' else l.hin
-        by = l.hin ** 2 * (3 if l.index == 0 else sum(l.cin) * es)
+        by = l.hin ** 2 * (3 if (l.index == 0 or (stem_fused and l.index == 1)) else sum(l.cin) * es)
         by += IMG * IMG * 3 if l.index == 17 else hout ** 2 * l.cout * es * (1.25 if l.pool else 1.0)
         gbs = by * B / (ms_per_step * 1e-3) / 1e9 if ms_per_step > 0 else 0.0
         t_tensor = fl / (peaks['tflops_sustained'] * 1e12)
@@ -377,7 +385,7 @@ def layer_table(graph, layer_times, steps, B, precision, peaks):
                           'gbs': round(gbs, 1), 'bound': 'tensor' if t_tensor >= t_hbm else 'hbm',
                           'frac_of_bound': round(max(t_tensor, t_hbm) * B / (ms_per_step * 1e-3), 4) if ms_per_step > 0 else None,
                           'launches_per_step': calls / steps})
-        if l.index != 0:
+        if l.index != 0:    # conv2d_1 alone is rgb_conv_tc_kernel, not the implicit-GEMM kernel family
             igemm_flops += fl * B
             igemm_ms += ms_per_step
     return per_layer, igemm_flops, igemm_ms
@@ -477,6 +485,9 @@ def run_batch_leg(a, hz, precision=None, batch=None, steps=None, with_e2e=True, 
     if hz.rank == 0:
         log(f'per-layer [{prec}, batch {B}] (rank 0, CUDA events inside the timed region):')
         for p in per_layer:
+            if 'fused_into' in p:
+                log(f"  {p['layer']:<22} fused into {p['fused_into']}")
+                continue
             log(f"  {p['layer']:<22} {p['ms_per_step']:9.3f} ms/step  {p['tflops']:8.1f} TFLOP/s  {p['gbs']:8.1f} GB/s  "
                 f"{p['bound']:<6} {p['frac_of_bound']}")
         log(f'  sum of layers {sum(p["ms_per_step"] for p in per_layer):.3f} ms, step {ms_step:.3f} ms')
