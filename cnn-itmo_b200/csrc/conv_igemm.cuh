@@ -63,7 +63,10 @@ enum StoreMode : int { kStorePlain = 0, kStoreTf32Rna = 1, kStoreSplit = 2 };
 // (conv2d_14 is bound by exactly that), the N = 256 layers stream 4 KB instead of 8 KB of weights per MMA.
 // | kEpiHeadConst (with kEpiHead): the head's folded weights as 64-bit constant-bank operands too (ConvParams::c_head) — no
 // shared-memory reads left in conv2d_14's epilogue, whose MMAs already use ~90 % of the shared-memory pipe.
-enum EpiKind : int { kEpiGeneric = 0, kEpiConv = 1, kEpiConvPool = 2, kEpiConvT = 3, kEpiHead = 4, kEpiConstAffine = 16, kEpiPair = 32, kEpiHeadConst = 64 };
+// Training step (bf16): kEpiStats = z = max(acc + b, 0) stored as is + the BatchNormalization batch statistics of the stored
+// values (ConvParams::stats), 3x3 and transposed convolutions alike; kEpiIdentity = the accumulator stored as is (the
+// data-gradient convolutions).
+enum EpiKind : int { kEpiGeneric = 0, kEpiConv = 1, kEpiConvPool = 2, kEpiConvT = 3, kEpiHead = 4, kEpiStats = 5, kEpiIdentity = 6, kEpiConstAffine = 16, kEpiPair = 32, kEpiHeadConst = 64 };
 
 struct ConvParams {
   CUtensorMap tmA[4];  // activation sources: dims (C, W, H, N), box (BK, 8*NM+2*pad, 16+2*pad, 1)
@@ -411,12 +414,14 @@ template <typename Elem, int BLOCK_N, int EPI>
 __device__ __forceinline__ void epilogue_fast(const ConvParams& p, uint32_t tmem_base, uint64_t* tmem_full_bar,
                                               uint64_t* tmem_empty_bar, uint8_t* epi_stage, const float* s_bias,
                                               const float* s_scale, const float* s_shift, const float* s_head,
-                                              int warp_idx, int lane) {
+                                              int warp_idx, int lane, float* s_stat = nullptr) {
   constexpr int kKind = EPI & 15;
   constexpr bool kConst = (EPI & kEpiConstAffine) != 0;
   constexpr bool kPool = kKind == kEpiConvPool;
   constexpr bool kHead = kKind == kEpiHead;
   constexpr bool kConvT = kKind == kEpiConvT;
+  constexpr bool kStats = kKind == kEpiStats;        // runtime p.mode decides 3x3 / transposed addressing
+  constexpr bool kIdent = kKind == kEpiIdentity;
   constexpr bool kF16 = ElemTraits<Elem>::kFmt == sm100::kFmtF16;
   const int nm = p.nm;                              // M blocks per tile: natural_nm(BLOCK_N) or half of it
   constexpr int kRowB = BLOCK_N >= 64 ? 128 : 64;   // bytes of one staged pixel row
@@ -428,6 +433,7 @@ __device__ __forceinline__ void epilogue_fast(const ConvParams& p, uint32_t tmem
   static_assert(!kConst || kConvT || BLOCK_N <= 64, "constant-bank affine: cout <= 64");
   static_assert(!kHead || (BLOCK_N == 64 && kConst), "fused head: conv2d_14 only");
   static_assert(sizeof(Elem) == 2, "16-bit element types");
+  static_assert(!kStats || ElemTraits<Elem>::kFmt == sm100::kFmtBF16, "training statistics: bf16 storage");
 
   const int ew = warp_idx - 4;            // 0..7
   const int q = warp_idx & 3;             // TMEM lane quarter this warp may read
@@ -499,7 +505,20 @@ __device__ __forceinline__ void epilogue_fast(const ConvParams& p, uint32_t tmem
         for (int h = 0; h < kHalves; ++h) {
           const int col = g * kGroupCh + h * 32;                      // compile-time after unrolling
           float f[32];
-          if constexpr (kHead) {
+          if constexpr (kIdent) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[h][i]);
+          } else if constexpr (kStats) {
+            const int n_glob = n_tile * BLOCK_N + col;
+            const int co0 = p.mode == kModeConvT2x2 ? (n_glob & (p.cout - 1)) : n_glob;
+            const float4* bb = reinterpret_cast<const float4*>(s_bias + co0);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const float4 b4 = bb[i];
+              relu_bias2(v[h][4 * i], v[h][4 * i + 1], b4.x, b4.y, f[4 * i], f[4 * i + 1]);
+              relu_bias2(v[h][4 * i + 2], v[h][4 * i + 3], b4.z, b4.w, f[4 * i + 2], f[4 * i + 3]);
+            }
+          } else if constexpr (kHead) {
             // the BN affine is folded into the head's weights (see the kernel's setup): only max(acc + b, 0) here
 #pragma unroll
             for (int i = 0; i < 32; i += 2) relu_bias2(v[h][i], v[h][i + 1], cpair(p.c_bias, col + i), f[i], f[i + 1]);
@@ -549,6 +568,25 @@ __device__ __forceinline__ void epilogue_fast(const ConvParams& p, uint32_t tmem
             uint32_t pk[16];
 #pragma unroll
             for (int i = 0; i < 16; ++i) pk[i] = pack2<Elem>(f[2 * i], f[2 * i + 1]);
+            if constexpr (kStats) {
+              // statistics of the ROUNDED values (what bn_apply and the backward read back from HBM); each epilogue warp
+              // owns a shared-memory row, plain adds in program order: bit-reproducible
+              float sv[32], sq[32];
+#pragma unroll
+              for (int i = 0; i < 16; ++i) {
+                sv[2 * i] = __uint_as_float(pk[i] << 16);
+                sv[2 * i + 1] = __uint_as_float(pk[i] & 0xFFFF0000u);
+                sq[2 * i] = sv[2 * i] * sv[2 * i];
+                sq[2 * i + 1] = sv[2 * i + 1] * sv[2 * i + 1];
+              }
+              const float tsum = warp_transpose_sum32(sv, lane);
+              const float tsq = warp_transpose_sum32(sq, lane);
+              const int n_glob = n_tile * BLOCK_N + col;
+              const int co0 = p.mode == kModeConvT2x2 ? (n_glob & (p.cout - 1)) : n_glob;
+              float* row = s_stat + ew * 2 * p.cout;
+              row[co0 + lane] += tsum;
+              row[p.cout + co0 + lane] += tsq;
+            }
             if constexpr (kF16) {
               // |max| of the packed pairs, two words per instruction (three-input VHMNMX with |.| operands)
 #pragma unroll
@@ -598,7 +636,7 @@ __device__ __forceinline__ void epilogue_fast(const ConvParams& p, uint32_t tmem
           if (lane == 0) {
             const int ng = n_tile * BLOCK_N + g * kGroupCh;          // first column of the staged group
             const int x0 = tx * kTileW + j * kBlkW, y0 = ty * kBlkH + 4 * q;
-            if constexpr (kConvT) {
+            if (kConvT || (kStats && p.mode == kModeConvT2x2)) {
               const int a_row = ng >> (p.cout_log2 + 1);               // kernel row a of this column group
               sm100::tma_store_4d(&p.tmOut[a_row], st_out, ng - (a_row << (p.cout_log2 + 1)), x0, y0, img);
             } else {
@@ -961,7 +999,7 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_igemm_kernel(const __grid
     // ===== epilogue warps: TMEM -> registers -> bias/ReLU/BN (-> pool / head) -> global =====
     if constexpr (EPI != kEpiGeneric && sizeof(Elem) == 2) {
       epilogue_fast<Elem, BLOCK_N, EPI>(p, tmem_base, tmem_full_bar, tmem_empty_bar, epi_stage, s_bias, s_scale, s_shift,
-                                        s_head, warp_idx, lane);
+                                        s_head, warp_idx, lane, s_stat);
     } else {
     const int ew = warp_idx - 4;            // 0..7
     const int q = warp_idx & 3;             // TMEM lane quarter this warp may read

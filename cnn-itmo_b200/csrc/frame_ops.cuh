@@ -65,10 +65,23 @@ __global__ void __launch_bounds__(256) tile_gather_kernel(const uint8_t* __restr
 }
 
 struct FrameStats {      // per frame, inverse_Reinhard.m:5-14
-  double log_sum;        // sum over pixels of log(max(X, realmin))
+  double log_sum;        // 0, or +inf when a pixel's term was infinite (as-written mode, I == 1); the finite terms are below
   unsigned long long zero_lum;  // PB1 = #(I == 0)
-  unsigned long long pad;
+  unsigned long long log_sum_fx;  // sum over pixels of log(max(X, realmin)) in 40.24 fixed point, two's complement.
+                                  // INTEGER atomics: addition is associative, so the frame statistic — and with it every
+                                  // HDR pixel — is bit-reproducible whatever order the blocks finish in (each warp's /
+                                  // block's own partial is a fixed-order double sum, rounded to 2^-24 once; |term| <= 745,
+                                  // 2^33 pixels fit)
 };
+constexpr double kLogFx = 16777216.0;   // 2^24
+__device__ __forceinline__ void stats_add(FrameStats* st, double lsum, unsigned long long zeros) {
+  atomicAdd(&st->log_sum_fx, static_cast<unsigned long long>(__double2ll_rn(lsum * kLogFx)));
+  atomicAdd(&st->zero_lum, zeros);
+}
+__device__ __forceinline__ double stats_log_sum(const FrameStats* st) {
+  if (isinf(st->log_sum)) return st->log_sum;   // an infinite term was seen (see the kernels): the double sum would be inf
+  return double(static_cast<long long>(st->log_sum_fx)) / kLogFx;
+}
 
 __device__ __forceinline__ double srgb_pow22(uint8_t v) { return pow(double(v) / 255.0, 2.2); }  // inverse_Reinhard.m:2
 __device__ __forceinline__ double rgb2lum(double r, double g, double b) {  // HDR-Toolbox RGB2Lum (Rec.709), :3
@@ -117,7 +130,9 @@ __global__ void __launch_bounds__(256) tile_scatter_kernel(const T* __restrict__
 #pragma unroll 4
       for (int p = 0; p < kPixPerThread; ++p) {
         const double I = rgb2lum(srgb_pow22(px[3 * p]), srgb_pow22(px[3 * p + 1]), srgb_pow22(px[3 * p + 2]));
-        lsum += log_term(I, as_written);
+        const double lt = log_term(I, as_written);
+        if (isinf(lt)) stats->log_sum = lt;   // as written, I == 1 gives X = +inf: kept out of the fixed-point sum, flagged
+        else lsum += lt;                      // (every writer stores the same value: order-free)
         zeros += (I == 0.0);
       }
     }
@@ -139,8 +154,7 @@ __global__ void __launch_bounds__(256) tile_scatter_kernel(const T* __restrict__
         lsum += s_l[w];
         zeros += s_z[w];
       }
-      atomicAdd(&stats->log_sum, lsum);
-      atomicAdd(&stats->zero_lum, zeros);
+      stats_add(stats, lsum, zeros);
     }
   }
 }
@@ -152,17 +166,16 @@ __global__ void __launch_bounds__(256) frame_stats_kernel(const uint8_t* __restr
   unsigned long long zeros = 0;
   for (size_t p = blockIdx.x * size_t(blockDim.x) + threadIdx.x; p < n_pix; p += size_t(gridDim.x) * blockDim.x) {
     const double I = rgb2lum(srgb_pow22(frame[3 * p]), srgb_pow22(frame[3 * p + 1]), srgb_pow22(frame[3 * p + 2]));
-    lsum += log_term(I, as_written);
+    const double lt = log_term(I, as_written);
+    if (isinf(lt)) stats->log_sum = lt;
+    else lsum += lt;
     zeros += (I == 0.0);
   }
   for (int o = 16; o > 0; o >>= 1) {
     lsum += __shfl_xor_sync(0xFFFFFFFFu, lsum, o);
     zeros += __shfl_xor_sync(0xFFFFFFFFu, zeros, o);
   }
-  if ((threadIdx.x & 31) == 0) {
-    atomicAdd(&stats->log_sum, lsum);
-    atomicAdd(&stats->zero_lum, zeros);
-  }
+  if ((threadIdx.x & 31) == 0) stats_add(stats, lsum, zeros);
 }
 
 // inverse_Reinhard.m:11-23 per pixel. as_written = 1 follows the script literally (IEEE semantics of its
@@ -178,7 +191,8 @@ __global__ void __launch_bounds__(256) inverse_reinhard_kernel(const uint8_t* __
   const double P = double(n_pix);
   const double nz = P - double(stats->zero_lum);
   // :11; the repaired form averages over the non-zero-luminance pixels (an all-black frame stays black)
-  const double G_X = as_written ? exp(stats->log_sum / P) : (nz > 0 ? exp(stats->log_sum / nz) : 1.0);
+  const double log_sum = stats_log_sum(stats);
+  const double G_X = as_written ? exp(log_sum / P) : (nz > 0 ? exp(log_sum / nz) : 1.0);
   double scale;
   if (as_written) {
     const double PB1 = double(stats->zero_lum), PB2 = P - PB1;  // :13-14

@@ -337,7 +337,7 @@ int launch_conv_t(const itmo::ConvParams& p, int total_tiles, int smem_bytes, cu
 // Specialised-epilogue instantiations (itmo::EpiKind): the shapes of the inference forward pass. Returns -1 when the
 // combination is not compiled (the caller then takes the generic kernel).
 template <typename Elem, int BLOCK_N, int SWZ, int EPI>
-int launch_conv_epi(const itmo::ConvParams& p, int total_tiles, int smem_bytes, cudaStream_t stream) {
+int launch_conv_epi(const itmo::ConvParams& p, int total_tiles, int smem_bytes, cudaStream_t stream, int* grid_out) {
   auto kern = itmo::conv_igemm_kernel<Elem, BLOCK_N, SWZ, EPI>;
   static bool configured = false;  // per template instantiation
   if (!configured) {
@@ -373,14 +373,44 @@ int launch_conv_epi(const itmo::ConvParams& p, int total_tiles, int smem_bytes, 
     int pairs = std::min(total_tiles / 2, max_pairs);
     if (p.n_stationary) pairs = pairs / p.n_tiles * p.n_tiles;   // every N tile gets the same number of pairs
     cfg.gridDim = dim3(2 * pairs);
+    if (grid_out) *grid_out = 2 * pairs;
     ITMO_CUDA(cudaLaunchKernelEx(&cfg, kern, p));
     return ITMO_OK;
   }
   int grid = std::min(total_tiles, num_sms());
   if (p.n_stationary) grid = grid / p.n_tiles * p.n_tiles;
+  if (grid_out) *grid_out = grid;
   kern<<<grid, itmo::kNumThreads, smem_bytes, stream>>>(p);
   ITMO_CUDA(cudaGetLastError());
   return ITMO_OK;
+}
+
+// bf16 only: the training step's variants (statistics forward, identity data gradient); -1 = not compiled
+int launch_conv_train(int block_n, int swz, int epi, const itmo::ConvParams& p, int total_tiles, int smem_bytes,
+                      cudaStream_t stream, int* grid_out) {
+  using namespace itmo;
+  using Elem = __nv_bfloat16;
+  constexpr int P = kEpiPair;
+#define ITMO_TRAIN(BN, SW, EP) \
+  if (block_n == BN && swz == SW && epi == (EP)) return launch_conv_epi<Elem, BN, SW, (EP)>(p, total_tiles, smem_bytes, stream, grid_out)
+  ITMO_TRAIN(32, 64, kEpiStats);        // conv2d_2
+  ITMO_TRAIN(64, 64, kEpiStats);        // conv2d_3, conv2d_14
+  ITMO_TRAIN(64, 128, kEpiStats);       // conv2d_4
+  ITMO_TRAIN(128, 128, kEpiStats);      // conv2d_5, 6, 13
+  ITMO_TRAIN(256, 128, kEpiStats);      // conv2d_7 ... 12, transposed convolutions
+  ITMO_TRAIN(64, 64, kEpiStats | P);
+  ITMO_TRAIN(128, 128, kEpiStats | P);
+  ITMO_TRAIN(256, 128, kEpiStats | P);
+  ITMO_TRAIN(32, 64, kEpiIdentity);     // data gradients: N = the layer's input channels
+  ITMO_TRAIN(32, 128, kEpiIdentity);
+  ITMO_TRAIN(64, 128, kEpiIdentity);
+  ITMO_TRAIN(128, 128, kEpiIdentity);
+  ITMO_TRAIN(256, 128, kEpiIdentity);
+  ITMO_TRAIN(64, 128, kEpiIdentity | P);
+  ITMO_TRAIN(128, 128, kEpiIdentity | P);
+  ITMO_TRAIN(256, 128, kEpiIdentity | P);
+#undef ITMO_TRAIN
+  return -1;
 }
 
 template <typename Elem>
@@ -389,7 +419,7 @@ int launch_conv_fast(int block_n, int swz, int epi, const itmo::ConvParams& p, i
   using namespace itmo;
   constexpr int C = kEpiConstAffine;
 #define ITMO_FAST(BN, SW, EP) \
-  if (block_n == BN && swz == SW && epi == (EP)) return launch_conv_epi<Elem, BN, SW, (EP)>(p, total_tiles, smem_bytes, stream)
+  if (block_n == BN && swz == SW && epi == (EP)) return launch_conv_epi<Elem, BN, SW, (EP)>(p, total_tiles, smem_bytes, stream, nullptr)
   ITMO_FAST(32, 64, kEpiConvPool | C);    // conv2d_2
   ITMO_FAST(64, 64, kEpiConv | C);        // conv2d_3
   ITMO_FAST(64, 128, kEpiConvPool | C);   // conv2d_4
@@ -593,6 +623,28 @@ int run_conv(const ConvArgs& a, cudaStream_t stream) {
       b_stage /= 2;
     }
   }
+  // ---- training step variants (bf16): statistics forward / identity data gradient, as pairs where the 3x3 layer is wide
+  static const int allow_train_fast = env_int("ITMO_TRAIN_FAST_EPI", 1);
+  if (allow_train_fast && allow_fast && epi == itmo::kEpiGeneric && a.precision == ITMO_PREC_BF16 && acc_split == 1 &&
+      nm == natural_nm && !a.one_tap && dbg_env == 0 && tma_store && a.out != nullptr && !a.pooled &&
+      a.head_dtype == itmo::kHeadNone && swz >= 64) {
+    const int tiles_x = a.w / (itmo::kBlkW * nm);
+    int kind = 0;
+    if (a.stats && !a.no_relu) kind = itmo::kEpiStats;
+    else if (!a.stats && a.no_relu && a.identity_epi && conv) kind = itmo::kEpiIdentity;
+    const bool compiled = kind == itmo::kEpiStats
+                              ? ((block_n == 32 && swz == 64) || (block_n == 64) || (block_n >= 128 && swz == 128))
+                              : kind == itmo::kEpiIdentity ? ((block_n == 32) || (block_n >= 64 && swz == 128)) : false;
+    if (compiled) {
+      epi = kind;
+      const bool pair_compiled = kind == itmo::kEpiStats ? ((block_n == 64 && swz == 64) || (block_n >= 128 && swz == 128))
+                                                         : (block_n >= 64 && swz == 128);
+      if (allow_pair && conv && pair_compiled && cin >= 96 && tiles_x % 2 == 0 && num_sms() >= 2) {
+        epi |= itmo::kEpiPair;
+        b_stage /= 2;
+      }
+    }
+  }
   static const int fast_bufs = std::max(1, std::min(2, env_int("ITMO_EPI_BUFS", 1)));
   int epi_bufs = (epi != itmo::kEpiGeneric && tma_store) ? fast_bufs : 1;
   const int epi_one = itmo::kNumEpiWarps * 40 * epi_row;
@@ -753,6 +805,13 @@ int run_conv(const ConvArgs& a, cudaStream_t stream) {
     *a.capture = p;
     if (a.capture_epi) *a.capture_epi = epi;
     return ITMO_OK;
+  }
+  if ((epi & 15) == itmo::kEpiStats || (epi & 15) == itmo::kEpiIdentity) {
+    int grid = 0;
+    const int rct = launch_conv_train(block_n, swz, epi, p, total_tiles, smem_bytes, stream, &grid);
+    if (rct == -1) return fail(ITMO_ERR_INVALID, "training kernel variant %d not compiled for BLOCK_N %d / %d-byte rows", epi, block_n, swz);
+    if (a.stats_blocks) *a.stats_blocks = grid;   // rows of the statistics workspace = CTAs launched
+    return rct;
   }
   if (epi != itmo::kEpiGeneric) {
     const int rcf = a.precision == ITMO_PREC_BF16

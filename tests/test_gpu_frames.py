@@ -123,3 +123,16 @@ def test_4k_frame_properties(calibrated_weights):
     assert (out[:416, :416] == alone[:416, :416]).all()
     assert m.launch_count() > 0
     m.close()
+
+
+def test_hdr_output_is_bit_reproducible(model, frame):
+    """The per-frame log-luminance statistic is accumulated with INTEGER atomics (fixed point), so the fused HDR output does
+    not depend on the order in which blocks finish: repeated runs return identical bits."""
+    from cnn_itmo_b200 import frames
+    a = frames.predict_frames(model, frame, out='hdr', key=0.18)
+    for _ in range(3):
+        assert np.array_equal(frames.predict_frames(model, frame, out='hdr', key=0.18), a)
+    u8 = frames.predict_frames(model, frame, out='u8')
+    b = frames.inverse_reinhard(u8, as_written=False)
+    for _ in range(3):
+        assert np.array_equal(frames.inverse_reinhard(u8, as_written=False), b)
