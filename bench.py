@@ -453,7 +453,7 @@ def run_batch_leg(a, hz, precision=None, batch=None, steps=None, with_e2e=True, 
         del hx, hy
 
     per_layer, igemm_flops, igemm_ms = layer_table(graph, layer_times, steps, B, prec, peaks)
-    n_igemm = sum(int(p['launches_per_step']) for p in per_layer[1:])
+    n_igemm = sum(int(p.get('launches_per_step', 0)) for p in per_layer[1:])
     achieved = igemm_flops / (igemm_ms * 1e-3) / 1e12 if igemm_ms > 0 else 0.0
     peak = peaks['tflops_sustained']
     # DRAM bytes per launch from the committed ncu --set full capture of the same launches (profiles/, made by
@@ -478,8 +478,8 @@ def run_batch_leg(a, hz, precision=None, batch=None, steps=None, with_e2e=True, 
                 'flops_per_launch': igemm_flops / max(1, n_igemm),
                 'avg_launch_ms': round(igemm_ms / max(1, n_igemm), 4),
                 'share_of_step': round(igemm_ms / ms_step, 4),
-                'layers': [{k: p[k] for k in ('layer', 'ms_per_step', 'tflops', 'gbs', 'bound', 'frac_of_bound')}
-                           for p in per_layer]}
+                'layers': [{k: p[k] for k in ('layer', 'ms_per_step', 'tflops', 'gbs', 'bound', 'frac_of_bound', 'fused_into')
+                            if k in p} for p in per_layer]}
 
     line = None
     if hz.rank == 0:

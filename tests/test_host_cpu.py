@@ -196,3 +196,24 @@ def test_product_code_never_imports_the_oracle():
             if f.endswith(('.py', '.cu', '.cuh', '.h')):
                 src = open(os.path.join(dirpath, f)).read()
                 assert 'unet_ref' not in src and not re.search(r'^\s*(from|import)\s+oracle', src, flags=re.M), f
+
+
+def test_bench_layer_table_with_and_without_the_fused_stem():
+    """bench.py's per-layer roofline table: with conv2d_1 + conv2d_2 fused (no launch booked under conv2d_1) the first
+    row says so and conv2d_2's row carries both layers' FLOPs; the JSON `layers` list must build in both cases."""
+    import bench
+    from cnn_itmo_b200 import graph
+    peaks = {'tflops_sustained': 1381.5, 'hbm_gbs': 6554.0}
+    keys = ('layer', 'ms_per_step', 'tflops', 'gbs', 'bound', 'frac_of_bound', 'fused_into')
+    flops = {}
+    for fused in (True, False):
+        lt = {l.index: (5.0, 5) for l in graph.LAYERS}
+        if fused:
+            lt[0] = (0.0, 0)
+        per, fl, ms = bench.layer_table(graph, lt, 5, 256, 'fp16', peaks)
+        layers = [{k: p[k] for k in keys if k in p} for p in per]
+        assert len(layers) == 18 and layers[0]['layer'] == 'conv2d_1'
+        assert ('fused_into' in layers[0]) == fused
+        assert sum(int(p.get('launches_per_step', 0)) for p in per[1:]) == 17
+        flops[fused] = fl
+    assert flops[True] > flops[False]          # the first layer's FLOPs are counted with the fused kernel
