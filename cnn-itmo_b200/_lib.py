@@ -19,6 +19,7 @@ NUM_LAYERS = 19
 TRAIN_NO_DROPOUT, TRAIN_FREEZE_MOVING, TRAIN_KEEP_GRADS = 1, 2, 4
 OPT_RMSPROP, OPT_ADAM = 0, 1
 IPC_HANDLE_BYTES = 64
+REINHARD_STATIC_MAX_IMAGES = 256   # ITMO_REINHARD_STATIC_MAX_IMAGES
 
 
 class LayerWeights(ctypes.Structure):
@@ -94,6 +95,8 @@ SIGNATURES = {
     'itmo_virtual_camera': (c_int, [c_void_p, c_int, c_int, c_int, POINTER(CameraParams), c_void_p, c_int, c_void_p]),
     'itmo_reinhard_target': (c_int, [c_void_p, c_int, c_int, c_int, c_double, c_void_p, c_int, c_void_p]),
     'itmo_augment': (c_int, [c_void_p, c_int, c_int, c_int, c_int, POINTER(AffineParams), c_void_p, c_float, c_void_p]),
+    # allocation-free variant of itmo_reinhard_target (static device scratch; no counterpart in the reference)
+    'itmo_reinhard_target_static': (c_int, [c_void_p, c_int, c_int, c_int, c_double, c_void_p, c_int, c_void_p]),
     # fused gradient exchange over NVLink peer memory (SURVEY §8 e, K8)
     'itmo_exchange_create': (c_int, [POINTER(c_void_p), c_int, c_void_p]),
     'itmo_exchange_grads': (c_void_p, [c_void_p]),

@@ -1871,3 +1871,69 @@ int itmo_conv3x3_bn_rgb(int precision, const void* in, int in_dtype, int n, int 
 #include "train_api.cuh"
 #include "exchange_api.cuh"
 #include "datagen_api.cuh"
+
+// ------------------------------------------------------------------------------------------------
+// itmo_reinhard_target_static: itmo_reinhard_target (datagen_api.cuh) for callers that may not allocate — code under CUDA
+// graph capture, tight serving loops, harnesses that forbid cudaMalloc. No counterpart in the reference.
+// Same three kernels, same launch shapes, same result; the scratch of the per-image
+// log-average (64 block partials + G per image, doubles) lives in the file-scope device array below instead of two
+// cudaMallocAsync blocks. Every GPU that loads the library holds the array (133,120 bytes) until exit.
+// ------------------------------------------------------------------------------------------------
+namespace {
+
+constexpr int kStaticTargetMaxImages = ITMO_REINHARD_STATIC_MAX_IMAGES;
+constexpr size_t kStaticTargetDoubles = size_t(kStaticTargetMaxImages) * (itmo::kDgBlocksPerImage + 1);
+// [kStaticTargetMaxImages][kDgBlocksPerImage] block partials, then [kStaticTargetMaxImages] G. In HOST code this name is
+// a stand-in for the symbol, not a device address: kernels get the pointer cudaGetSymbolAddress returns (below).
+static __device__ __align__(256) double g_static_target_scratch[kStaticTargetDoubles];
+
+constexpr int kStaticMaxDevices = 64;
+std::mutex g_static_target_mu;
+double* g_static_target_ptr[kStaticMaxDevices] = {};   // per device: the array's address in THAT device's memory
+
+// Set-up, once per device, with that device current: resolve the symbol to its device address.
+int static_target_scratch(double** out) {
+  int dev = -1;
+  ITMO_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kStaticMaxDevices) return fail(ITMO_ERR_INVALID, "device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(g_static_target_mu);
+  if (!g_static_target_ptr[dev]) {
+    double* ptr = nullptr;
+    cudaError_t e = cudaGetSymbolAddress((void**)&ptr, g_static_target_scratch);
+    if (e != cudaSuccess || !ptr)
+      return fail(ITMO_ERR_CUDA, "cudaGetSymbolAddress(static scratch) failed on device %d: %s", dev, cudaGetErrorString(e));
+    g_static_target_ptr[dev] = ptr;
+  }
+  *out = g_static_target_ptr[dev];
+  return ITMO_OK;
+}
+
+}  // namespace
+
+extern "C" int itmo_reinhard_target_static(const float* hdr_dev, int n, int h, int w, double key, void* out_dev,
+                                           int out_dtype, void* stream) {
+  if (!hdr_dev || !out_dev) return fail(ITMO_ERR_INVALID, "null argument");
+  if (n <= 0 || h <= 0 || w <= 0) return fail(ITMO_ERR_INVALID, "bad shape");
+  if (out_dtype != ITMO_DT_U8 && out_dtype != ITMO_DT_F32) return fail(ITMO_ERR_INVALID, "bad out_dtype");
+  if (n > kStaticTargetMaxImages)
+    return fail(ITMO_ERR_INVALID,
+                "itmo_reinhard_target_static: n = %d images exceeds the static scratch's maximum of %d per call "
+                "(split the batch, or use itmo_reinhard_target)", n, kStaticTargetMaxImages);
+  double* scratch = nullptr;
+  int rc = static_target_scratch(&scratch);
+  if (rc) return rc;
+  cudaStream_t s = (cudaStream_t)stream;
+  double* partial = scratch;                                                         // [n][kDgBlocksPerImage]
+  double* G = scratch + size_t(kStaticTargetMaxImages) * itmo::kDgBlocksPerImage;    // [n]
+  // The array keeps the previous call's contents. Nothing has to start at zero: the first kernel WRITES (does not
+  // accumulate into) every partial the second reads, the second writes every G the third reads.
+  itmo::loglum_partial_kernel<<<dim3(itmo::kDgBlocksPerImage, n), 256, 0, s>>>(hdr_dev, h, w, partial);
+  itmo::geomean_finalize_kernel<<<(n + 127) / 128, 128, 0, s>>>(partial, itmo::kDgBlocksPerImage, double(h) * w, n, G);
+  const dim3 grid(std::max(1, std::min(dg_grid(size_t(h) * w), std::max(1, num_sms() * 8 / n))), n);
+  if (out_dtype == ITMO_DT_U8)
+    itmo::tonemap_kernel<uint8_t><<<grid, 256, 0, s>>>(hdr_dev, (uint8_t*)out_dev, h, w, G, nullptr, 1, key);
+  else
+    itmo::tonemap_kernel<float><<<grid, 256, 0, s>>>(hdr_dev, (float*)out_dev, h, w, G, nullptr, 1, key);
+  ITMO_CUDA(cudaGetLastError());
+  return ITMO_OK;
+}

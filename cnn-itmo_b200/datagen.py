@@ -127,6 +127,24 @@ def reinhard_target_device(hdr, key: float = 0.18, as_float: bool = True):
     return out
 
 
+def reinhard_target_static_into(hdr, out, key: float = 0.18):
+    """reinhard_target_device without any allocation: the caller passes the output tensor ([n,h,w,3] float32 or uint8, same
+    device) and the library's static device scratch holds the per-image log-average (itmo_reinhard_target_static; at most
+    _lib.REINHARD_STATIC_MAX_IMAGES images per call; calls that overlap on the GPU race on that scratch). No counterpart
+    in the reference."""
+    import torch
+    n, h, w, _ = hdr.shape
+    if tuple(out.shape) != (n, h, w, 3) or out.dtype not in (torch.float32, torch.uint8) or out.device != hdr.device:
+        raise ValueError('out must be [n,h,w,3] float32 or uint8 on the device of hdr')
+    if hdr.dtype != torch.float32 or not hdr.is_contiguous() or not out.is_contiguous():
+        raise ValueError('hdr must be contiguous float32, out contiguous')
+    with torch.cuda.device(hdr.device):
+        _lib.check(_lib.load().itmo_reinhard_target_static(hdr.data_ptr(), n, h, w, float(key), out.data_ptr(),
+                                                           _lib.DT_F32 if out.dtype == torch.float32 else _lib.DT_U8,
+                                                           torch.cuda.current_stream().cuda_stream))
+    return out
+
+
 def augment_device(x, params: Sequence[Dict[str, float]], scale: Optional[float] = None):
     """ImageDataGenerator's random transform (main.py:71-76) of a CUDA batch [n,h,w,3] (uint8 0..255, or float32) with one
     parameter set per image -> float32. scale defaults to 1/255 for uint8 input (rescale) and 1 for float input."""

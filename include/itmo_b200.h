@@ -302,6 +302,24 @@ int itmo_exchange_step(itmo_exchange* x, itmo_trainer* t, int optimizer, float l
                        float eps, float grad_scale, void* stream);
 void itmo_exchange_destroy(itmo_exchange* x);
 
+/* ---- allocation-free variant (NO counterpart in the reference) ------------------
+ * itmo_reinhard_target for callers that may not allocate (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc): same kernels, same arguments, bit-identical output, but the per-image log-average scratch
+ * (64 block partials + G per image, doubles) is a file-scope `static __device__` array of the library instead of two
+ * cudaMallocAsync blocks. The call makes no cudaMalloc / cudaFree / cudaMallocAsync and calls no allocating library
+ * routine; it runs on the CURRENT device, asynchronously on `stream`.
+ *   limit: n <= ITMO_REINHARD_STATIC_MAX_IMAGES images per call (any h, w); a larger n returns ITMO_ERR_INVALID and
+ *          launches nothing — split the batch or use itmo_reinhard_target.
+ *   cost : every GPU that loads the library holds the array (256 * 65 * 8 = 133,120 bytes) until the process exits.
+ *   races: ALL calls on a device share the one array — calls that overlap on the GPU (different streams, or two host
+ *          threads on different streams) race on it; keep them on one stream or order them with events. The array keeps
+ *          the previous call's contents; nothing in it has to start at zero (every element is written before it is read).
+ *   The first call on each device resolves the array's device address (cudaGetSymbolAddress); make that call outside a
+ *   stream capture. */
+#define ITMO_REINHARD_STATIC_MAX_IMAGES 256
+int itmo_reinhard_target_static(const float* hdr_dev, int n, int h, int w, double key, void* out_dev, int out_dtype,
+                                void* stream);
+
 #ifdef __cplusplus
 }
 #endif
