@@ -404,15 +404,18 @@ class Model:
             self._range_checked = False
         self._trained_dirty = False
 
-    def train_on_batch(self, x, y, sample_weight=None, class_weight=None):
+    def train_on_batch(self, x, y, sample_weight=None, class_weight=None, prefetch=None):
         """One optimizer step on x [N,512,512,3] (floats in [0,1] like main.py:71's rescale=1./255, or raw uint8) and
-        the target y [N,512,512,3]; returns [loss, accuracy] like Keras with metrics=['accuracy']."""
+        the target y [N,512,512,3]; returns [loss, accuracy] like Keras with metrics=['accuracy']. prefetch: the next
+        step's (x, y), see Trainer.train_on_batch (fit_generator passes its look-ahead batch)."""
         x = self._check_input(x)
         y = np.asarray(y)
         if y.shape != x.shape:
             raise ValueError(f'Error when checking target: expected conv2d_15 to have shape {x.shape[1:]} but got '
                              f'array with shape {y.shape[1:]}')
-        out = self._ensure_trainer().train_on_batch(x, y)
+        if prefetch is not None:
+            prefetch = (self._check_input(prefetch[0]), np.asarray(prefetch[1]))
+        out = self._ensure_trainer().train_on_batch(x, y, prefetch=prefetch)
         self._trained_dirty = True
         return out
 
@@ -438,14 +441,21 @@ class Model:
         for cb in callbacks:
             if hasattr(cb, 'on_train_begin'):
                 cb.on_train_begin({})
+        ahead, done_steps = None, 0
         for epoch in range(int(epochs)):
             for cb in callbacks:
                 if hasattr(cb, 'on_epoch_begin'):
                     cb.on_epoch_begin(epoch, {})
             ls, ac = [], []
+            # one batch of look-ahead: the next batch's first micro-batch is uploaded under this step's compute
+            total_steps = int(epochs) * int(steps_per_epoch)
             for _ in range(int(steps_per_epoch)):
-                x, y = next(it)
-                l, a = self.train_on_batch(x, y)
+                if ahead is None:
+                    ahead = next(it)
+                x, y = ahead
+                done_steps += 1
+                ahead = next(it, None) if done_steps < total_steps else None
+                l, a = self.train_on_batch(x, y, prefetch=ahead)
                 ls.append(l)
                 ac.append(a)
             logs = {'loss': float(np.mean(ls)), 'acc': float(np.mean(ac))}

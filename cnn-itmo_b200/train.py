@@ -241,6 +241,7 @@ class Trainer:
         self.set_weights(weights)
         self.seed_base = int.from_bytes(os.urandom(4), 'little') if seed is None else int(seed)
         self._copy_stream = None
+        self._staged = None         # (key, (xs, ys, event), host arrays) of a prefetched first micro-batch
 
     @property
     def step_index(self) -> int:
@@ -397,15 +398,30 @@ class Trainer:
                                                   self._stream()))
         return sq.value, hits.value
 
-    def train_on_batch(self, x, y, seed: Optional[int] = None, dropout: bool = True) -> List[float]:
+    @staticmethod
+    def _host_batch(x, y):
+        x = np.ascontiguousarray(x if np.asarray(x).dtype == np.uint8 else np.asarray(x, np.float32))
+        y = np.ascontiguousarray(np.asarray(y, np.float32))
+        return x, y
+
+    @staticmethod
+    def _batch_key(x, y):
+        # identity of the arrays AS PASSED (before any dtype conversion makes a copy)
+        x, y = np.asarray(x), np.asarray(y)
+        return (x.ctypes.data, y.ctypes.data, x.shape, x.dtype.str, y.dtype.str)
+
+    def train_on_batch(self, x, y, seed: Optional[int] = None, dropout: bool = True, prefetch=None) -> List[float]:
         """One optimizer step on HOST arrays x [N,h,w,3] (uint8, or float in [0,1]) and y [N,h,w,3] (float target): this
         rank's share of the batch. Returns [loss, accuracy] of the whole (all-rank) batch, like Keras' train_on_batch
         with metrics=['accuracy']. The H2D copy of micro-batch i+1 runs on a side stream while micro-batch i computes
-        (asynchronous only from pinned arrays — model.pinned_empty)."""
+        (asynchronous only from pinned arrays — model.pinned_empty). `prefetch=(x_next, y_next)`: the NEXT step's batch
+        (what fit_generator's look-ahead passes): its first micro-batch is uploaded under this step's last micro-batch,
+        so no copy of the next call is exposed. The arrays must stay unmodified until that call, which must be given the
+        same arrays (otherwise the staged copy is dropped and nothing is lost but the overlap)."""
         import torch
         import torch.distributed as dist
-        x = np.ascontiguousarray(x if np.asarray(x).dtype == np.uint8 else np.asarray(x, np.float32))
-        y = np.ascontiguousarray(np.asarray(y, np.float32))
+        key = self._batch_key(x, y)
+        x, y = self._host_batch(x, y)
         n = x.shape[0]
         world, _ = world_info()
         n_global = n * world
@@ -416,21 +432,25 @@ class Trainer:
         main = torch.cuda.current_stream(self._dev)
         starts = list(range(0, n, self.micro_batch))
 
-        def upload(i0):
+        def upload(i0, hx=x, hy=y):
             # staged on the side stream; the tensors are handed to the compute stream through an event
             with torch.cuda.stream(self._copy_stream):
-                xs = torch.from_numpy(x[i0:i0 + self.micro_batch]).to(self._dev, non_blocking=True)
-                ys = torch.from_numpy(y[i0:i0 + self.micro_batch]).to(self._dev, non_blocking=True)
+                xs = torch.from_numpy(hx[i0:i0 + self.micro_batch]).to(self._dev, non_blocking=True)
+                ys = torch.from_numpy(hy[i0:i0 + self.micro_batch]).to(self._dev, non_blocking=True)
                 ev = torch.cuda.Event()
                 ev.record(self._copy_stream)
             return xs, ys, ev
 
+        staged, self._staged = self._staged, None
         self.zero_grad()
-        nxt = upload(starts[0])
+        nxt = staged[1] if staged is not None and staged[0] == key else upload(starts[0])
         for k, i0 in enumerate(starts):
             xs, ys, ev = nxt
             if k + 1 < len(starts):
                 nxt = upload(starts[k + 1])
+            elif prefetch is not None:
+                px, py = self._host_batch(*prefetch)
+                self._staged = (self._batch_key(*prefetch), upload(0, px, py), (prefetch, px, py))   # keeps the arrays alive
             main.wait_event(ev)
             # BN moving statistics move once per optimizer step (Keras updates them once per batch): last micro-batch only
             self.backward(xs, ys, loss_count, seed=self.micro_seed(step, i0), dropout=dropout,

@@ -372,6 +372,61 @@ def test_loss_decreases_and_model_api(dev):
     m.close()
 
 
+def test_prefetched_next_batch_changes_nothing_but_the_overlap(dev):
+    """Trainer.train_on_batch(prefetch=next batch) uploads the next step's first micro-batch under this step's compute
+    (what Model.fit_generator's look-ahead does, main.py:126-132): losses and weights are bit-identical to plain calls,
+    a prefetch that is not followed by the announced batch is dropped, and fit_generator pulls exactly
+    epochs * steps_per_epoch batches from the generator."""
+    from cnn_itmo_b200 import train
+    import cnn_itmo_b200 as M
+    ws0 = _weights()
+    batches = [T.synthetic_pair(4, H, W, seed=40 + i) for i in range(3)]
+
+    def run(prefetching):
+        tr = train.Trainer(ws0, micro_batch=2, image_hw=(H, W), device=0, optimizer='rmsprop')
+        out = []
+        for i, (x, y) in enumerate(batches):
+            nxt = batches[i + 1] if prefetching and i + 1 < len(batches) else None
+            out.append(tr.train_on_batch(x, y, prefetch=nxt))
+        if prefetching:   # announced batch 0, then trained on batch 2: the staged copy must not be used
+            out.append(tr.train_on_batch(*batches[1], prefetch=batches[0]))
+            out.append(tr.train_on_batch(*batches[2]))
+        else:
+            out.append(tr.train_on_batch(*batches[1]))
+            out.append(tr.train_on_batch(*batches[2]))
+        w = tr.get_weights()
+        tr.close()
+        return out, w
+    a, wa = run(False)
+    b, wb = run(True)
+    assert a == b, (a, b)
+    for la, lb in zip(wa, wb):
+        for k in la:
+            assert np.array_equal(la[k], lb[k]), k
+    # the Keras surface: look-ahead of one batch, no extra pull at the end
+    m = M.Model(M.initial_weights(7), precision='bf16', max_batch=2)
+    m.compile(optimizer='rmsprop', loss='mse', metrics=['accuracy'])
+    m.train_micro_batch = 2
+    m.train_seed = 5          # the Dropout mask stream (None = fresh entropy per engine)
+    pulled = []
+    full = [T.synthetic_pair(2, 512, 512, seed=50 + i) for i in range(4)]
+
+    def gen():
+        for i, b_ in enumerate(full):
+            pulled.append(i)
+            yield b_
+    h = m.fit_generator(gen(), steps_per_epoch=2, epochs=2, verbose=0)
+    assert pulled == [0, 1, 2, 3] and len(h['loss']) == 2 and all(np.isfinite(h['loss']))
+    m2 = M.Model(M.initial_weights(7), precision='bf16', max_batch=2)
+    m2.compile(optimizer='rmsprop', loss='mse', metrics=['accuracy'])
+    m2.train_micro_batch = 2
+    m2.train_seed = 5
+    plain = [m2.train_on_batch(x, y)[0] for x, y in full]
+    assert h['loss'] == [float(np.mean(plain[:2])), float(np.mean(plain[2:]))]
+    m.close()
+    m2.close()
+
+
 def test_adam_resume_continues_bias_correction(dev, tmp_path):
     """save after 2 Adam steps, load, 1 more step == 3 uninterrupted steps, bit for bit (the step counter
     behind Adam's lr_t = lr sqrt(1-b2^t)/(1-b1^t) travels through /optimizer_weights and itmo_train_set_step)."""
