@@ -66,7 +66,9 @@ enum StoreMode : int { kStorePlain = 0, kStoreTf32Rna = 1, kStoreSplit = 2 };
 // Training step (bf16): kEpiStats = z = max(acc + b, 0) stored as is + the BatchNormalization batch statistics of the stored
 // values (ConvParams::stats), 3x3 and transposed convolutions alike; kEpiIdentity = the accumulator stored as is (the
 // data-gradient convolutions).
-enum EpiKind : int { kEpiGeneric = 0, kEpiConv = 1, kEpiConvPool = 2, kEpiConvT = 3, kEpiHead = 4, kEpiStats = 5, kEpiIdentity = 6, kEpiConstAffine = 16, kEpiPair = 32, kEpiHeadConst = 64 };
+// | kEpiRows (conv_rows.cuh): the tile is nm image rows x 128 pixels, M block j = output row nm - 1 - j of the tile and
+// a TMEM lane is a pixel column, so an epilogue warp holds 32 consecutive pixels of one row (store box 32 x 1).
+enum EpiKind : int { kEpiGeneric = 0, kEpiConv = 1, kEpiConvPool = 2, kEpiConvT = 3, kEpiHead = 4, kEpiStats = 5, kEpiIdentity = 6, kEpiConstAffine = 16, kEpiPair = 32, kEpiHeadConst = 64, kEpiRows = 128 };
 
 struct ConvParams {
   CUtensorMap tmA[4];  // activation sources: dims (C, W, H, N), box (BK, 8*NM+2*pad, 16+2*pad, 1)
@@ -429,7 +431,9 @@ __device__ __forceinline__ void epilogue_fast(const ConvParams& p, uint32_t tmem
   constexpr int kGroups = BLOCK_N / kGroupCh;
   constexpr int kHalves = kGroupCh / 32;            // tcgen05.ld x32 per item
   constexpr int kStageB = 40 * kRowB;               // 32 pixel rows + 8 pooled rows
-  const int kTileW = kBlkW * nm;
+  constexpr bool kRows = (EPI & kEpiRows) != 0;
+  const int kTileW = kRows ? 128 : kBlkW * nm;
+  static_assert(!kRows || kKind == kEpiConv || kKind == kEpiHead, "row tiles: plain ConvBN and the fused head");
   static_assert(!kConst || kConvT || BLOCK_N <= 64, "constant-bank affine: cout <= 64");
   static_assert(!kHead || (BLOCK_N == 64 && kConst), "fused head: conv2d_14 only");
   static_assert(sizeof(Elem) == 2, "16-bit element types");
@@ -443,7 +447,7 @@ __device__ __forceinline__ void epilogue_fast(const ConvParams& p, uint32_t tmem
   constexpr bool kPair = (EPI & kEpiPair) != 0;
   const uint32_t cta_rank = kPair ? sm100::cluster_ctarank() : 0u;
   const int tiles_x = p.W / kTileW;
-  const int tiles_y = p.H / kBlkH;
+  const int tiles_y = kRows ? p.H / nm : p.H / kBlkH;
   const int m_tiles = p.NB * tiles_y * tiles_x;
   const int m_units = kPair ? (m_tiles >> 1) : m_tiles;
   const int cta_unit = kPair ? int(blockIdx.x >> 1) : int(blockIdx.x);
@@ -635,7 +639,8 @@ __device__ __forceinline__ void epilogue_fast(const ConvParams& p, uint32_t tmem
           __syncwarp();
           if (lane == 0) {
             const int ng = n_tile * BLOCK_N + g * kGroupCh;          // first column of the staged group
-            const int x0 = tx * kTileW + j * kBlkW, y0 = ty * kBlkH + 4 * q;
+            const int x0 = kRows ? tx * kTileW + 32 * q : tx * kTileW + j * kBlkW;
+            const int y0 = kRows ? ty * nm + (nm - 1 - j) : ty * kBlkH + 4 * q;
             if (kConvT || (kStats && p.mode == kModeConvT2x2)) {
               const int a_row = ng >> (p.cout_log2 + 1);               // kernel row a of this column group
               sm100::tma_store_4d(&p.tmOut[a_row], st_out, ng - (a_row << (p.cout_log2 + 1)), x0, y0, img);
@@ -650,7 +655,8 @@ __device__ __forceinline__ void epilogue_fast(const ConvParams& p, uint32_t tmem
       }
       if constexpr (kHead) {
         // Conv2D(3, 1, activation='sigmoid') (model.py:276) on the post-BN fp32 values
-        const int y = ty * kBlkH + r, x = tx * kTileW + j * kBlkW + c;
+        const int y = kRows ? ty * nm + (nm - 1 - j) : ty * kBlkH + r;
+        const int x = kRows ? tx * kTileW + 32 * q + lane : tx * kTileW + j * kBlkW + c;
         float e0, o0, e1, o1, e2, o2;
         f2_unpack(hh0, e0, o0);
         f2_unpack(hh1, e1, o1);

@@ -295,3 +295,22 @@ def test_conv3x3_bn_small_and_ragged(dev, prec, shape):
     if pool:
         gp = pooled.float().cpu().double().numpy()
         assert (np.abs(gp - ref_pool) <= _tol(ref_pool, prec)).all(), float(np.abs(gp - ref_pool).max())
+
+
+@pytest.mark.parametrize('env', [{'ITMO_ROWS': '0'}, {'ITMO_ROWS_POOL': '1'}], ids=['igemm', 'rows_pool'])
+def test_row_tile_layers_on_the_other_kernel(dev, env):
+    """conv2d_3 / conv2d_4 / conv2d_14 + head shapes run on conv_rows.cuh's row tiles by default (conv2d_4 only with
+    ITMO_ROWS_POOL=1: measured slower). The switches are read once per process, so the same parity cases run in a fresh
+    process on the other kernel: conv_igemm_kernel for all three (ITMO_ROWS=0), and the pooled row-tile variant."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    e = dict(os.environ)
+    e.update(env)
+    r = subprocess.run([sys.executable, '-m', 'pytest', os.path.join(root, 'tests', 'test_gpu_parity.py'), '-m', 'gpu', '-q', '-x',
+                        '-p', 'no:cacheprovider', '-k',
+                        '(every_shape and (256x32+0to64 or 256x64+0to64p or 512x32+64to64)) or fused_head'],
+                       cwd=root, env=e, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+    assert ' passed' in r.stdout and 'failed' not in r.stdout, r.stdout[-2000:]
