@@ -246,7 +246,7 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_rows_kernel(const __grid_
       for (int kb = 0; kb < kb_total; ++kb)
         for (int dx = 0; dx < 3; ++dx)
           sm100::tma_load_4d(smem_b + (kb * 3 + dx) * kRowsBTile, &p.tmB, b_full, kb * kRowsBK, 0, dx, 0, sm100::kEvictLast);
-      int sa = 0;
+      int sa = 0, a_loads = 0;
       uint32_t pa = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
         int m = tile;
@@ -259,8 +259,13 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_rows_kernel(const __grid_
           const CUtensorMap* tmA = &p.tmA[p.seg_map[s]];
           for (int kb = 0; kb < p.seg_kb[s]; ++kb) {
             sm100::mbar_wait(&a_empty[sa], pa ^ 1);
-            sm100::mbar_arrive_expect_tx(&a_full[sa], uint32_t(kRowsABytes));
-            sm100::tma_load_4d(smem_a + sa * kRowsAStage, tmA, &a_full[sa], kb * kRowsBK, x0, y0, img, sm100::kEvictNormal);
+            if ((p.dbg & 16) && a_loads >= n_a) {   // timing experiment (results wrong): no activation traffic after the ring filled
+              sm100::mbar_arrive(&a_full[sa]);
+            } else {
+              sm100::mbar_arrive_expect_tx(&a_full[sa], uint32_t(kRowsABytes));
+              sm100::tma_load_4d(smem_a + sa * kRowsAStage, tmA, &a_full[sa], kb * kRowsBK, x0, y0, img, sm100::kEvictNormal);
+            }
+            ++a_loads;
             if (++sa == n_a) {
               sa = 0;
               pa ^= 1;
@@ -289,8 +294,9 @@ __global__ void __launch_bounds__(kNumThreads, 1) conv_rows_kernel(const __grid_
           sm100::mbar_wait(&a_full[sa], pa);
           sm100::tc_fence_after_sync();
           const uint32_t a_lo = sm100::smem_desc_lo(sm100::smem_u32(smem_a + sa * kRowsAStage));
-          issue_kb_rows<ElemTraits<Elem>::kFmt>(tmem_d, a_lo, a_hi, b_lo0 + uint32_t(kb) * (uint32_t(3 * kRowsBTile) >> 4), b_hi,
-                                                kb == 0);
+          if (!(p.dbg & 64))   // 64: timing experiment without the MMAs
+            issue_kb_rows<ElemTraits<Elem>::kFmt>(tmem_d, a_lo, a_hi, b_lo0 + uint32_t(kb) * (uint32_t(3 * kRowsBTile) >> 4), b_hi,
+                                                  kb == 0);
           sm100::umma_commit(&a_empty[sa]);
           if (++sa == n_a) {
             sa = 0;

@@ -544,7 +544,7 @@ int rows_epi_bytes(const ConvArgs& a) {
 bool rows_eligible(const ConvArgs& a) {
   static const int allow_rows = env_int("ITMO_ROWS", 1);
   static const int dbg_env = env_int("ITMO_DBG", 0);
-  if (!allow_rows || dbg_env != 0 || a.mode != itmo::kModeConv3x3 || a.one_tap || !prec_is16(a.precision) || a.cout != itmo::kRowsCout ||
+  if (!allow_rows || (dbg_env & ~(16 | 32 | 64)) != 0 || a.mode != itmo::kModeConv3x3 || a.one_tap || !prec_is16(a.precision) || a.cout != itmo::kRowsCout ||
       a.c0 <= 0 || a.c0 % itmo::kRowsBK || a.c1 % itmo::kRowsBK || a.stats || a.no_relu || a.capture || a.src0_lo || a.src1_lo ||
       a.row_stride[0] || a.row_stride[1] || a.img_stride[0] || a.img_stride[1] || a.w_tap_stride_rows || a.n <= 0 ||
       a.w % itmo::kRowsTileW || a.h % itmo::kRowsNM)
@@ -612,6 +612,8 @@ int run_conv_rows(const ConvArgs& a, cudaStream_t stream) {
     memcpy(p.c_scale + rep * 64, a.h_scale, 64 * sizeof(float));
     memcpy(p.c_shift + rep * 64, a.h_shift, 64 * sizeof(float));
   }
+  static const int dbg = env_int("ITMO_DBG", 0);
+  p.dbg = dbg;   // timing ablations (results wrong): 16 no activation loads, 32 no epilogue work, 64 no MMAs
   p.sat_count = a.precision == ITMO_PREC_FP16 ? a.sat_count : nullptr;
   p.bias = a.bias;
   p.bn_scale = a.scale;
@@ -627,6 +629,7 @@ int run_conv_rows(const ConvArgs& a, cudaStream_t stream) {
   constexpr int kH = itmo::kEpiHead | itmo::kEpiConstAffine | itmo::kEpiRows;
   constexpr int kC = itmo::kEpiConv | itmo::kEpiConstAffine | itmo::kEpiRows;
   constexpr int kP = itmo::kEpiConvPool | itmo::kEpiConstAffine | itmo::kEpiRows;
+  // (the head's weights as constant-bank operands, kEpiHeadConst, measured neutral here too: 6.47 against 6.48 ms)
   if (a.precision == ITMO_PREC_BF16)
     return head       ? launch_conv_rows<__nv_bfloat16, kH>(p, total_tiles, smem_bytes, stream)
            : a.pooled ? launch_conv_rows<__nv_bfloat16, kP>(p, total_tiles, smem_bytes, stream)
