@@ -750,7 +750,8 @@ def run_train_leg(a, hz, steps=None, warmup=None):
     torch.cuda.synchronize()
     h2d_ms = hz.max_over_ranks((time.perf_counter() - t0) * 1e3)
     e2e_steps = max(1, min(steps, 3))
-    tr.train_on_batch(hx, hy)          # warm-up of the host path (side stream, allocator)
+    tr.train_on_batch(hx, hy, prefetch=(hx, hy))   # warm-up of the host path (side stream, allocator); the loop below is then in
+                                                   # the steady state of a fit_generator epoch (every step finds its first micro-batch staged)
     hz.barrier()
     t0 = time.perf_counter()
     last = None
