@@ -126,6 +126,77 @@ def predict_frames(model, frames_u8, out: str = 'u8', key: float = 0.18) -> np.n
     return yd.cpu().numpy()
 
 
+def predict_frame_batches(model, batches, out: str = 'hdr', key: float = 0.18):
+    """A stream of frame batches (a video): for every uint8 batch [n,h,w,3] of the iterable — all of one shape, in pinned
+    host memory (model.pinned_empty) for the copies to be asynchronous — yields the result of predict_frames as a pinned
+    host array. Three CUDA streams and double-buffered device / host buffers: the upload of batch k + 1 and the download of
+    batch k - 1 run under the kernels of batch k, so a step costs max(copy, compute) instead of their sum (the float32 HDR
+    frame is 4 x the input's bytes). The yielded array is one of two buffers: it is overwritten two batches later — use it
+    (or copy it) before asking for the batch after the next; the buffers (and the three streams) stay with the model for the
+    next call of the same shape and kind."""
+    import torch
+    from .model import pinned_empty
+    dev = torch.device('cuda', model.device)
+    # streams and buffers are kept on the model between calls (page-locking 2 x 100 MB costs more than a 4K step)
+    cache = model.__dict__.setdefault('_frame_stream_cache', {})
+    if 'streams' not in cache:
+        cache['streams'] = tuple(torch.cuda.Stream(dev) for _ in range(3))
+    s_in, s_cmp, s_out = cache['streams']
+    for a_ in cache['streams']:          # an abandoned earlier stream of batches may still be in flight on the shared buffers
+        for b_ in cache['streams']:
+            if a_ is not b_:
+                a_.wait_stream(b_)
+    xd, yd, hy, ht = [None, None], [None, None], [None, None], [None, None]
+    ev_in, ev_cmp, ev_out = [None, None], [None, None], [None, None]
+    shape = None
+    pending = None     # buffer index whose download is in flight and not yet yielded
+    k = 0
+    with torch.cuda.device(dev):
+        for batch in batches:
+            x = _check_frames(batch)
+            if shape is None:
+                shape = x.shape
+                n, h, w, _ = shape
+                bufs = cache.get((shape, out))
+                if bufs is None:
+                    for key_ in [k_ for k_ in cache if k_ != 'streams']:
+                        del cache[key_]               # one shape / kind at a time: a 4K float32 pair is 250 MB of pinned memory
+                    bufs = cache[(shape, out)] = {
+                        'xd': [torch.empty(shape, dtype=torch.uint8, device=dev) for _ in range(2)],
+                        'yd': [torch.empty(shape, dtype=getattr(torch, OUT_DTYPES[out]), device=dev) for _ in range(2)],
+                        'hy': [pinned_empty(shape, np.dtype(OUT_DTYPES[out])) for _ in range(2)]}
+                    bufs['ht'] = [torch.from_numpy(a_) for a_ in bufs['hy']]
+                xd, yd, hy, ht = bufs['xd'], bufs['yd'], bufs['hy'], bufs['ht']
+            elif x.shape != shape:
+                raise ValueError(f'all batches of a stream must have one shape: {shape} then {x.shape}')
+            b = k & 1
+            if ev_cmp[b] is not None:
+                s_in.wait_event(ev_cmp[b])            # the kernels of batch k - 2 have read xd[b]
+            with torch.cuda.stream(s_in):
+                xd[b].copy_(torch.from_numpy(x), non_blocking=True)
+                ev_in[b] = torch.cuda.Event()
+                ev_in[b].record(s_in)
+            s_cmp.wait_event(ev_in[b])
+            if ev_out[b] is not None:
+                s_cmp.wait_event(ev_out[b])           # the download of batch k - 2 has read yd[b]
+            predict_frames_device(model, xd[b].data_ptr(), n, h, w, yd[b].data_ptr(), out, key, s_cmp.cuda_stream)
+            ev_cmp[b] = torch.cuda.Event()
+            ev_cmp[b].record(s_cmp)
+            if pending is not None:                    # batch k - 1: its download was queued last iteration
+                ev_out[pending].synchronize()
+                yield hy[pending]
+            s_out.wait_event(ev_cmp[b])
+            with torch.cuda.stream(s_out):
+                ht[b].copy_(yd[b], non_blocking=True)
+                ev_out[b] = torch.cuda.Event()
+                ev_out[b].record(s_out)
+            pending = b
+            k += 1
+        if pending is not None:
+            ev_out[pending].synchronize()
+            yield hy[pending]
+
+
 def inverse_reinhard(frames_u8, as_written: bool = False, key: float = 0.18, device: int = 0) -> np.ndarray:
     """m-files/inverse_Reinhard.m on the GPU: uint8 CNN-output frames [n,h,w,3] -> float32 HDR."""
     import torch

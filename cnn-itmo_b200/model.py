@@ -190,6 +190,7 @@ class Model:
                               "clipped; use precision='tf32' or 'fp32' for this checkpoint", RuntimeWarning, stacklevel=3)
 
     def close(self):
+        self.__dict__.pop('_frame_stream_cache', None)   # frames.predict_frame_batches' streams and pinned buffers
         if getattr(self, '_ctx', None):
             _lib.load().itmo_destroy(self._ctx)
             self._ctx = ctypes.c_void_p()

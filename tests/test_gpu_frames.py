@@ -136,3 +136,25 @@ def test_hdr_output_is_bit_reproducible(model, frame):
     b = frames.inverse_reinhard(u8, as_written=False)
     for _ in range(3):
         assert np.array_equal(frames.inverse_reinhard(u8, as_written=False), b)
+
+
+def test_streamed_frame_batches_equal_one_call_per_batch(model):
+    """frames.predict_frame_batches (upload / kernels / download on three streams, double-buffered) yields, batch by batch,
+    exactly what predict_frames returns for that batch — five different batches through the two buffers, pinned and
+    ordinary host arrays, and a shape change is refused."""
+    from cnn_itmo_b200 import frames
+    from cnn_itmo_b200.model import pinned_empty
+    batches = []
+    for i in range(5):
+        b = pinned_empty((2, 528, 640, 3), np.uint8) if i % 2 == 0 else np.empty((2, 528, 640, 3), np.uint8)
+        b[...] = R.synthetic_images_u8(2, seed=30 + i, size=640)[:, :528, :640]
+        batches.append(b)
+    for kind in ('hdr', 'u8'):
+        got = [np.array(r, copy=True) for r in frames.predict_frame_batches(model, iter(batches), out=kind)]
+        assert len(got) == len(batches)
+        for b, g in zip(batches, got):
+            want = frames.predict_frames(model, b, out=kind)
+            assert g.dtype == want.dtype and np.array_equal(g, want)
+    assert list(frames.predict_frame_batches(model, iter([]), out='hdr')) == []
+    with pytest.raises(ValueError):
+        list(frames.predict_frame_batches(model, iter([batches[0], batches[0][:1]]), out='u8'))
