@@ -547,7 +547,7 @@ bool rows_eligible(const ConvArgs& a) {
   if (!allow_rows || (dbg_env & ~(16 | 32 | 64)) != 0 || a.mode != itmo::kModeConv3x3 || a.one_tap || !prec_is16(a.precision) || a.cout != itmo::kRowsCout ||
       a.c0 <= 0 || a.c0 % itmo::kRowsBK || a.c1 % itmo::kRowsBK || a.stats || a.no_relu || a.capture || a.src0_lo || a.src1_lo ||
       a.row_stride[0] || a.row_stride[1] || a.img_stride[0] || a.img_stride[1] || a.w_tap_stride_rows || a.n <= 0 ||
-      a.w % itmo::kRowsTileW || a.h % itmo::kRowsNM)
+      a.w % itmo::kRowsTileW || a.h % itmo::kBlkH)   // the shapes conv_igemm_kernel accepts: ITMO_ROWS must not change the API
     return false;
   const bool head = a.head_dtype != itmo::kHeadNone;
   if (head ? (a.out != nullptr || a.pooled != nullptr || !a.head_w || !a.head_b || !a.head_out) : (a.out == nullptr)) return false;

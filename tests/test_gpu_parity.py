@@ -261,7 +261,9 @@ def test_last_conv_with_fused_head(dev, prec):
 
 # ragged / minimum tiles: one 16x8 M block, tiles narrower than the preferred 4-block width, odd tile counts
 SMALL_SHAPES = [(1, 16, 8, 64, 0, 64, False), (1, 16, 16, 32, 0, 32, True), (3, 16, 24, 64, 0, 128, False),
-                (1, 32, 8, 128, 0, 256, True), (2, 16, 40, 32, 64, 64, False), (1, 48, 16, 128, 256, 512, False)]
+                (1, 32, 8, 128, 0, 256, True), (2, 16, 40, 32, 64, 64, False), (1, 48, 16, 128, 256, 512, False),
+                # 64 output channels, width a multiple of 128: conv_rows.cuh's row tiles (one tile wide / three wide, odd counts)
+                (1, 16, 128, 32, 0, 64, False), (3, 48, 384, 64, 0, 64, False), (2, 32, 128, 64, 0, 64, True)]
 
 
 @pytest.mark.parametrize('prec', PRECS)
