@@ -537,9 +537,15 @@ int launch_conv_rows(const itmo::ConvParams& p, int total_tiles, int smem_bytes,
 // The 64-output-channel 3x3 layers on row tiles (conv_rows.cuh): conv2d_3 and conv2d_14 + head of the inference forward
 // pass. Returns 1 when the launch is not of that shape (the caller goes on with conv_igemm_kernel), 0 after a launch,
 // < 0 on errors. ITMO_ROWS=0: A/B.
+int rows_epi_bufs(const ConvArgs& a) {
+  // two staging tiles per epilogue warp: the next 32 pixels are staged while the TMA still reads the last tile. conv2d_3
+  // (HBM-bound, 36 KB of weights: room for them beside two halo stages) 0.82 -> 0.73 ms per 256 images; ITMO_ROWS_EPI_BUFS=1: A/B
+  static const int bufs = std::max(1, std::min(2, env_int("ITMO_ROWS_EPI_BUFS", 2)));
+  return (a.head_dtype != itmo::kHeadNone || a.pooled) ? 1 : bufs;
+}
 int rows_epi_bytes(const ConvArgs& a) {
   if (a.head_dtype != itmo::kHeadNone) return 0;
-  return itmo::kNumEpiWarps * (a.pooled ? itmo::kRowsPoolStageB : 40 * 128);
+  return itmo::kNumEpiWarps * (a.pooled ? itmo::kRowsPoolStageB : 40 * 128 * rows_epi_bufs(a));
 }
 bool rows_eligible(const ConvArgs& a) {
   static const int allow_rows = env_int("ITMO_ROWS", 1);
@@ -584,7 +590,7 @@ int run_conv_rows(const ConvArgs& a, cudaStream_t stream) {
   }
   if (rc) return rc;
   p.epi_bytes = epi_bytes;
-  p.epi_bufs = 1;
+  p.epi_bufs = rows_epi_bufs(a);
   p.n_seg = a.c1 > 0 ? 2 : 1;
   p.seg_map[0] = 0;
   p.seg_kb[0] = a.c0 / itmo::kRowsBK;
