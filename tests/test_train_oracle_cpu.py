@@ -215,3 +215,24 @@ def test_fused_exchange_shards_partition_the_flat_buffer():
             assert e0 == b1 and b1 % 4 == 0
         sizes = [e - b for b, e in cuts]
         assert max(sizes) - min(sizes) <= 4 * world
+
+
+def test_prefetch_identity_of_host_batches():
+    """Trainer.train_on_batch(prefetch=...) recognises the announced batch by the identity of the arrays AS PASSED (address,
+    shape, dtype), before any dtype conversion copies them; the conversion itself keeps uint8 inputs and makes everything
+    else float32 (main.py:71's rescaled floats)."""
+    from cnn_itmo_b200 import train
+    key, host = train.Trainer._batch_key, train.Trainer._host_batch
+    x8 = np.zeros((2, 16, 16, 3), np.uint8)
+    y32 = np.zeros((2, 16, 16, 3), np.float32)
+    x64 = np.zeros((2, 16, 16, 3), np.float64)
+    assert key(x8, y32) == key(x8, y32)
+    assert key(x8, y32) != key(x8.copy(), y32) and key(x8, y32) != key(x8, y32.copy())
+    assert key(x8, y32) != key(x8[:1], y32[:1])                 # same address, other shape
+    assert key(x64, y32) == key(x64, y32)                       # float64 input: converted later, recognised by the original
+    hx, hy = host(x8, y32)
+    assert hx.dtype == np.uint8 and hy.dtype == np.float32 and hx.ctypes.data == x8.ctypes.data and hy.ctypes.data == y32.ctypes.data
+    hx, hy = host(x64, x64)
+    assert hx.dtype == np.float32 and hy.dtype == np.float32
+    hx, _ = host(x8[:, :, ::2], y32)                            # non-contiguous view -> contiguous copy
+    assert hx.flags['C_CONTIGUOUS']
