@@ -263,6 +263,7 @@ class Trainer:
         return self._torch.cuda.current_stream(self._dev).cuda_stream
 
     def close(self):
+        self._staged = None                          # a prefetched micro-batch nobody came for
         if getattr(self, '_h', None):
             _lib.load().itmo_trainer_destroy(self._h)
             self._h = ctypes.c_void_p()
