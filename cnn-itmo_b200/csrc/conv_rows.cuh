@@ -98,23 +98,25 @@ __device__ __forceinline__ void epilogue_rows_pool(const ConvParams& p, uint32_t
     const uint32_t taddr = tmem_base + (uint32_t(32 * q) << 16) + uint32_t(acc) * uint32_t(kRowsNM * kRowsCout);
     const int x0 = tx * kRowsTileW + 32 * q;
     uint32_t keep[32];
-#pragma unroll
+#pragma unroll 1
     for (int jj = 0; jj < 2; ++jj) {
       const int j = 2 * ws + jj;                      // M block; output row 3 - j of the tile
-      uint32_t v[2][32];
-      sm100::tmem_ld_32x32b_x32(taddr + uint32_t(j * kRowsCout), v[0]);
-      sm100::tmem_ld_32x32b_x32(taddr + uint32_t(j * kRowsCout + 32), v[1]);
-      if (lane == 0) sm100::tma_store_wait_read<0>();   // the bulk stores that last read the staging tiles are done with them
-      __syncwarp();
-      sm100::tmem_ld_wait();
+      // one 32-channel half at a time and a ROLLED row loop: with both halves' accumulators, this row's packed values and the
+      // kept row live at once (and both rows' code interleaved) the epilogue spilled 496 bytes under the 384-thread register
+      // bound and ran slower than conv_igemm_kernel's
       uint32_t pk[32];
       uint32_t m2 = 0;
+      if (lane == 0) sm100::tma_store_wait_read<0>();   // the bulk stores that last read the staging tiles are done with them
+      __syncwarp();
 #pragma unroll
       for (int h = 0; h < 2; ++h) {
+        uint32_t v[32];
+        sm100::tmem_ld_32x32b_x32(taddr + uint32_t(j * kRowsCout + h * 32), v);
+        sm100::tmem_ld_wait();
 #pragma unroll
         for (int i = 0; i < 32; i += 2) {
           float r0, r1, f0, f1;
-          relu_bias2(v[h][i], v[h][i + 1], cpair(p.c_bias, h * 32 + i), r0, r1);
+          relu_bias2(v[i], v[i + 1], cpair(p.c_bias, h * 32 + i), r0, r1);
           f2_unpack(f2_fma(f2_pack(r0, r1), cpair(p.c_scale, h * 32 + i), cpair(p.c_shift, h * 32 + i)), f0, f1);
           pk[h * 16 + (i >> 1)] = pack2<Elem>(f0, f1);
         }

@@ -557,10 +557,10 @@ bool rows_eligible(const ConvArgs& a) {
     return false;
   const bool head = a.head_dtype != itmo::kHeadNone;
   if (head ? (a.out != nullptr || a.pooled != nullptr || !a.head_w || !a.head_b || !a.head_out) : (a.out == nullptr)) return false;
-  // conv2d_4 (pool fused, two channel blocks): measured 9 % SLOWER on row tiles than on conv_igemm_kernel's two-M-block tile
-  // with resident weights (1.76 against 1.61 ms per 256 images, same box) — twice the halo bytes per tile, and the two rows
-  // of a pooling pair serialise on one staging tile. Opt-in for A/B only.
-  static const int allow_rows_pool = env_int("ITMO_ROWS_POOL", 0);
+  // conv2d_4 (pool fused, two channel blocks): 1.57 -> 1.30 ms per 256 images same-box on row tiles. (The first version of the
+  // pooled epilogue spilled 496 bytes under the 384-thread register bound and measured 9 % SLOWER than conv_igemm_kernel;
+  // one 32-channel half at a time and a rolled row loop keep it in registers.) ITMO_ROWS_POOL=0: A/B.
+  static const int allow_rows_pool = env_int("ITMO_ROWS_POOL", 1);
   if (a.pooled && (!allow_rows_pool || (a.h & 1) || (a.w & 1))) return false;
   const int kb_total = (a.c0 + a.c1) / itmo::kRowsBK;
   const int epi_bytes = rows_epi_bytes(a);
