@@ -469,7 +469,7 @@ def run_batch_leg(a, hz, precision=None, batch=None, steps=None, with_e2e=True, 
                 traffic = tj['dram_bytes_per_launch_avg']
                 traffic_src = os.path.relpath(tpath, ROOT) + f" (captured in {tj.get('precision')}: same bytes)"
                 break
-    roofline = {'bound': 'tensor', 'kernel': 'itmo::conv_igemm_kernel (+ itmo::stem_fused_kernel for the first two layers, itmo::conv_rows_kernel for conv2d_3 / conv2d_14)', 'achieved': round(achieved, 2),
+    roofline = {'bound': 'tensor', 'kernel': 'itmo::conv_igemm_kernel (+ itmo::stem_fused_kernel for the first two layers, itmo::conv_rows_kernel for conv2d_3 / conv2d_4 / conv2d_14)', 'achieved': round(achieved, 2),
                 'peak': peak, 'unit': 'TFLOP/s', 'frac': round(achieved / peak, 4), 'traffic': traffic,
                 'traffic_unit': 'DRAM bytes per launch (ncu dram__bytes_read.sum + dram__bytes_write.sum)',
                 'traffic_source': traffic_src,
